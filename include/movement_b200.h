@@ -1,0 +1,219 @@
+/* movement_b200.h -- C ABI of the B200-native mesh-relocation hot path.
+ *
+ * The reference (mesh-adaptation/movement) has no FFI: every arithmetic step is a
+ * Firedrake `assemble` / `interpolate` or a PETSc KSP/SNES solve reached from Python.
+ * Each entry point below replaces one such call site; the citation after "replaces:" is
+ * the reference file:line (relative to the reference checkout) whose arithmetic the
+ * function performs.  The Python package `movement_b200` binds these with ctypes
+ * (movement_b200/_lib.py); INTEGRATION.md shows the stub a reference maintainer adds.
+ *
+ * Conventions
+ *  - All array arguments are plain pointers.  Unless stated otherwise they may be
+ *    DEVICE pointers (torch-owned) or HOST pointers: the library inspects them with
+ *    cudaPointerGetAttributes and stages host buffers itself (inside the call).
+ *  - Layouts are Firedrake's `dat.data` layouts: scalar [V], vector [V,d], tensor
+ *    [V,d,d] (row-major), P0 [C]; cell-node map [C,d+1] int32; all reals are fp64.
+ *  - Every function returns an mv_status; mv_last_error() gives the message.
+ *  - Handles are not thread-safe; one handle per GPU / process.  Work is enqueued on the
+ *    stream set by mv_set_stream (default: the legacy default stream); a function syncs
+ *    the stream only when it returns a scalar to the host.
+ *  - There is no CPU fallback: without a CUDA device every compute call fails with
+ *    MV_ERR_CUDA.
+ */
+#ifndef MOVEMENT_B200_H
+#define MOVEMENT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  MV_OK = 0,
+  MV_ERR_BADARG = 1,
+  MV_ERR_CUDA = 2,
+  MV_ERR_NOT_CONVERGED = 3, /* inner linear solve hit maxit */
+  MV_ERR_VALENCE = 4,       /* a vertex has more neighbours than MV_MAX_ROW */
+  MV_ERR_COMM = 5,
+  MV_ERR_UNSUPPORTED = 6
+} mv_status;
+
+typedef struct mv_mesh mv_mesh; /* ingested topology + constant operators on the xi-mesh */
+typedef struct mv_ma mv_ma;     /* Monge-Ampere mover state */
+
+/* operators a linear-algebra call can name */
+enum { MV_OP_MASS = 0, MV_OP_STIFFNESS = 1, MV_OP_MASS_PLUS_STIFFNESS = 2 };
+
+/* built-in (fused) monitor functions -- replaces: movement/monitor.py:138-143,
+ * test/monitors.py:9-16, demos/monge_ampere_helmholtz.py:54-61,115-122,
+ * demos/monge_ampere_3d.py:13-15,52-69 */
+enum {
+  MV_MON_CONST = 0,     /* m = 1 */
+  MV_MON_BALL = 1,      /* params: c[3], radius, amplitude, width : 1 + a/cosh^2(w(|x-c|^2 - r^2)) */
+  MV_MON_BALL_RAW = 2,  /* as BALL but (|x-c|^2 - r) unsquared radius (test/monitors.py) */
+  MV_MON_GAUSS_HESS = 3,/* params: x0,y0,w,alpha : 1 + alpha |Hess exp(-|x-x0|^2/w^2)|_F / max */
+  MV_MON_SINATAN3 = 4,  /* params: alpha : 1 + alpha (H:H)/max, H = Hess sinatan3 */
+  MV_MON_USER = 100     /* caller writes the monitor field itself */
+};
+
+/* fields of an mv_ma that the caller owns and binds (device pointers, fp64) */
+enum {
+  MV_F_XI = 0,      /* [V,d]  computational coordinates            mover.py:97-99    */
+  MV_F_X = 1,       /* [V,d]  physical coordinates                 mover.py:96       */
+  MV_F_PHI = 2,     /* [V]    monge_ampere.py:412-417 */
+  MV_F_PHI_OLD = 3, /* [V]    */
+  MV_F_H = 4,       /* [V,d,d]*/
+  MV_F_H_OLD = 5,   /* [V,d,d]*/
+  MV_F_GRAD_PHI = 6,/* [V,d]  monge_ampere.py:178-179 */
+  MV_F_MONITOR = 7, /* [V]    monge_ampere.py:177     */
+  MV_F_VOLUME = 8,  /* [C]    mover.py:101-102        */
+  MV_F_ORIG_VOLUME = 9, /* [C] monge_ampere.py:182    */
+  MV_F_RESIDUAL = 10,   /* [V] assembled a - theta*m_l (monge_ampere.py:409) */
+  MV_F_COUNT = 11
+};
+
+/* what mv_mesh_get can copy out (host or device destination) -- used by tests */
+enum {
+  MV_GET_ROW_NNZ = 0,   /* int32 [V]            */
+  MV_GET_SLICE_PTR = 1, /* int64 [nslices+1]    */
+  MV_GET_COLS = 2,      /* int32 [sell_len]     */
+  MV_GET_MASS = 3,      /* f64   [sell_len]     */
+  MV_GET_STIFF = 4,     /* f64   [sell_len]     */
+  MV_GET_LUMPED = 5,    /* f64   [V]            */
+  MV_GET_CELL_VOL = 6,  /* f64   [C]            */
+  MV_GET_BF_NORMAL = 7, /* f64   [F,d]          */
+  MV_GET_BF_AREA = 8,   /* f64   [F]            */
+  MV_GET_BF_CELL = 9    /* int32 [F]            */
+};
+
+/* ---- library --------------------------------------------------------------------- */
+int mv_version(void);
+const char* mv_last_error(void);
+int mv_device_count(void);
+int mv_set_device(int device);
+int mv_set_stream(void* cuda_stream);
+int mv_sync(void);
+
+/* ---- ingest (replaces: movement/mover.py:49-102 -- mesh copy, function spaces, cell
+ * volumes; monge_ampere.py:176-184 -- total volume; and the operator assembly Firedrake
+ * does inside every LinearVariationalSolver: monge_ampere.py:327,437,476,
+ * laplacian_smoothing.py:68).
+ *   n_owned_vertices / n_owned_cells: rows / cells this rank owns (== V / C on one GPU);
+ *   owned entities come first in the local numbering, ghosts after.               */
+int mv_mesh_create(int dim, int64_t V, int64_t C, const double* coords, const int32_t* cells,
+                   int64_t F, const int32_t* bfacet_verts, const int32_t* bfacet_tags,
+                   int64_t n_owned_vertices, int64_t n_owned_cells, mv_mesh** out);
+void mv_mesh_destroy(mv_mesh* m);
+/* info[0..9] = V, C, F, nnz, sell_len, nslices, max_row, dim, n_owned_vertices, n_owned_cells */
+int mv_mesh_info(const mv_mesh* m, int64_t* info);
+/* scalars[0..2] = total_volume (owned cells), sum m_l^2 (owned), sum m_l (owned) */
+int mv_mesh_scalars(const mv_mesh* m, double* scalars);
+int mv_mesh_get(const mv_mesh* m, int what, void* dst);
+
+/* ---- tangling (replaces: movement/tangling.py:26-29 and :39-53) --------------------
+ * detJ = det[x1-x0 ... xd-x0] in cell-node-map order, evaluated without FMA contraction so
+ * the sign agrees bit-for-bit with the CPU oracle; ratio = detJ/detJ0; count(ratio <= 0)
+ * over owned cells.  `ratio` may be NULL.                                             */
+int mv_tangle_init(mv_mesh* m, const double* coords, double* detJ0);
+int mv_tangle_check(mv_mesh* m, const double* coords, const double* detJ0, double* ratio,
+                    int64_t* count);
+
+/* ---- sparse linear algebra (replaces: PETSc KSP cg + bjacobi/ilu,
+ * movement/solver_parameters.py:62-71 as used at monge_ampere.py:340,441-448,483 and
+ * laplacian_smoothing.py:75) -----------------------------------------------------
+ * y = A x for ncomp interleaved components [V,ncomp].                                 */
+int mv_spmv(mv_mesh* m, int op, int ncomp, const double* x, double* y);
+/* Jacobi-preconditioned CG, ncomp independent right-hand sides sharing one matrix
+ * stream.  x holds the initial guess on entry.  mask (uint16 per vertex, bit c set =
+ * component c is a Dirichlet dof whose value in x is kept) may be NULL.  rhs may be NULL
+ * (zero).  Stops when sqrt(r.D^-1 r) <= max(rtol*ref, atol) for every component, with
+ * ref = max over {rhs, initial residual} of the same norm.  project_mean: treat the
+ * operator as singular with constant nullspace (rhs and solution projected to zero mean
+ * over all ranks).  iters / relres (per component, length ncomp) may be NULL.        */
+int mv_pcg_solve(mv_mesh* m, int op, int ncomp, const double* rhs, double* x,
+                 const uint16_t* mask, double rtol, double atol, int maxit, int project_mean,
+                 int* iters, double* relres);
+
+/* ---- Monge-Ampere pieces ---------------------------------------------------------- */
+int mv_ma_create(mv_mesh* m, mv_ma** out);
+void mv_ma_destroy(mv_ma* ma);
+int mv_ma_bind(mv_ma* ma, int field, double* device_ptr);
+/* replaces: monge_ampere.py:246-272 (axis-aligned branch).  fixed_tags: boundary tags with
+ * a full zero Dirichlet condition.  Returns MV_ERR_UNSUPPORTED if a segment is not
+ * axis-aligned (EquationBC branch, monge_ampere.py:274-309, not built yet).          */
+int mv_ma_set_boundary(mv_ma* ma, int n_fixed, const int32_t* fixed_tags);
+/* uint16 per owned vertex, bit c set = component c of grad_phi is a Dirichlet dof */
+int mv_ma_get_bcmask(mv_ma* ma, uint16_t* dst);
+int mv_ma_set_solver(mv_ma* ma, double rtol, double atol, int maxit_mass, int maxit_poisson);
+int mv_ma_set_monitor(mv_ma* ma, int kind, int nparams, const double* params);
+/* replaces: monge_ampere.py:311-342 + :501 -- M g = int psi grad(phi_old), d components */
+int mv_ma_l2_project(mv_ma* ma, int* iters);
+/* replaces: monge_ampere.py:226-241 (+ :505-506 when the monitor is built in):
+ * x = xi + grad_phi, and m(x) evaluated and normalised in the same pass.             */
+int mv_ma_update_coordinates(mv_ma* ma);
+/* evaluate the built-in monitor at arbitrary coordinates (monge_ampere.py:181)        */
+int mv_ma_eval_monitor(mv_ma* ma, const double* coords, double* m_out);
+/* replaces: monge_ampere.py:507-517 + mover.py:199-217.
+ * out[0..5] = theta, relative_l2_residual, vol_max, vol_min, vol_mean, vol_cov        */
+int mv_ma_diagnostics(mv_ma* ma, int use_H_old, double* out);
+/* replaces: monge_ampere.py:419-449 + :535 -- K dphi = dt * residual, phi = phi_old+dphi */
+int mv_ma_pseudotimestep(mv_ma* ma, double pseudo_dt, int* iters);
+/* replaces: monge_ampere.py:451-485 + :536 -- M H = -int div(tau).grad(phi) + bdry      */
+int mv_ma_equidistribute(mv_ma* ma, int* iters);
+/* replaces: monge_ampere.py:537-538 */
+int mv_ma_advance(mv_ma* ma);
+/* K relaxation iterations without convergence tests (bench / profiling helper);
+ * trace[K*6] receives mv_ma_diagnostics' output per iteration, cg_iters[K*3] the inner
+ * iteration counts (l2 projection, poisson, hessian).                                */
+int mv_ma_relax_iterate(mv_ma* ma, double pseudo_dt, int niter, double* trace, int* cg_iters);
+
+/* raw pieces exposed for parity tests */
+int mv_ma_l2_rhs(mv_mesh* m, const double* phi, double* b);            /* monge_ampere.py:328 */
+int mv_ma_hess_rhs(mv_mesh* m, const double* phi, double* c);          /* monge_ampere.py:477-480 */
+int mv_ma_assemble_a(mv_mesh* m, const double* mon, const double* H, double* a); /* :406-409 */
+
+/* ---- cell volumes + diagnostics for Laplacian / spring movers
+ * (replaces: laplacian_smoothing.py:119, spring.py:274, mover.py:199-217)
+ * stats[0..3] = max, min, mean, coefficient of variation                              */
+int mv_cell_volumes(mv_mesh* m, const double* coords, double* volume, double* stats);
+
+/* ---- Laplacian smoothing (replaces: laplacian_smoothing.py:64-77 + :109-117)
+ * Solves K v = 0 per component with v prescribed where mask bit is set (values already in
+ * v), then x += v*dt.  displacement_norm = ||v*dt||_2.                                  */
+int mv_laplace_move(mv_mesh* m, double* v, const uint16_t* mask, double dt, double* x,
+                    double rtol, double atol, int maxit, int* iters, double* displacement_norm);
+
+/* ---- lineal springs (replaces: spring.py:70-146 edge geometry, :148-181 stiffness,
+ * :183-235 Dirichlet rows, :266 dense solve)                                          */
+int mv_spring_edge_count(mv_mesh* m, int64_t* n_edges);
+/* edges [E,2] int32 (i<j, sorted), length [E], tangent [E,2], angle [E]; any may be NULL */
+int mv_spring_edge_geometry(mv_mesh* m, const double* coords, int32_t* edges, double* length,
+                            double* tangent, double* angle);
+/* u = K(coords)^-1 forcing with rows of masked vertices replaced by identity;
+ * coords += u*dt; displacement [V,2] = u*dt.                                          */
+int mv_spring_move(mv_mesh* m, double* coords, const double* forcing, const uint16_t* mask,
+                   double dt, double* displacement, double rtol, double atol, int maxit,
+                   int* iters, double* displacement_norm);
+/* y = K(coords) x for the row-replaced spring matrix (tests: spring.py:184-235); mask bit c
+ * set = dof (v,c) is a Dirichlet row (identity).  mask may be NULL.                    */
+int mv_spring_apply(mv_mesh* m, const double* coords, const uint16_t* mask, const double* x,
+                    double* y);
+
+/* ---- multi-GPU (replaces: the MPI halo exchange / allreduce implicit in PyOP2 and PETSc;
+ * SURVEY 5.8).  nccl_lib_path: path of libnccl.so.2; unique_id: 128 bytes from
+ * mv_comm_unique_id on rank 0, broadcast by the caller.                               */
+int mv_comm_unique_id(const char* nccl_lib_path, void* unique_id_128);
+int mv_comm_init(const char* nccl_lib_path, const void* unique_id_128, int rank, int nranks);
+int mv_comm_finalize(void);
+/* halo plan: for each neighbour rank, the local owned vertices to send (send_idx grouped by
+ * neighbour via send_ptr) and the contiguous ghost range received from it.             */
+int mv_mesh_set_halo(mv_mesh* m, int n_neighbours, const int32_t* neighbour_ranks,
+                     const int64_t* send_ptr, const int32_t* send_idx, const int64_t* recv_ptr);
+int mv_halo_exchange(mv_mesh* m, int ncomp, double* vec);
+int mv_allreduce_sum(double* device_scalars, int n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MOVEMENT_B200_H */

@@ -1,0 +1,189 @@
+// Multi-GPU plumbing: one process per GPU, NCCL over NVLink 5 / NVSwitch.
+//
+// replaces: the MPI traffic that is implicit in the reference -- PyOP2 halo
+//           exchanges behind every assemble/interpolate/assign and the MPI_Allreduce inside
+//           every PETSc KSP dot product / norm and adapt_common's function_data_{max,min,sum}.
+//
+// The path shards by vertex ownership (owner computes): the only data-path collectives are
+//   * forward halo exchange of a vertex field (owned -> ghost), grouped ncclSend/ncclRecv,
+//     receiving straight into the contiguous ghost segment of the vector;
+//   * ncclAllReduce of a handful of device-resident fp64 scalars (sum / max / min).
+// NCCL is dlopen'ed so that the single-GPU library has no link-time dependency on it.
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include "mv_internal.cuh"
+
+namespace mv {
+
+struct NcclApi {
+  void* lib = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+static NcclApi g_nccl;
+static ncclComm_t g_comm = nullptr;
+static int g_rank = 0, g_nranks = 1;
+
+#define MV_NCCL(call)                                                                   \
+  do {                                                                                  \
+    ncclResult_t r__ = (call);                                                          \
+    if (r__ != ncclSuccess) {                                                           \
+      set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call,                           \
+                g_nccl.GetErrorString ? g_nccl.GetErrorString(r__) : "nccl error");     \
+      return MV_ERR_COMM;                                                               \
+    }                                                                                   \
+  } while (0)
+
+static int load_nccl(const char* path) {
+  if (g_nccl.lib) return MV_OK;
+  void* lib = dlopen(path && path[0] ? path : "libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!lib) {
+    set_error("cannot dlopen NCCL (%s): %s", path ? path : "libnccl.so.2", dlerror());
+    return MV_ERR_COMM;
+  }
+#define SYM(field, name)                                         \
+  *(void**)(&g_nccl.field) = dlsym(lib, name);                   \
+  if (!g_nccl.field) {                                           \
+    set_error("NCCL symbol %s missing", name);                   \
+    return MV_ERR_COMM;                                          \
+  }
+  SYM(GetUniqueId, "ncclGetUniqueId");
+  SYM(CommInitRank, "ncclCommInitRank");
+  SYM(CommDestroy, "ncclCommDestroy");
+  SYM(AllReduce, "ncclAllReduce");
+  SYM(Send, "ncclSend");
+  SYM(Recv, "ncclRecv");
+  SYM(GroupStart, "ncclGroupStart");
+  SYM(GroupEnd, "ncclGroupEnd");
+  SYM(GetErrorString, "ncclGetErrorString");
+#undef SYM
+  g_nccl.lib = lib;
+  return MV_OK;
+}
+
+bool comm_active() { return g_comm != nullptr && g_nranks > 1; }
+int comm_size() { return g_nranks; }
+
+int allreduce_dev(double* d, int n, int op) {
+  if (!comm_active()) return MV_OK;
+  const ncclRedOp_t rop = op == 0 ? ncclSum : (op == 1 ? ncclMax : ncclMin);
+  MV_NCCL(g_nccl.AllReduce(d, d, (size_t)n, ncclDouble, rop, g_comm, g_stream));
+  return MV_OK;
+}
+int allreduce_sum_dev(double* d, int n) { return allreduce_dev(d, n, 0); }
+int allreduce_volstats_dev(double* dout) {
+  MV_CHECK(allreduce_dev(dout + 0, 1, 0));
+  MV_CHECK(allreduce_dev(dout + 1, 1, 1));
+  MV_CHECK(allreduce_dev(dout + 2, 1, 2));
+  return MV_OK;
+}
+
+template <int C>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_halo_pack(int64_t n, const int* __restrict__ idx, const double* __restrict__ vec, double* __restrict__ buf) {
+  const int64_t tot = n * C;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < tot; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t k = i / C;
+    const int c = (int)(i - k * C);
+    buf[i] = vec[(int64_t)__ldg(&idx[k]) * C + c];
+  }
+}
+
+int halo_exchange(mv_mesh* m, int C, double* vec) {
+  if (!comm_active() || m->halo.nn == 0) return MV_OK;
+  Halo& h = m->halo;
+  const int64_t nsend = h.send_ptr[h.nn];
+  const int grid = grid_for(nsend * C);
+  switch (C) {
+    case 1: k_halo_pack<1><<<grid, MV_BLOCK, 0, g_stream>>>(nsend, h.send_idx, vec, h.send_buf); break;
+    case 2: k_halo_pack<2><<<grid, MV_BLOCK, 0, g_stream>>>(nsend, h.send_idx, vec, h.send_buf); break;
+    case 3: k_halo_pack<3><<<grid, MV_BLOCK, 0, g_stream>>>(nsend, h.send_idx, vec, h.send_buf); break;
+    case 4: k_halo_pack<4><<<grid, MV_BLOCK, 0, g_stream>>>(nsend, h.send_idx, vec, h.send_buf); break;
+    case 9: k_halo_pack<9><<<grid, MV_BLOCK, 0, g_stream>>>(nsend, h.send_idx, vec, h.send_buf); break;
+    default: set_error("halo_exchange: unsupported ncomp %d", C); return MV_ERR_UNSUPPORTED;
+  }
+  MV_KERNEL_CHECK();
+  MV_NCCL(g_nccl.GroupStart());
+  for (int k = 0; k < h.nn; ++k) {
+    const int64_t ns = h.send_ptr[k + 1] - h.send_ptr[k], nr = h.recv_ptr[k + 1] - h.recv_ptr[k];
+    if (ns > 0) MV_NCCL(g_nccl.Send(h.send_buf + h.send_ptr[k] * C, (size_t)(ns * C), ncclDouble, h.ranks[k], g_comm, g_stream));
+    if (nr > 0)
+      MV_NCCL(g_nccl.Recv(vec + (m->Vown + h.recv_ptr[k]) * C, (size_t)(nr * C), ncclDouble, h.ranks[k], g_comm, g_stream));
+  }
+  MV_NCCL(g_nccl.GroupEnd());
+  return MV_OK;
+}
+
+}  // namespace mv
+
+using namespace mv;
+
+extern "C" int mv_comm_unique_id(const char* nccl_lib_path, void* unique_id_128) {
+  if (!unique_id_128) return MV_ERR_BADARG;
+  MV_CHECK(load_nccl(nccl_lib_path));
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+  ncclUniqueId id;
+  MV_NCCL(g_nccl.GetUniqueId(&id));
+  memcpy(unique_id_128, &id, sizeof(id));
+  return MV_OK;
+}
+
+extern "C" int mv_comm_init(const char* nccl_lib_path, const void* unique_id_128, int rank, int nranks) {
+  if (!unique_id_128 || rank < 0 || rank >= nranks) return MV_ERR_BADARG;
+  MV_CHECK(load_nccl(nccl_lib_path));
+  ncclUniqueId id;
+  memcpy(&id, unique_id_128, sizeof(id));
+  MV_NCCL(g_nccl.CommInitRank(&g_comm, nranks, id, rank));
+  g_rank = rank;
+  g_nranks = nranks;
+  return MV_OK;
+}
+
+extern "C" int mv_comm_finalize(void) {
+  if (g_comm) {
+    cudaStreamSynchronize(g_stream);
+    g_nccl.CommDestroy(g_comm);
+    g_comm = nullptr;
+  }
+  g_nranks = 1;
+  g_rank = 0;
+  return MV_OK;
+}
+
+extern "C" int mv_mesh_set_halo(mv_mesh* m, int nn, const int32_t* ranks, const int64_t* send_ptr, const int32_t* send_idx,
+                                const int64_t* recv_ptr) {
+  if (!m || nn < 0 || (nn > 0 && (!ranks || !send_ptr || !send_idx || !recv_ptr))) return MV_ERR_BADARG;
+  Halo& h = m->halo;
+  h.nn = nn;
+  h.ranks.assign(ranks, ranks + nn);
+  h.send_ptr.assign(send_ptr, send_ptr + nn + 1);
+  h.recv_ptr.assign(recv_ptr, recv_ptr + nn + 1);
+  dev_free(h.send_idx);
+  dev_free(h.send_buf);
+  const int64_t nsend = nn ? send_ptr[nn] : 0;
+  if (m->Vown + (nn ? recv_ptr[nn] : 0) != m->V) {
+    set_error("mv_mesh_set_halo: ghost count %lld does not match V - n_owned = %lld", (long long)(nn ? recv_ptr[nn] : 0),
+              (long long)(m->V - m->Vown));
+    return MV_ERR_BADARG;
+  }
+  MV_CHECK(dev_alloc(&h.send_idx, nsend));
+  MV_CHECK(dev_alloc(&h.send_buf, nsend * (size_t)(m->dim * m->dim)));
+  if (nsend) MV_CUDA(cudaMemcpyAsync(h.send_idx, send_idx, nsend * sizeof(int), cudaMemcpyDefault, g_stream));
+  MV_CUDA(cudaStreamSynchronize(g_stream));
+  return MV_OK;
+}
+
+extern "C" int mv_halo_exchange(mv_mesh* m, int ncomp, double* vec) {
+  if (!m || !vec) return MV_ERR_BADARG;
+  return halo_exchange(m, ncomp, vec);
+}
+
+extern "C" int mv_allreduce_sum(double* device_scalars, int n) { return allreduce_sum_dev(device_scalars, n); }

@@ -1,0 +1,336 @@
+// Internal declarations shared by the translation units of libmovement_b200.so.
+// Nothing here is part of the ABI (see include/movement_b200.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+
+#include "movement_b200.h"
+
+#define MV_MAX_ROW 96        // max neighbours (incl. self) of one vertex
+#define MV_SLICE 32          // SELL slice height == warp size
+#define MV_BLOCK 256
+#define MV_MAX_COMP 9
+#define MV_RED_SLOTS 24      // doubles per block in the partials buffer
+#define MV_MAX_BLOCKS 2368   // 148 SMs x 16: upper bound on persistent grids
+
+namespace mv {
+
+void set_error(const char* fmt, ...);
+extern cudaStream_t g_stream;
+extern int g_nsm;
+
+#define MV_CUDA(call)                                                                  \
+  do {                                                                                 \
+    cudaError_t e__ = (call);                                                          \
+    if (e__ != cudaSuccess) {                                                          \
+      mv::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+      return MV_ERR_CUDA;                                                              \
+    }                                                                                  \
+  } while (0)
+
+#define MV_CHECK(call)              \
+  do {                              \
+    int s__ = (call);               \
+    if (s__ != MV_OK) return s__;   \
+  } while (0)
+
+#define MV_KERNEL_CHECK() MV_CUDA(cudaGetLastError())
+
+// ---------------------------------------------------------------------------------
+// device memory helpers
+// ---------------------------------------------------------------------------------
+template <typename T>
+int dev_alloc(T** p, size_t n) {
+  *p = nullptr;
+  if (n == 0) n = 1;
+  MV_CUDA(cudaMalloc((void**)p, n * sizeof(T)));
+  return MV_OK;
+}
+template <typename T>
+void dev_free(T*& p) {
+  if (p) cudaFree(p);
+  p = nullptr;
+}
+bool is_device_ptr(const void* p);
+
+// Stage an input that may live on the host: returns a device pointer valid until the
+// Staged object dies (async copy on g_stream).
+struct Staged {
+  void* dev = nullptr;
+  bool owned = false;
+  ~Staged() {
+    if (owned && dev) cudaFreeAsync(dev, g_stream);
+  }
+  int in(const void* src, size_t bytes);              // host or device -> device (read)
+  int out_begin(void* dst, size_t bytes);             // prepare device buffer for an output
+  int out_end(void* dst, size_t bytes);               // copy back if dst is host
+  template <typename T>
+  T* as() { return (T*)dev; }
+};
+
+// ---------------------------------------------------------------------------------
+// structures
+// ---------------------------------------------------------------------------------
+struct Sell {
+  int64_t nrows = 0;       // owned rows
+  int64_t nslices = 0;
+  int64_t len = 0;         // padded length
+  int64_t nnz = 0;
+  int maxw = 0;
+  int64_t* slice_ptr = nullptr;  // [nslices+1]
+  int* cols = nullptr;           // [len]
+  int* row_nnz = nullptr;        // [nrows]
+};
+
+struct Halo {
+  int nn = 0;
+  std::vector<int> ranks;
+  std::vector<int64_t> send_ptr, recv_ptr;  // host copies
+  int* send_idx = nullptr;                  // device [send_ptr[nn]]
+  double* send_buf = nullptr;               // device [send_ptr[nn]*MV_MAX_COMP]
+};
+
+struct Reduce {
+  double* partials = nullptr;   // [MV_MAX_BLOCKS*MV_RED_SLOTS]
+  unsigned* counter = nullptr;  // ticket for the last-block pattern
+};
+
+struct PcgWork {
+  double *r = nullptr, *p = nullptr, *q = nullptr;  // [V*MV_MAX_COMP] (p spans ghosts)
+  double* scal = nullptr;   // device scalars, see pcg.cu
+  int* flags = nullptr;     // device: [0]=done, [1]=iterations, [2]=breakdown
+  int* h_flags = nullptr;   // pinned host mirror
+  double* h_scal = nullptr; // pinned host mirror
+};
+
+}  // namespace mv
+
+struct mv_mesh {
+  int dim = 0;
+  int64_t V = 0, C = 0, F = 0, Vown = 0, Cown = 0;
+  double* xi = nullptr;     // [V*dim] coordinates at ingest (computational mesh)
+  int* cells = nullptr;     // [C*(dim+1)]
+  int* v2c_ptr = nullptr;   // [Vown+1]
+  int* v2c = nullptr;       // entries cell*(dim+1)+loc, ascending per vertex
+  // boundary facets
+  int* bf_verts = nullptr;  // [F*dim]
+  int* bf_tags = nullptr;   // [F]
+  int* bf_cell = nullptr;   // [F]
+  double* bf_normal = nullptr;  // [F*dim]
+  double* bf_area = nullptr;    // [F]
+  int* v2f_ptr = nullptr;   // [Vown+1]
+  int* v2f = nullptr;       // entries f*dim+loc
+  std::vector<int> h_bf_tags;   // host copy (small)
+  // operators
+  mv::Sell pat;
+  double* Mval = nullptr;
+  double* Kval = nullptr;
+  double* MKval = nullptr;   // lazily built M+K
+  double* ml = nullptr;      // [Vown] lumped mass
+  double* vol = nullptr;     // [C] cell volumes on xi
+  double* dinvM = nullptr;   // [Vown]
+  double* dinvK = nullptr;
+  double* dinvMK = nullptr;
+  double total_volume = 0, ml_sumsq = 0, ml_sum = 0;
+  // spring data (lazy)
+  int* edge_opp = nullptr;   // [sell_len] opposite vertex of the '+' cell for (row,col)
+  // work
+  mv::Reduce red;
+  mv::PcgWork pcg;
+  mv::Halo halo;
+  double* tmp_vec = nullptr;   // [V*MV_MAX_COMP]
+};
+
+struct mv_ma {
+  mv_mesh* mesh = nullptr;
+  double* f[MV_F_COUNT] = {nullptr};
+  uint16_t* bc_mask = nullptr;  // [V]
+  bool have_bc = false;
+  double* rhs = nullptr;        // [V*MV_MAX_COMP] assembled right-hand sides
+  double* a = nullptr;          // [V] assembled int psi m det(I+H)
+  double* dphi = nullptr;       // [V]
+  double* mon_raw = nullptr;    // [V]
+  double* dscal = nullptr;      // device scalars
+  double* h_scal = nullptr;     // pinned
+  int mon_kind = MV_MON_USER;
+  double mon_params[8] = {0};
+  double rtol = 1e-12, atol = 1e-50;
+  int maxit_mass = 500, maxit_poisson = 100000;
+};
+
+namespace mv {
+
+// PCG device scalar slots: scal[slot*16 + comp]
+enum { S_RZ = 0, S_PQ = 1, S_RZNEW = 2, S_BETA = 3, S_THR = 4, S_REF = 5, S_BB = 6, S_SUM = 7, S_NSLOTS = 8 };
+#define SC(slot, c) ((slot) * 16 + (c))
+
+struct LinOp {
+  const double* val = nullptr;            // SELL values; nullptr selects the matrix-free spring operator
+  const double* dinv = nullptr;           // inverse diagonal, per vertex (dpd=0) or per dof (dpd=1)
+  int dpd = 0;
+  int coupled = 0;                        // components form one vector (one alpha/beta)
+  const double* spring_coords = nullptr;
+};
+int spring_apply_dev(mv_mesh* m, const double* coords, const uint16_t* mask, const double* x, double* y, bool dot);
+int pcg_solve_spring(mv_mesh* m, const double* coords, const double* dinv_dof, double* x, const uint16_t* mask,
+                     double rtol, double atol, int maxit, int* iters);
+int ensure_pcg_workspace(mv_mesh* m);
+int exclusive_scan_i32(const int* in, int* out, int64_t n);
+
+// host-side entry points shared across translation units
+int pcg_solve(mv_mesh* m, int op, int ncomp, const double* rhs, double* x, const uint16_t* mask,
+              double rtol, double atol, int maxit, int project_mean, int* iters, double* relres);
+int spmv(mv_mesh* m, int op, int ncomp, const double* x, double* y);
+int op_arrays(mv_mesh* m, int op, const double** val, const double** dinv);
+int halo_exchange(mv_mesh* m, int ncomp, double* vec);
+int allreduce_sum_dev(double* dscal, int n);
+int allreduce_dev(double* dscal, int n, int op);  // op: 0 sum, 1 max, 2 min
+int allreduce_volstats_dev(double* dout);  // [0] sum, [1] max, [2] min
+int volume_stats_device(mv_mesh* m, const double* x, const double* mon, const double* vol0, double* volume,
+                        double* dout, int64_t global_cells);
+bool comm_active();
+int comm_size();
+int grid_for(int64_t nthreads_needed, int blocks_per_sm = 8);
+
+// ---------------------------------------------------------------------------------
+// device helpers
+// ---------------------------------------------------------------------------------
+#ifdef __CUDACC__
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Deterministic grid-wide sum of N doubles per thread.
+// Every thread of every block must call this (no early exits).  The block that takes
+// the last ticket adds the per-block partials in a fixed order and hands the totals to
+// `fin(total)` (executed by thread 0 of that block).  Results are independent of block
+// scheduling order, so repeated runs give identical bits.
+template <int N, typename Fin>
+__device__ __forceinline__ void grid_reduce_sum(double (&v)[N], double* partials,
+                                                unsigned* counter, Fin fin) {
+  static_assert(N <= MV_RED_SLOTS, "too many reduction slots");
+  __shared__ double s_red[MV_BLOCK / 32][MV_RED_SLOTS];
+  __shared__ bool s_last;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+#pragma unroll
+  for (int n = 0; n < N; ++n) {
+    double t = warp_sum(v[n]);
+    if (lane == 0) s_red[wid][n] = t;
+  }
+  __syncthreads();
+  if (threadIdx.x < N) {
+    double t = 0.0;
+    for (int w = 0; w < nw; ++w) t += s_red[w][threadIdx.x];
+    partials[(size_t)blockIdx.x * MV_RED_SLOTS + threadIdx.x] = t;
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned ticket = atomicAdd(counter, 1u);
+    s_last = (ticket == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  double tot[N];
+#pragma unroll
+  for (int n = 0; n < N; ++n) {
+    double t = 0.0;
+    for (unsigned b = threadIdx.x; b < gridDim.x; b += blockDim.x)
+      t += __ldcg(&partials[(size_t)b * MV_RED_SLOTS + n]);
+    t = warp_sum(t);
+    if (lane == 0) s_red[wid][n] = t;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int n = 0; n < N; ++n) {
+      double t = 0.0;
+      for (int w = 0; w < nw; ++w) t += s_red[w][n];
+      tot[n] = t;
+    }
+    *counter = 0u;
+    fin(tot);
+  }
+}
+
+// atomic max / min for non-negative doubles through their order-preserving bit pattern
+__device__ __forceinline__ void atomic_max_pos(double* addr, double v) {
+  atomicMax((unsigned long long*)addr, (unsigned long long)__double_as_longlong(v));
+}
+__device__ __forceinline__ void atomic_min_pos(double* addr, double v) {
+  atomicMin((unsigned long long*)addr, (unsigned long long)__double_as_longlong(v));
+}
+
+// P1 geometry of one simplex: volume and basis-function gradients.
+template <int D>
+struct CellGeom {
+  double vol;
+  double det;
+  double g[D + 1][D];
+};
+
+template <int D>
+__device__ __forceinline__ void load_cell_coords(const double* __restrict__ x, const int* cv,
+                                                 double (&xc)[D + 1][D]) {
+#pragma unroll
+  for (int j = 0; j <= D; ++j)
+#pragma unroll
+    for (int a = 0; a < D; ++a) xc[j][a] = __ldg(&x[(size_t)cv[j] * D + a]);
+}
+
+__device__ __forceinline__ void cell_geom(const double (&xc)[3][2], CellGeom<2>& o) {
+  const double a = xc[1][0] - xc[0][0], b = xc[2][0] - xc[0][0];
+  const double c = xc[1][1] - xc[0][1], d = xc[2][1] - xc[0][1];
+  const double det = a * d - b * c;
+  const double inv = 1.0 / det;
+  o.det = det;
+  o.vol = 0.5 * fabs(det);
+  o.g[1][0] = d * inv;
+  o.g[1][1] = -b * inv;
+  o.g[2][0] = -c * inv;
+  o.g[2][1] = a * inv;
+  o.g[0][0] = -(o.g[1][0] + o.g[2][0]);
+  o.g[0][1] = -(o.g[1][1] + o.g[2][1]);
+}
+
+__device__ __forceinline__ void cell_geom(const double (&xc)[4][3], CellGeom<3>& o) {
+  double e1[3], e2[3], e3[3];
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    e1[a] = xc[1][a] - xc[0][a];
+    e2[a] = xc[2][a] - xc[0][a];
+    e3[a] = xc[3][a] - xc[0][a];
+  }
+  // rows of J^-1 are (e2 x e3, e3 x e1, e1 x e2)/det
+  double c1[3] = {e2[1] * e3[2] - e2[2] * e3[1], e2[2] * e3[0] - e2[0] * e3[2], e2[0] * e3[1] - e2[1] * e3[0]};
+  double c2[3] = {e3[1] * e1[2] - e3[2] * e1[1], e3[2] * e1[0] - e3[0] * e1[2], e3[0] * e1[1] - e3[1] * e1[0]};
+  double c3[3] = {e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0]};
+  const double det = e1[0] * c1[0] + e1[1] * c1[1] + e1[2] * c1[2];
+  const double inv = 1.0 / det;
+  o.det = det;
+  o.vol = fabs(det) * (1.0 / 6.0);
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    o.g[1][a] = c1[a] * inv;
+    o.g[2][a] = c2[a] * inv;
+    o.g[3][a] = c3[a] * inv;
+    o.g[0][a] = -(o.g[1][a] + o.g[2][a] + o.g[3][a]);
+  }
+}
+
+template <int D>
+__device__ __forceinline__ void load_cell(const int* __restrict__ cells, int64_t c, int (&cv)[D + 1]) {
+#pragma unroll
+  for (int j = 0; j <= D; ++j) cv[j] = __ldg(&cells[c * (D + 1) + j]);
+}
+
+#endif  // __CUDACC__
+
+}  // namespace mv
