@@ -250,3 +250,22 @@ class MAState:
         use_current_stream()
         L.check(L.load().mv_ma_relax_iterate(self.handle, dt, niter, trace, its))
         return np.array(trace[:]).reshape(niter, 6), np.array(its[:]).reshape(niter, 3)
+
+
+def device_mesh_from(mesh):
+    """Ingest a :class:`movement_b200.mesh.Mesh` (one-off)."""
+    part = mesh.part
+    dm = DeviceMesh(mesh.coordinates.tensor, mesh.cells, mesh.bfacets, mesh.btags,
+                    n_owned_vertices=mesh.n_owned_vertices, n_owned_cells=mesh.n_owned_cells)
+    if part is not None:
+        lib = L.load()
+        nn = len(part.neighbours)
+        L.check(lib.mv_mesh_set_halo(dm.handle, nn, L.ptr(np.ascontiguousarray(part.neighbours, dtype=np.int32)),
+                                     L.ptr(np.ascontiguousarray(part.send_ptr, dtype=np.int64)),
+                                     L.ptr(np.ascontiguousarray(part.send_idx, dtype=np.int32)),
+                                     L.ptr(np.ascontiguousarray(part.recv_ptr, dtype=np.int64))))
+        dm.global_cells = part.global_num_cells
+        dm.global_vertices = part.global_num_vertices
+    else:
+        dm.global_cells, dm.global_vertices = dm.C, dm.V
+    return dm

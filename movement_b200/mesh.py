@@ -1,0 +1,397 @@
+"""Mesh adaptor: the minimal Firedrake-shaped surface the movers ingest.
+
+The reference reads ``mesh.coordinates.dat.data_with_halos`` ([V,d] f64), the P1 cell-node map
+([C,d+1] i32) and the exterior-facet markers (movement/mover.py:49,83; movement/spring.py:
+210-216).  On this box there is no Firedrake, so the same data comes from the generators
+below, which reproduce Firedrake's ``UnitSquareMesh`` ("left" diagonal) / ``UnitCubeMesh``
+(six Kuhn tetrahedra per hexahedron) layouts; :func:`from_firedrake` ingests a
+live Firedrake mesh when one is importable.
+
+A coordinate / boundary-value field is a :class:`Function`: a torch tensor (CUDA when a
+device is visible, the product path; CPU otherwise so that host logic can be unit-tested)
+plus a Firedrake-like ``.dat.data`` host view.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+
+def _default_device():
+    if torch.cuda.is_available():
+        return torch.device("cuda", torch.cuda.current_device())
+    return torch.device("cpu")
+
+
+class _Dat:
+    """``Function.dat``: host views of the field (``data``, ``data_ro``, ``data_with_halos``)."""
+
+    def __init__(self, f):
+        self._f = f
+
+    @property
+    def data(self):
+        return self._f._host_view(writable=True)
+
+    data_with_halos = data
+
+    @property
+    def data_ro(self):
+        return self._f._host_view(writable=False)
+
+    data_ro_with_halos = data_ro
+
+    @property
+    def norm(self):
+        return float(torch.linalg.vector_norm(self._f.tensor))
+
+
+class Function:
+    """A nodal (P1 scalar/vector/tensor) or cellwise (P0) field.
+
+    ``.tensor`` is the device tensor the kernels read and write.  ``.dat.data`` is a host
+    numpy array: on a CUDA field it is a mirror that is refreshed from the device when the
+    device copy is newer and uploaded again before the next device use (it is assumed to
+    have been written once handed out, as Firedrake assumes for ``dat.data``).
+    """
+
+    def __init__(self, space_or_function, name=None, val=None):
+        if isinstance(space_or_function, Function):
+            src = space_or_function
+            self.space = src.space
+            self._t = src.tensor.clone()
+        else:
+            self.space = space_or_function
+            self._t = torch.zeros(self.space.shape, dtype=torch.float64, device=self.space.mesh.device)
+            if val is not None:
+                self.assign(val)
+        self.name = name
+        self._host = None
+        self._host_dirty = False   # host mirror may hold user writes
+        self._dev_newer = True     # device copy changed since the last download
+        self.dat = _Dat(self)
+
+    # -- device side ---------------------------------------------------------------------
+    @property
+    def tensor(self):
+        if self._host_dirty:
+            self._t.copy_(torch.from_numpy(self._host), non_blocking=False)
+            self._host_dirty = False
+        return self._t
+
+    def written(self):
+        """Tell the field its device tensor was modified by a kernel."""
+        self._dev_newer = True
+        return self
+
+    # -- host side -----------------------------------------------------------------------
+    def _host_view(self, writable):
+        if self._t.device.type == "cpu":
+            a = self._t.numpy()
+            if not writable:
+                a = a.view()
+                a.flags.writeable = False
+            return a
+        if self._host is None:
+            self._host = np.empty(tuple(self._t.shape), dtype=np.float64)
+            self._dev_newer = True
+        if self._dev_newer and not self._host_dirty:
+            self._host[...] = self._t.cpu().numpy()
+            self._dev_newer = False
+        if writable:
+            self._host_dirty = True
+            return self._host
+        a = self._host.view()
+        a.flags.writeable = False
+        return a
+
+    # -- Firedrake-like helpers ----------------------------------------------------------
+    def function_space(self):
+        return self.space
+
+    def assign(self, other):
+        t = self.tensor
+        if isinstance(other, Function):
+            t.copy_(other.tensor)
+        elif isinstance(other, torch.Tensor):
+            t.copy_(other.to(t.device, torch.float64).expand_as(t))
+        else:
+            a = np.asarray(other, dtype=np.float64)
+            t.copy_(torch.from_numpy(np.broadcast_to(a, tuple(t.shape)).copy()).to(t.device))
+        return self.written()
+
+    def interpolate(self, expr):
+        """``expr``: Function / array / constant / callable ``x[V,d] -> values`` (vectorised
+        torch).  Stands in for Firedrake's ``interpolate`` of a UFL expression."""
+        if callable(expr) and not isinstance(expr, (Function, torch.Tensor)):
+            val = expr(self.space.mesh.coordinates.tensor)
+            if isinstance(val, (tuple, list)):
+                val = torch.stack([torch.as_tensor(v, dtype=torch.float64, device=self._t.device).expand(self._t.shape[0])
+                                   for v in val], dim=1)
+            return self.assign(val)
+        return self.assign(expr)
+
+    def copy(self, deepcopy=True):
+        return Function(self)
+
+    def __repr__(self):
+        return f"Function({self.name or ''}, shape={tuple(self._t.shape)}, device={self._t.device})"
+
+
+class FunctionSpace:
+    """Token naming a field layout on a mesh: 'P1', 'P1_vec', 'P1_ten', 'P0', 'edge', 'edge_vec'."""
+
+    def __init__(self, mesh, kind):
+        self.mesh = mesh
+        self.kind = kind
+
+    @property
+    def shape(self):
+        m, d = self.mesh, self.mesh.geometric_dimension
+        return {
+            "P1": (m.num_vertices(),), "P1_vec": (m.num_vertices(), d), "P1_ten": (m.num_vertices(), d, d),
+            "P0": (m.num_cells(),),
+        }[self.kind]
+
+    def __eq__(self, other):
+        return isinstance(other, FunctionSpace) and other.mesh is self.mesh and other.kind == self.kind
+
+    def __ne__(self, other):
+        return not self.__eq__(other)
+
+    def __hash__(self):
+        return hash((id(self.mesh), self.kind))
+
+
+class _ExteriorFacets:
+    def __init__(self, mesh):
+        self._mesh = mesh
+
+    @property
+    def unique_markers(self):
+        return [int(t) for t in np.unique(self._mesh.btags)]
+
+
+class DirichletBC:
+    """Stand-in for ``firedrake.DirichletBC(space, value, tags)`` on the coordinate space
+    (movement/laplacian_smoothing.py:103-106, movement/spring.py:193-221)."""
+
+    def __init__(self, space, value, sub_domain):
+        self._space = space
+        self._original_arg = value
+        if isinstance(sub_domain, (str, int, np.integer)):
+            sub_domain = (sub_domain,)
+        self.sub_domain = tuple(sub_domain)
+        mesh = space.mesh
+        tags = mesh.exterior_facets.unique_markers if self.sub_domain == ("on_boundary",) else self.sub_domain
+        sel = np.isin(mesh.btags, np.asarray(list(tags), dtype=np.int64)) if len(tags) else np.zeros(len(mesh.btags), bool)
+        self.nodes = np.unique(mesh.bfacets[sel]).astype(np.int64)
+
+    def function_space(self):
+        return self._space
+
+    def values(self):
+        """Boundary values as a [V,d] device tensor (only rows ``nodes`` are meaningful)."""
+        v = self._original_arg
+        shape = self._space.shape
+        dev = self._space.mesh.device
+        if isinstance(v, Function):
+            return v.tensor
+        if isinstance(v, torch.Tensor):
+            return v.to(dev, torch.float64).expand(shape)
+        a = np.broadcast_to(np.asarray(v, dtype=np.float64), shape)
+        return torch.from_numpy(a.copy()).to(dev)
+
+
+class Mesh:
+    """P1 simplex mesh: device-resident coordinates + host topology.
+
+    ``Mesh(coords, cells, bfacets, btags)`` builds from arrays; ``Mesh(function)`` (a coordinate
+    :class:`Function`) makes a mesh that shares topology with the function's mesh and owns that
+    function as its coordinates -- the idiom of movement/mover.py:49.
+    """
+
+    def __init__(self, coords, cells=None, bfacets=None, btags=None, device=None, part=None, degree=1):
+        if isinstance(coords, Function):
+            src = coords.space.mesh
+            self.cells, self.bfacets, self.btags = src.cells, src.bfacets, src.btags
+            self.device, self.part, self._degree = src.device, src.part, src._degree
+            self._dim = src._dim
+            self._nv = src._nv
+            self._spaces = {}
+            self.coordinates = Function(self.function_space("P1_vec"), name="Coordinates")
+            self.coordinates.assign(coords)
+            return
+        coords = np.ascontiguousarray(coords, dtype=np.float64)
+        if coords.ndim == 1:
+            coords = coords[:, None]
+        self._dim = coords.shape[1]
+        self._nv = int(coords.shape[0])
+        self.cells = np.ascontiguousarray(cells, dtype=np.int32)
+        d = self._dim
+        self.bfacets = np.zeros((0, d), np.int32) if bfacets is None else np.ascontiguousarray(bfacets, dtype=np.int32).reshape(-1, d)
+        self.btags = np.zeros((0,), np.int32) if btags is None else np.ascontiguousarray(btags, dtype=np.int32)
+        self.device = torch.device(device) if device is not None else _default_device()
+        self.part = part          # None on one GPU; a partition.LocalPart when distributed
+        self._degree = degree
+        self._spaces = {}
+        self.coordinates = Function(self.function_space("P1_vec"), name="Coordinates")
+        self.coordinates.assign(coords)
+
+    # -- Firedrake-like queries ----------------------------------------------------------
+    @property
+    def topological_dimension(self):
+        return self._dim
+
+    @property
+    def geometric_dimension(self):
+        return self._dim
+
+    def num_vertices(self):
+        return self._nv
+
+    def num_cells(self):
+        return int(self.cells.shape[0])
+
+    @property
+    def exterior_facets(self):
+        return _ExteriorFacets(self)
+
+    def function_space(self, kind):
+        if kind not in self._spaces:
+            self._spaces[kind] = FunctionSpace(self, kind)
+        return self._spaces[kind]
+
+    def coordinate_degree(self):
+        return self._degree
+
+    # owned counts (== totals on one GPU)
+    @property
+    def n_owned_vertices(self):
+        return self.part.n_owned_vertices if self.part is not None else self.num_vertices()
+
+    @property
+    def n_owned_cells(self):
+        return self.part.n_owned_cells if self.part is not None else self.num_cells()
+
+
+# --------------------------------------------------------------------------------------
+# generators (layouts: SURVEY 8d; verified against the reference's tangling KATs and demo traces)
+# --------------------------------------------------------------------------------------
+def square_arrays(nx, ny, Lx=1.0, Ly=1.0):
+    xs = np.linspace(0.0, Lx, nx + 1)
+    ys = np.linspace(0.0, Ly, ny + 1)
+    X, Y = np.meshgrid(xs, ys, indexing="ij")
+    coords = np.stack([X.ravel(), Y.ravel()], axis=1)
+    ii, jj = np.meshgrid(np.arange(nx, dtype=np.int64), np.arange(ny, dtype=np.int64), indexing="ij")
+    q0 = (ii * (ny + 1) + jj).ravel()
+    q1, q3 = q0 + 1, q0 + (ny + 1)
+    q2 = q3 + 1
+    cells = np.empty((2 * nx * ny, 3), dtype=np.int32)
+    cells[0::2, 0], cells[0::2, 1], cells[0::2, 2] = q0, q1, q3
+    cells[1::2, 0], cells[1::2, 1], cells[1::2, 2] = q1, q2, q3
+    j = np.arange(ny)
+    i = np.arange(nx)
+    bf = np.concatenate([
+        np.stack([j, j + 1], axis=1),
+        np.stack([nx * (ny + 1) + j, nx * (ny + 1) + j + 1], axis=1),
+        np.stack([i * (ny + 1), (i + 1) * (ny + 1)], axis=1),
+        np.stack([i * (ny + 1) + ny, (i + 1) * (ny + 1) + ny], axis=1)]).astype(np.int32)
+    bt = np.concatenate([np.full(ny, 1), np.full(ny, 2), np.full(nx, 3), np.full(nx, 4)]).astype(np.int32)
+    return coords, cells, bf, bt
+
+
+_KUHN = np.array([[0, 1, 3, 7], [0, 1, 7, 5], [0, 5, 7, 4], [0, 3, 2, 7], [0, 6, 4, 7], [0, 2, 6, 7]])
+
+
+def cube_arrays(nx, ny, nz):
+    xs, ys, zs = (np.linspace(0.0, 1.0, n + 1) for n in (nx, ny, nz))
+    Z, Y, X = np.meshgrid(zs, ys, xs, indexing="ij")
+    coords = np.stack([X.ravel(), Y.ravel(), Z.ravel()], axis=1)
+    sx, sy, sz = 1, nx + 1, (nx + 1) * (ny + 1)
+    kk, jj, ii = np.meshgrid(np.arange(nz, dtype=np.int64), np.arange(ny, dtype=np.int64),
+                             np.arange(nx, dtype=np.int64), indexing="ij")
+    v0 = (kk * sz + jj * sy + ii).ravel()
+    off = np.array([0, sx, sy, sx + sy, sz, sx + sz, sy + sz, sx + sy + sz], dtype=np.int64)
+    cells = np.empty((v0.size, 6, 4), dtype=np.int32)
+    for t in range(6):
+        for l in range(4):
+            cells[:, t, l] = v0 + off[_KUHN[t, l]]
+    cells = cells.reshape(-1, 4)
+    # boundary faces, per bounding plane, straight from the hex faces (two triangles each):
+    # the Kuhn split of a hex face (a,b,c,d) with a the lowest and d the highest corner is (a,b,d),(a,c,d)
+    def quad_faces(a, b, c, d):
+        return np.concatenate([np.stack([a, b, d], axis=1), np.stack([a, c, d], axis=1)])
+
+    def grid(n1, n2):
+        p, q = np.meshgrid(np.arange(n1, dtype=np.int64), np.arange(n2, dtype=np.int64), indexing="ij")
+        return p.ravel(), q.ravel()
+
+    bf, bt = [], []
+    j, k = grid(ny, nz)
+    for tag, i0 in ((1, 0), (2, nx)):
+        a = k * sz + j * sy + i0
+        bf.append(quad_faces(a, a + sy, a + sz, a + sy + sz)); bt.append(np.full(2 * a.size, tag))
+    i, k = grid(nx, nz)
+    for tag, j0 in ((3, 0), (4, ny)):
+        a = k * sz + j0 * sy + i
+        bf.append(quad_faces(a, a + sx, a + sz, a + sx + sz)); bt.append(np.full(2 * a.size, tag))
+    i, j = grid(nx, ny)
+    for tag, k0 in ((5, 0), (6, nz)):
+        a = k0 * sz + j * sy + i
+        bf.append(quad_faces(a, a + sx, a + sy, a + sx + sy)); bt.append(np.full(2 * a.size, tag))
+    return coords, cells, np.concatenate(bf).astype(np.int32), np.concatenate(bt).astype(np.int32)
+
+
+def _maybe_distribute(arrays, distribute):
+    from . import parallel
+
+    coords, cells, bf, bt = arrays
+    if distribute is None:
+        distribute = parallel.is_active()
+    if not distribute:
+        return Mesh(coords, cells, bf, bt)
+    from .partition import partition_mesh
+
+    lp = partition_mesh(coords, cells, bf, bt, parallel.rank(), parallel.size())
+    return Mesh(lp.coords, lp.cells, lp.bfacets, lp.btags, part=lp)
+
+
+def UnitSquareMesh(nx, ny=None, distribute=None):
+    return _maybe_distribute(square_arrays(nx, nx if ny is None else ny), distribute)
+
+
+def RectangleMesh(nx, ny, Lx, Ly, distribute=None):
+    return _maybe_distribute(square_arrays(nx, ny, Lx, Ly), distribute)
+
+
+def UnitCubeMesh(nx, ny=None, nz=None, distribute=None):
+    ny = nx if ny is None else ny
+    nz = nx if nz is None else nz
+    return _maybe_distribute(cube_arrays(nx, ny, nz), distribute)
+
+
+def UnitTriangleMesh():
+    return Mesh(np.array([[0.0, 0.0], [1.0, 0.0], [0.0, 1.0]]), np.array([[0, 1, 2]]),
+                np.array([[1, 2], [0, 2], [0, 1]]), np.array([1, 1, 1]))
+
+
+def UnitIntervalMesh(n):
+    """1D meshes exist only so that argument validation can reject them like the reference does."""
+    return Mesh(np.linspace(0.0, 1.0, n + 1)[:, None], np.stack([np.arange(n), np.arange(n) + 1], axis=1),
+                np.array([[0], [n]]), np.array([1, 2]))
+
+
+def from_firedrake(fmesh):
+    """Ingest a live Firedrake mesh (P1 coordinates only; SURVEY 8b 'what is ingested')."""
+    coords = np.array(fmesh.coordinates.dat.data_ro_with_halos, dtype=np.float64)
+    cells = np.array(fmesh.coordinates.cell_node_map().values_with_halo, dtype=np.int32)
+    ef = fmesh.exterior_facets
+    d = coords.shape[1] if coords.ndim > 1 else 1
+    # facet -> vertices: the facet's cell minus the vertex opposite the local facet number
+    fcells = np.asarray(ef.facet_cell).reshape(-1)
+    lfn = np.asarray(ef.local_facet_dat.data_ro).reshape(-1)
+    bf = np.stack([np.delete(cells[c], l) for c, l in zip(fcells, lfn)]) if len(fcells) else np.zeros((0, d), np.int32)
+    bt = np.asarray(ef.markers, dtype=np.int32) if ef.markers is not None else np.zeros(len(fcells), np.int32)
+    deg = fmesh.coordinates.ufl_element().degree()
+    return Mesh(coords, cells, bf, bt, degree=deg)
