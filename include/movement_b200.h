@@ -94,6 +94,13 @@ int mv_device_count(void);
 int mv_set_device(int device);
 int mv_set_stream(void* cuda_stream);
 int mv_sync(void);
+/* Measurement hooks (bench.py): when enabled, CUDA events on the launching stream bracket the
+ * SpMV launches inside PCG.  mv_prof_get: accumulated SpMV milliseconds / launch counts / PCG
+ * iterations, indexed by the number of interleaved right-hand sides (arrays of 16), and the number
+ * of kernels this library has launched since mv_prof_reset.  Any pointer may be NULL.           */
+int mv_prof_enable(int on);
+int mv_prof_reset(void);
+int mv_prof_get(double* spmv_ms16, int64_t* spmv_count16, int64_t* pcg_iters16, int64_t* launches);
 
 /* ---- ingest (replaces: movement/mover.py:49-102 -- mesh copy, function spaces, cell
  * volumes; monge_ampere.py:176-184 -- total volume; and the operator assembly Firedrake

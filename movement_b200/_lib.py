@@ -30,6 +30,9 @@ SIGNATURES = {
     "mv_set_device": (_i, [_i]),
     "mv_set_stream": (_i, [_vp]),
     "mv_sync": (_i, []),
+    "mv_prof_enable": (_i, [_i]),
+    "mv_prof_reset": (_i, []),
+    "mv_prof_get": (_i, [_pd, _pi64, _pi64, _pi64]),
     "mv_mesh_create": (_i, [_i, _i64, _i64, _vp, _vp, _i64, _vp, _vp, _i64, _i64, C.POINTER(_vp)]),
     "mv_mesh_destroy": (None, [_vp]),
     "mv_mesh_info": (_i, [_vp, _pi64]),

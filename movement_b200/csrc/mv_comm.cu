@@ -103,11 +103,11 @@ int halo_exchange(mv_mesh* m, int C, double* vec) {
   const int64_t nsend = h.send_ptr[h.nn];
   const int grid = grid_for(nsend * C);
   switch (C) {
-    case 1: k_halo_pack<1><<<grid, MV_BLOCK, 0, g_stream>>>(nsend, h.send_idx, vec, h.send_buf); break;
-    case 2: k_halo_pack<2><<<grid, MV_BLOCK, 0, g_stream>>>(nsend, h.send_idx, vec, h.send_buf); break;
-    case 3: k_halo_pack<3><<<grid, MV_BLOCK, 0, g_stream>>>(nsend, h.send_idx, vec, h.send_buf); break;
-    case 4: k_halo_pack<4><<<grid, MV_BLOCK, 0, g_stream>>>(nsend, h.send_idx, vec, h.send_buf); break;
-    case 9: k_halo_pack<9><<<grid, MV_BLOCK, 0, g_stream>>>(nsend, h.send_idx, vec, h.send_buf); break;
+    case 1: MV_L k_halo_pack<1><<<grid, MV_BLOCK, 0, g_stream>>>(nsend, h.send_idx, vec, h.send_buf); break;
+    case 2: MV_L k_halo_pack<2><<<grid, MV_BLOCK, 0, g_stream>>>(nsend, h.send_idx, vec, h.send_buf); break;
+    case 3: MV_L k_halo_pack<3><<<grid, MV_BLOCK, 0, g_stream>>>(nsend, h.send_idx, vec, h.send_buf); break;
+    case 4: MV_L k_halo_pack<4><<<grid, MV_BLOCK, 0, g_stream>>>(nsend, h.send_idx, vec, h.send_buf); break;
+    case 9: MV_L k_halo_pack<9><<<grid, MV_BLOCK, 0, g_stream>>>(nsend, h.send_idx, vec, h.send_buf); break;
     default: set_error("halo_exchange: unsupported ncomp %d", C); return MV_ERR_UNSUPPORTED;
   }
   MV_KERNEL_CHECK();

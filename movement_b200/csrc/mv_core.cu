@@ -8,6 +8,35 @@ namespace mv {
 static thread_local char g_err[1024] = "";
 cudaStream_t g_stream = 0;
 int g_nsm = 0;
+long long g_launches = 0;
+Prof g_prof;
+
+int prof_begin(int ncomp) {
+  Prof& p = g_prof;
+  if (!p.on || p.used >= Prof::NPAIR) return -1;
+  if (!p.created) {
+    for (int i = 0; i < 2 * Prof::NPAIR; ++i) cudaEventCreate(&p.ev[i]);
+    p.created = true;
+  }
+  const int s = p.used++;
+  p.cls[s] = ncomp & 15;
+  cudaEventRecord(p.ev[2 * s], g_stream);
+  return s;
+}
+void prof_end(int slot) {
+  if (slot >= 0) cudaEventRecord(g_prof.ev[2 * slot + 1], g_stream);
+}
+void prof_drain() {
+  Prof& p = g_prof;
+  for (int s = 0; s < p.used; ++s) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, p.ev[2 * s], p.ev[2 * s + 1]) == cudaSuccess) {
+      p.ms[p.cls[s]] += ms;
+      p.count[p.cls[s]] += 1;
+    }
+  }
+  p.used = 0;
+}
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -174,15 +203,15 @@ __global__ void k_init_volstats(double* out) {
 int volume_stats_device(mv_mesh* m, const double* x, const double* mon, const double* vol0, double* volume,
                         double* dout, int64_t global_cells) {
   const int64_t C = m->Cown;
-  k_init_volstats<<<1, 1, 0, g_stream>>>(dout);
+  MV_L k_init_volstats<<<1, 1, 0, g_stream>>>(dout);
   const int grid = grid_for(C);
   if (m->dim == 2)
-    k_volumes<2><<<grid, MV_BLOCK, 0, g_stream>>>(x, m->cells, C, mon, vol0, volume, m->red.partials, m->red.counter, dout);
+    MV_L k_volumes<2><<<grid, MV_BLOCK, 0, g_stream>>>(x, m->cells, C, mon, vol0, volume, m->red.partials, m->red.counter, dout);
   else
-    k_volumes<3><<<grid, MV_BLOCK, 0, g_stream>>>(x, m->cells, C, mon, vol0, volume, m->red.partials, m->red.counter, dout);
+    MV_L k_volumes<3><<<grid, MV_BLOCK, 0, g_stream>>>(x, m->cells, C, mon, vol0, volume, m->red.partials, m->red.counter, dout);
   MV_KERNEL_CHECK();
   if (comm_active()) MV_CHECK(allreduce_volstats_dev(dout));
-  k_volume_var<<<grid, MV_BLOCK, 0, g_stream>>>(volume, C, 1.0 / (double)global_cells, m->red.partials, m->red.counter, dout);
+  MV_L k_volume_var<<<grid, MV_BLOCK, 0, g_stream>>>(volume, C, 1.0 / (double)global_cells, m->red.partials, m->red.counter, dout);
   MV_KERNEL_CHECK();
   return MV_OK;
 }
@@ -207,6 +236,27 @@ extern "C" int mv_set_stream(void* s) {
   g_stream = (cudaStream_t)s;
   return MV_OK;
 }
+extern "C" int mv_prof_enable(int on) {
+  if (g_prof.used) { cudaStreamSynchronize(g_stream); prof_drain(); }
+  g_prof.on = on != 0;
+  return MV_OK;
+}
+extern "C" int mv_prof_reset(void) {
+  if (g_prof.used) { cudaStreamSynchronize(g_stream); prof_drain(); }
+  for (int i = 0; i < 16; ++i) { g_prof.ms[i] = 0; g_prof.count[i] = 0; g_prof.pcg_iters[i] = 0; }
+  g_launches = 0;
+  return MV_OK;
+}
+extern "C" int mv_prof_get(double* spmv_ms16, int64_t* spmv_count16, int64_t* pcg_iters16, int64_t* launches) {
+  if (g_prof.used) { cudaStreamSynchronize(g_stream); prof_drain(); }
+  for (int i = 0; i < 16; ++i) {
+    if (spmv_ms16) spmv_ms16[i] = g_prof.ms[i];
+    if (spmv_count16) spmv_count16[i] = g_prof.count[i];
+    if (pcg_iters16) pcg_iters16[i] = g_prof.pcg_iters[i];
+  }
+  if (launches) *launches = g_launches;
+  return MV_OK;
+}
 extern "C" int mv_sync(void) {
   MV_CUDA(cudaStreamSynchronize(g_stream));
   return MV_OK;
@@ -219,9 +269,9 @@ extern "C" int mv_tangle_init(mv_mesh* m, const double* coords, double* detJ0) {
   MV_CHECK(sd.out_begin(detJ0, m->C * sizeof(double)));
   const int grid = grid_for(m->C);
   if (m->dim == 2)
-    k_tangle<2, true><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, m->C, m->C, sd.as<double>(), nullptr, nullptr);
+    MV_L k_tangle<2, true><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, m->C, m->C, sd.as<double>(), nullptr, nullptr);
   else
-    k_tangle<3, true><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, m->C, m->C, sd.as<double>(), nullptr, nullptr);
+    MV_L k_tangle<3, true><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, m->C, m->C, sd.as<double>(), nullptr, nullptr);
   MV_KERNEL_CHECK();
   return sd.out_end(detJ0, m->C * sizeof(double));
 }
@@ -238,9 +288,9 @@ extern "C" int mv_tangle_check(mv_mesh* m, const double* coords, const double* d
   const int64_t C = ratio ? m->C : m->Cown;
   const int grid = grid_for(C);
   if (m->dim == 2)
-    k_tangle<2, false><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, C, m->Cown, sd.as<double>(), sr.as<double>(), d_count);
+    MV_L k_tangle<2, false><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, C, m->Cown, sd.as<double>(), sr.as<double>(), d_count);
   else
-    k_tangle<3, false><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, C, m->Cown, sd.as<double>(), sr.as<double>(), d_count);
+    MV_L k_tangle<3, false><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, C, m->Cown, sd.as<double>(), sr.as<double>(), d_count);
   MV_KERNEL_CHECK();
   unsigned long long h = 0;
   MV_CUDA(cudaMemcpyAsync(&h, d_count, sizeof(h), cudaMemcpyDeviceToHost, g_stream));
@@ -257,11 +307,28 @@ extern "C" int mv_cell_volumes(mv_mesh* m, const double* coords, double* volume,
   double* dout = nullptr;
   MV_CUDA(cudaMallocAsync((void**)&dout, 4 * sizeof(double), g_stream));
   int64_t gcells = m->Cown;
+  if (comm_active()) {
+    double hc = (double)m->Cown;
+    MV_CUDA(cudaMemcpyAsync(dout, &hc, sizeof(double), cudaMemcpyHostToDevice, g_stream));
+    MV_CHECK(allreduce_sum_dev(dout, 1));
+    MV_CUDA(cudaMemcpyAsync(&hc, dout, sizeof(double), cudaMemcpyDeviceToHost, g_stream));
+    MV_CUDA(cudaStreamSynchronize(g_stream));
+    gcells = (int64_t)(hc + 0.5);
+  }
   MV_CHECK(volume_stats_device(m, sx.as<double>(), nullptr, nullptr, sv.as<double>(), dout, gcells));
   double h[4];
   MV_CUDA(cudaMemcpyAsync(h, dout, sizeof(h), cudaMemcpyDeviceToHost, g_stream));
   MV_CUDA(cudaFreeAsync(dout, g_stream));
   MV_CUDA(cudaStreamSynchronize(g_stream));
+  if (comm_active()) {   // sum of squared deviations is per rank
+    double* d2 = nullptr;
+    MV_CUDA(cudaMallocAsync((void**)&d2, sizeof(double), g_stream));
+    MV_CUDA(cudaMemcpyAsync(d2, &h[3], sizeof(double), cudaMemcpyHostToDevice, g_stream));
+    MV_CHECK(allreduce_sum_dev(d2, 1));
+    MV_CUDA(cudaMemcpyAsync(&h[3], d2, sizeof(double), cudaMemcpyDeviceToHost, g_stream));
+    MV_CUDA(cudaFreeAsync(d2, g_stream));
+    MV_CUDA(cudaStreamSynchronize(g_stream));
+  }
   if (stats) {
     const double mean = h[0] / (double)gcells;
     stats[0] = h[1];

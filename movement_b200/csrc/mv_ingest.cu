@@ -77,7 +77,7 @@ static int build_inverse_map(const int* keys, int64_t n, int64_t nown, int** ptr
   MV_CHECK(dev_alloc(&ptr, nown + 1));
   MV_CUDA(cudaMemsetAsync(cnt, 0, (nown + 1) * sizeof(int), g_stream));
   int grid = grid_for(n);
-  if (n > 0) k_count_keys<<<grid, MV_BLOCK, 0, g_stream>>>(keys, n, nown, cnt);
+  if (n > 0) MV_L k_count_keys<<<grid, MV_BLOCK, 0, g_stream>>>(keys, n, nown, cnt);
   MV_KERNEL_CHECK();
   MV_CHECK(exclusive_scan_i32(cnt, ptr, nown + 1));
   int total = 0;
@@ -85,9 +85,9 @@ static int build_inverse_map(const int* keys, int64_t n, int64_t nown, int** ptr
   MV_CUDA(cudaStreamSynchronize(g_stream));
   MV_CHECK(dev_alloc(&list, (size_t)total));
   MV_CUDA(cudaMemsetAsync(cnt, 0, (nown + 1) * sizeof(int), g_stream));
-  if (n > 0) k_fill_keys<<<grid, MV_BLOCK, 0, g_stream>>>(keys, n, nown, ptr, cnt, list);
+  if (n > 0) MV_L k_fill_keys<<<grid, MV_BLOCK, 0, g_stream>>>(keys, n, nown, ptr, cnt, list);
   MV_KERNEL_CHECK();
-  if (nown > 0) k_sort_rows<<<grid_for(nown), MV_BLOCK, 0, g_stream>>>(ptr, nown, list);
+  if (nown > 0) MV_L k_sort_rows<<<grid_for(nown), MV_BLOCK, 0, g_stream>>>(ptr, nown, list);
   MV_KERNEL_CHECK();
   dev_free(cnt);
   *ptr_out = ptr;
@@ -333,12 +333,12 @@ static int ingest_impl(mv_mesh* m) {
   int* d_err = nullptr;
   MV_CHECK(dev_alloc(&d_err, 1));
   MV_CUDA(cudaMemsetAsync(d_err, 0, sizeof(int), g_stream));
-  k_row_count<D><<<grid_for(Vown), MV_BLOCK, 0, g_stream>>>(m->cells, m->v2c_ptr, m->v2c, Vown, p.row_nnz, d_err);
+  MV_L k_row_count<D><<<grid_for(Vown), MV_BLOCK, 0, g_stream>>>(m->cells, m->v2c_ptr, m->v2c, Vown, p.row_nnz, d_err);
   MV_KERNEL_CHECK();
   int64_t* slice_len = nullptr;
   MV_CHECK(dev_alloc(&slice_len, p.nslices + 1));
   MV_CHECK(dev_alloc(&p.slice_ptr, p.nslices + 1));
-  k_slice_width<<<grid_for(p.nslices * 32), MV_BLOCK, 0, g_stream>>>(p.row_nnz, Vown, p.nslices, slice_len);
+  MV_L k_slice_width<<<grid_for(p.nslices * 32), MV_BLOCK, 0, g_stream>>>(p.row_nnz, Vown, p.nslices, slice_len);
   MV_KERNEL_CHECK();
   MV_CHECK(exclusive_scan_i64(slice_len, p.slice_ptr, p.nslices + 1));
   int h_err = 0;
@@ -352,7 +352,7 @@ static int ingest_impl(mv_mesh* m) {
     return MV_ERR_VALENCE;
   }
   MV_CHECK(dev_alloc(&p.cols, p.len));
-  k_fill_cols<D><<<grid_for(p.nslices * MV_SLICE), MV_BLOCK, 0, g_stream>>>(m->cells, m->v2c_ptr, m->v2c, Vown, p.nslices,
+  MV_L k_fill_cols<D><<<grid_for(p.nslices * MV_SLICE), MV_BLOCK, 0, g_stream>>>(m->cells, m->v2c_ptr, m->v2c, Vown, p.nslices,
                                                                          p.slice_ptr, p.cols);
   MV_KERNEL_CHECK();
   // 4. values
@@ -364,16 +364,16 @@ static int ingest_impl(mv_mesh* m) {
   MV_CHECK(dev_alloc(&m->vol, C));
   MV_CUDA(cudaMemsetAsync(m->Mval, 0, p.len * sizeof(double), g_stream));
   MV_CUDA(cudaMemsetAsync(m->Kval, 0, p.len * sizeof(double), g_stream));
-  if (C > 0) k_cell_volume<D><<<grid_for(C), MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, C, m->vol);
+  if (C > 0) MV_L k_cell_volume<D><<<grid_for(C), MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, C, m->vol);
   MV_KERNEL_CHECK();
-  k_assemble_MK<D><<<grid_for(Vown), MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, Vown, p.slice_ptr, p.cols,
+  MV_L k_assemble_MK<D><<<grid_for(Vown), MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, Vown, p.slice_ptr, p.cols,
                                                             m->Mval, m->Kval, m->ml, m->dinvM, m->dinvK);
   MV_KERNEL_CHECK();
   // scalars (fixed-order sums)
   double* d_s = nullptr;
   MV_CHECK(dev_alloc(&d_s, 4));
-  k_sum_fixed<<<1, MV_BLOCK, 0, g_stream>>>(m->vol, m->Cown, d_s, nullptr);
-  k_sum_fixed<<<1, MV_BLOCK, 0, g_stream>>>(m->ml, Vown, d_s + 1, d_s + 2);
+  MV_L k_sum_fixed<<<1, MV_BLOCK, 0, g_stream>>>(m->vol, m->Cown, d_s, nullptr);
+  MV_L k_sum_fixed<<<1, MV_BLOCK, 0, g_stream>>>(m->ml, Vown, d_s + 1, d_s + 2);
   MV_KERNEL_CHECK();
   double h_s[3];
   int h_nnz_dummy = 0;
@@ -401,7 +401,7 @@ static int ingest_impl(mv_mesh* m) {
     MV_CHECK(dev_alloc(&m->bf_cell, F));
     MV_CHECK(dev_alloc(&m->bf_normal, F * D));
     MV_CHECK(dev_alloc(&m->bf_area, F));
-    k_facet_geometry<D><<<grid_for(F), MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, F, Vown, m->bf_verts,
+    MV_L k_facet_geometry<D><<<grid_for(F), MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, F, Vown, m->bf_verts,
                                                               m->bf_cell, m->bf_normal, m->bf_area);
     MV_KERNEL_CHECK();
   }

@@ -21,6 +21,26 @@ namespace mv {
 void set_error(const char* fmt, ...);
 extern cudaStream_t g_stream;
 extern int g_nsm;
+extern long long g_launches;   // kernels launched by this library (every launch site is prefixed MV_L)
+#define MV_L (void)++mv::g_launches,
+
+// Optional live timing of the SpMV launches inside PCG (bench.py's roofline figure): CUDA events
+// on the launching stream around each sampled launch, drained whenever the host polls the solve.
+struct Prof {
+  bool on = false;
+  static const int NPAIR = 128;
+  cudaEvent_t ev[2 * NPAIR];
+  int cls[NPAIR];
+  int used = 0;
+  bool created = false;
+  double ms[16] = {0};       // by number of right-hand sides
+  long long count[16] = {0};
+  long long pcg_iters[16] = {0};
+};
+extern Prof g_prof;
+int prof_begin(int ncomp);   // returns slot or -1
+void prof_end(int slot);
+void prof_drain();           // stream must be synchronised
 
 #define MV_CUDA(call)                                                                  \
   do {                                                                                 \

@@ -385,18 +385,18 @@ static int eval_monitor(mv_ma* ma, bool update_x, const double* xin, double* xou
   for (int i = 0; i < 8; ++i) mp.p[i] = ma->mon_params[i];
   const int64_t n = m->V;  // ghosts too: every rank evaluates the monitor at all its local vertices
   const int grid = grid_for(n);
-  if (monitor_normalised(mp.kind)) k_set_scalar<<<1, 1, 0, g_stream>>>(ma->dscal + D_MONMAX, 0.0);
+  if (monitor_normalised(mp.kind)) MV_L k_set_scalar<<<1, 1, 0, g_stream>>>(ma->dscal + D_MONMAX, 0.0);
   if (update_x)
-    k_update_x_monitor<D, true><<<grid, MV_BLOCK, 0, g_stream>>>(n, xin, ma->f[MV_F_GRAD_PHI], xout, mp, mon, ma->dscal);
+    MV_L k_update_x_monitor<D, true><<<grid, MV_BLOCK, 0, g_stream>>>(n, xin, ma->f[MV_F_GRAD_PHI], xout, mp, mon, ma->dscal);
   else
-    k_update_x_monitor<D, false><<<grid, MV_BLOCK, 0, g_stream>>>(n, nullptr, nullptr, xout, mp, mon, ma->dscal);
+    MV_L k_update_x_monitor<D, false><<<grid, MV_BLOCK, 0, g_stream>>>(n, nullptr, nullptr, xout, mp, mon, ma->dscal);
   MV_KERNEL_CHECK();
   if (monitor_normalised(mp.kind)) {
     // NB the reference demos take a rank-local max (demos/monge_ampere_3d.py:67); a global
     // max is the only definition that is partition independent.
     if (comm_active()) MV_CHECK(allreduce_dev(ma->dscal + D_MONMAX, 1, 1));
     const double alpha = mp.kind == MV_MON_GAUSS_HESS ? mp.p[3] : mp.p[0];
-    k_monitor_normalise<<<grid, MV_BLOCK, 0, g_stream>>>(n, alpha, mon, ma->dscal);
+    MV_L k_monitor_normalise<<<grid, MV_BLOCK, 0, g_stream>>>(n, alpha, mon, ma->dscal);
     MV_KERNEL_CHECK();
   }
   return MV_OK;
@@ -519,7 +519,7 @@ extern "C" int mv_ma_set_boundary(mv_ma* ma, int n_fixed, const int32_t* fixed_t
   MV_CUDA(cudaMallocAsync((void**)&d_bits, bits.size() * sizeof(unsigned), g_stream));
   MV_CUDA(cudaMemcpyAsync(d_tagidx, tagidx.data(), F * sizeof(int), cudaMemcpyHostToDevice, g_stream));
   MV_CUDA(cudaMemcpyAsync(d_bits, bits.data(), bits.size() * sizeof(unsigned), cudaMemcpyHostToDevice, g_stream));
-  k_bc_mask<<<grid_for(F), MV_BLOCK, 0, g_stream>>>(F, d, m->bf_verts, d_tagidx, d_bits, m->Vown, (unsigned*)ma->bc_mask);
+  MV_L k_bc_mask<<<grid_for(F), MV_BLOCK, 0, g_stream>>>(F, d, m->bf_verts, d_tagidx, d_bits, m->Vown, (unsigned*)ma->bc_mask);
   MV_KERNEL_CHECK();
   MV_CUDA(cudaFreeAsync(d_tagidx, g_stream));
   MV_CUDA(cudaFreeAsync(d_bits, g_stream));
@@ -538,19 +538,19 @@ extern "C" int mv_ma_get_bcmask(mv_ma* ma, uint16_t* dst) {
 static int l2_rhs_dev(mv_mesh* m, const double* phi, double* b) {
   const int grid = grid_for(m->Vown);
   if (m->dim == 2)
-    k_l2_rhs<2><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->Vown, phi, b);
+    MV_L k_l2_rhs<2><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->Vown, phi, b);
   else
-    k_l2_rhs<3><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->Vown, phi, b);
+    MV_L k_l2_rhs<3><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->Vown, phi, b);
   MV_KERNEL_CHECK();
   return MV_OK;
 }
 static int hess_rhs_dev(mv_mesh* m, const double* phi, double* c) {
   const int grid = grid_for(m->Vown);
   if (m->dim == 2)
-    k_hess_rhs<2><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->v2f_ptr, m->v2f, m->bf_cell,
+    MV_L k_hess_rhs<2><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->v2f_ptr, m->v2f, m->bf_cell,
                                                    m->bf_normal, m->bf_area, m->Vown, phi, c);
   else
-    k_hess_rhs<3><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->v2f_ptr, m->v2f, m->bf_cell,
+    MV_L k_hess_rhs<3><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->v2f_ptr, m->v2f, m->bf_cell,
                                                    m->bf_normal, m->bf_area, m->Vown, phi, c);
   MV_KERNEL_CHECK();
   return MV_OK;
@@ -558,10 +558,10 @@ static int hess_rhs_dev(mv_mesh* m, const double* phi, double* c) {
 static int assemble_a_dev(mv_mesh* m, const double* mon, const double* H, double* a, double* dscal) {
   const int grid = grid_for(m->Vown);
   if (m->dim == 2)
-    k_assemble_a<2><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->Vown, mon, H, a,
+    MV_L k_assemble_a<2><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->Vown, mon, H, a,
                                                      m->red.partials, m->red.counter, dscal);
   else
-    k_assemble_a<3><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->Vown, mon, H, a,
+    MV_L k_assemble_a<3><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->Vown, mon, H, a,
                                                      m->red.partials, m->red.counter, dscal);
   MV_KERNEL_CHECK();
   return MV_OK;
@@ -663,7 +663,7 @@ extern "C" int mv_ma_diagnostics(mv_ma* ma, int use_H_old, double* out) {
   // A5 theta + residual
   MV_CHECK(assemble_a_dev(m, ma->f[MV_F_MONITOR], ma->f[hf], ma->a, ma->dscal));
   if (dist) MV_CHECK(allreduce_sum_dev(ma->dscal + D_SUMA, 1));
-  k_residual<<<grid_for(m->Vown), MV_BLOCK, 0, g_stream>>>(m->Vown, ma->a, m->ml, 1.0 / gtotvol, ma->f[MV_F_RESIDUAL],
+  MV_L k_residual<<<grid_for(m->Vown), MV_BLOCK, 0, g_stream>>>(m->Vown, ma->a, m->ml, 1.0 / gtotvol, ma->f[MV_F_RESIDUAL],
                                                           m->red.partials, m->red.counter, ma->dscal);
   MV_KERNEL_CHECK();
   if (dist) MV_CHECK(allreduce_sum_dev(ma->dscal + D_RES2, 1));
@@ -688,11 +688,11 @@ extern "C" int mv_ma_pseudotimestep(mv_ma* ma, double dt, int* iters) {
   MA_REQUIRE(ma, MV_F_RESIDUAL);
   mv_mesh* m = ma->mesh;
   const int64_t n = m->Vown;
-  k_scale<<<grid_for(n), MV_BLOCK, 0, g_stream>>>(n, dt, ma->f[MV_F_RESIDUAL], ma->rhs);
+  MV_L k_scale<<<grid_for(n), MV_BLOCK, 0, g_stream>>>(n, dt, ma->f[MV_F_RESIDUAL], ma->rhs);
   MV_CUDA(cudaMemsetAsync(ma->dphi, 0, m->V * sizeof(double), g_stream));
   MV_CHECK(pcg_solve(m, MV_OP_STIFFNESS, 1, ma->rhs, ma->dphi, nullptr, ma->rtol, ma->atol, ma->maxit_poisson, 1, iters,
                      nullptr));
-  k_add<<<grid_for(n), MV_BLOCK, 0, g_stream>>>(n, ma->f[MV_F_PHI_OLD], ma->dphi, ma->f[MV_F_PHI]);
+  MV_L k_add<<<grid_for(n), MV_BLOCK, 0, g_stream>>>(n, ma->f[MV_F_PHI_OLD], ma->dphi, ma->f[MV_F_PHI]);
   MV_KERNEL_CHECK();
   return MV_OK;
 }

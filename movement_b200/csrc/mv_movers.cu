@@ -208,7 +208,7 @@ static int ensure_edge_opp(mv_mesh* m) {
   }
   if (m->edge_opp) return MV_OK;
   MV_CHECK(dev_alloc(&m->edge_opp, m->pat.len));
-  k_edge_opp<<<grid_for(m->Vown), MV_BLOCK, 0, g_stream>>>(m->cells, m->v2c_ptr, m->v2c, m->Vown, m->pat.slice_ptr, m->pat.cols,
+  MV_L k_edge_opp<<<grid_for(m->Vown), MV_BLOCK, 0, g_stream>>>(m->cells, m->v2c_ptr, m->v2c, m->Vown, m->pat.slice_ptr, m->pat.cols,
                                                          m->pat.row_nnz, m->edge_opp);
   MV_KERNEL_CHECK();
   return MV_OK;
@@ -218,10 +218,10 @@ int spring_apply_dev(mv_mesh* m, const double* coords, const uint16_t* mask, con
   const Sell& p = m->pat;
   const int grid = grid_for(p.nslices * MV_SLICE, 8);
   if (dot)
-    k_spring_apply<true><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, p.nrows, p.slice_ptr, p.cols, m->edge_opp, coords, mask, x, y,
+    MV_L k_spring_apply<true><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, p.nrows, p.slice_ptr, p.cols, m->edge_opp, coords, mask, x, y,
                                                           m->pcg.flags, m->red.partials, m->red.counter, m->pcg.scal);
   else
-    k_spring_apply<false><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, p.nrows, p.slice_ptr, p.cols, m->edge_opp, coords, mask, x,
+    MV_L k_spring_apply<false><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, p.nrows, p.slice_ptr, p.cols, m->edge_opp, coords, mask, x,
                                                            y, nullptr, nullptr, nullptr, nullptr);
   MV_KERNEL_CHECK();
   return MV_OK;
@@ -242,13 +242,13 @@ extern "C" int mv_laplace_move(mv_mesh* m, double* v, const uint16_t* mask, doub
   MV_CHECK(sm.in(mask, m->Vown * sizeof(uint16_t)));
   const int d = m->dim;
   const int64_t n = m->Vown;
-  if (d == 2) k_zero_free<2><<<grid_for(n * d), MV_BLOCK, 0, g_stream>>>(n, sm.as<uint16_t>(), v);
-  else k_zero_free<3><<<grid_for(n * d), MV_BLOCK, 0, g_stream>>>(n, sm.as<uint16_t>(), v);
+  if (d == 2) MV_L k_zero_free<2><<<grid_for(n * d), MV_BLOCK, 0, g_stream>>>(n, sm.as<uint16_t>(), v);
+  else MV_L k_zero_free<3><<<grid_for(n * d), MV_BLOCK, 0, g_stream>>>(n, sm.as<uint16_t>(), v);
   MV_KERNEL_CHECK();
   int st = pcg_solve(m, MV_OP_STIFFNESS, d, nullptr, v, sm.as<uint16_t>(), rtol, atol, maxit, 0, iters, nullptr);
   if (st != MV_OK) return st;
   double* dout = m->pcg.scal + SC(S_SUM, 8);
-  k_axpy_norm<<<grid_for(n * d), MV_BLOCK, 0, g_stream>>>(n * d, dt, v, x, nullptr, m->red.partials, m->red.counter, dout);
+  MV_L k_axpy_norm<<<grid_for(n * d), MV_BLOCK, 0, g_stream>>>(n * d, dt, v, x, nullptr, m->red.partials, m->red.counter, dout);
   MV_KERNEL_CHECK();
   if (comm_active()) {
     MV_CHECK(allreduce_sum_dev(dout, 1));
@@ -283,9 +283,9 @@ extern "C" int mv_spring_edge_geometry(mv_mesh* m, const double* coords, int32_t
   MV_CHECK(dev_alloc(&ptr, m->Vown + 1));
   MV_CUDA(cudaMemsetAsync(cnt, 0, (m->Vown + 1) * sizeof(int), g_stream));
   const int grid = grid_for(m->Vown);
-  k_edge_count<<<grid, MV_BLOCK, 0, g_stream>>>(m->Vown, m->pat.slice_ptr, m->pat.cols, m->edge_opp, cnt);
+  MV_L k_edge_count<<<grid, MV_BLOCK, 0, g_stream>>>(m->Vown, m->pat.slice_ptr, m->pat.cols, m->edge_opp, cnt);
   MV_CHECK(exclusive_scan_i32(cnt, ptr, m->Vown + 1));
-  k_edge_fill<<<grid, MV_BLOCK, 0, g_stream>>>(m->Vown, m->pat.slice_ptr, m->pat.cols, m->edge_opp, ptr, sx.as<double>(),
+  MV_L k_edge_fill<<<grid, MV_BLOCK, 0, g_stream>>>(m->Vown, m->pat.slice_ptr, m->pat.cols, m->edge_opp, ptr, sx.as<double>(),
                                               se.as<int>(), sl.as<double>(), st.as<double>(), sa.as<double>());
   MV_KERNEL_CHECK();
   MV_CHECK(se.out_end(edges, E * 2 * sizeof(int)));
@@ -328,13 +328,13 @@ extern "C" int mv_spring_move(mv_mesh* m, double* coords, const double* forcing,
   double* u = m->tmp_vec;
   double* dinv = m->tmp_vec + m->V * 2;
   MV_CUDA(cudaMemcpyAsync(u, sf.dev, m->V * 2 * sizeof(double), cudaMemcpyDeviceToDevice, g_stream));
-  k_zero_free<2><<<grid_for(n * 2), MV_BLOCK, 0, g_stream>>>(n, sm.as<uint16_t>(), u);
-  k_spring_diag<<<grid_for(n), MV_BLOCK, 0, g_stream>>>(n, m->pat.slice_ptr, m->pat.cols, m->edge_opp, coords, dinv);
+  MV_L k_zero_free<2><<<grid_for(n * 2), MV_BLOCK, 0, g_stream>>>(n, sm.as<uint16_t>(), u);
+  MV_L k_spring_diag<<<grid_for(n), MV_BLOCK, 0, g_stream>>>(n, m->pat.slice_ptr, m->pat.cols, m->edge_opp, coords, dinv);
   MV_KERNEL_CHECK();
   int st = pcg_solve_spring(m, coords, dinv, u, sm.as<uint16_t>(), rtol, atol, maxit, iters);
   if (st != MV_OK) return st;
   double* dout = m->pcg.scal + SC(S_SUM, 8);
-  k_axpy_norm<<<grid_for(n * 2), MV_BLOCK, 0, g_stream>>>(n * 2, dt, u, coords, displacement, m->red.partials, m->red.counter,
+  MV_L k_axpy_norm<<<grid_for(n * 2), MV_BLOCK, 0, g_stream>>>(n * 2, dt, u, coords, displacement, m->red.partials, m->red.counter,
                                                          dout);
   MV_KERNEL_CHECK();
   double h = 0.0;

@@ -268,8 +268,8 @@ int op_arrays(mv_mesh* m, int op, const double** val, const double** dinv) {
       if (!m->MKval) {
         MV_CHECK(dev_alloc(&m->MKval, m->pat.len));
         MV_CHECK(dev_alloc(&m->dinvMK, m->Vown));
-        k_add_vals<<<grid_for(m->pat.len), MV_BLOCK, 0, g_stream>>>(m->pat.len, m->Mval, m->Kval, m->MKval);
-        k_dinv_sum<<<grid_for(m->Vown), MV_BLOCK, 0, g_stream>>>(m->Vown, m->dinvM, m->dinvK, m->dinvMK);
+        MV_L k_add_vals<<<grid_for(m->pat.len), MV_BLOCK, 0, g_stream>>>(m->pat.len, m->Mval, m->Kval, m->MKval);
+        MV_L k_dinv_sum<<<grid_for(m->Vown), MV_BLOCK, 0, g_stream>>>(m->Vown, m->dinvM, m->dinvK, m->dinvMK);
         MV_KERNEL_CHECK();
       }
       *val = m->MKval; *dinv = m->dinvMK; return MV_OK;
@@ -288,10 +288,10 @@ static int spmv_launch(mv_mesh* m, const double* val, const double* x, double* y
   const Sell& p = m->pat;
   const int grid = spmv_grid(m);
   if (dot)
-    k_spmv<C, true><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, p.nrows, p.slice_ptr, p.cols, val, x, y, m->pcg.flags,
+    MV_L k_spmv<C, true><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, p.nrows, p.slice_ptr, p.cols, val, x, y, m->pcg.flags,
                                                      m->red.partials, m->red.counter, m->pcg.scal, slot);
   else
-    k_spmv<C, false><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, p.nrows, p.slice_ptr, p.cols, val, x, y, nullptr, nullptr,
+    MV_L k_spmv<C, false><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, p.nrows, p.slice_ptr, p.cols, val, x, y, nullptr, nullptr,
                                                       nullptr, nullptr, 0);
   MV_KERNEL_CHECK();
   return MV_OK;
@@ -343,21 +343,21 @@ static int pcg_impl(mv_mesh* m, const LinOp& op, const double* rhs, double* x, c
   const int gv = grid_for(n);
   const int ge = grid_for(n * C);
   if (project_mean && rhs) {
-    k_comp_sum<C><<<gv, MV_BLOCK, 0, g_stream>>>(n, rhs, m->red.partials, m->red.counter, w.scal);
+    MV_L k_comp_sum<C><<<gv, MV_BLOCK, 0, g_stream>>>(n, rhs, m->red.partials, m->red.counter, w.scal);
     MV_KERNEL_CHECK();
     if (dist) MV_CHECK(allreduce_sum_dev(w.scal + SC(S_SUM, 0), C));
   }
   // initial residual
   if (dist) MV_CHECK(halo_exchange(m, C, x));
   MV_CHECK(apply_op<C>(m, op, mask, x, w.q, false));
-  k_pcg_init<C><<<gv, MV_BLOCK, 0, g_stream>>>(n, rhs, w.q, dinv, mask, w.r, w.p, m->red.partials, m->red.counter, w.scal,
+  MV_L k_pcg_init<C><<<gv, MV_BLOCK, 0, g_stream>>>(n, rhs, w.q, dinv, mask, w.r, w.p, m->red.partials, m->red.counter, w.scal,
                                                inv_ng, project_mean && rhs ? 1 : 0, dpd, coupled);
   MV_KERNEL_CHECK();
   if (dist) {
     MV_CHECK(allreduce_sum_dev(w.scal + SC(S_RZ, 0), C));
     MV_CHECK(allreduce_sum_dev(w.scal + SC(S_BB, 0), C));
   }
-  k_pcg_setup<<<1, 1, 0, g_stream>>>(C, rtol, atol, w.scal, w.flags);
+  MV_L k_pcg_setup<<<1, 1, 0, g_stream>>>(C, rtol, atol, w.scal, w.flags);
   MV_KERNEL_CHECK();
 
   int it = 0, batch = 8;
@@ -365,32 +365,36 @@ static int pcg_impl(mv_mesh* m, const LinOp& op, const double* rhs, double* x, c
   while (true) {
     MV_CUDA(cudaMemcpyAsync(w.h_flags, w.flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, g_stream));
     MV_CUDA(cudaStreamSynchronize(g_stream));
+    if (g_prof.used) prof_drain();
     if (w.h_flags[0] || it >= maxit) break;
     const int nb = batch < maxit - it ? batch : maxit - it;
     for (int k = 0; k < nb; ++k) {
       if (dist) MV_CHECK(halo_exchange(m, C, w.p));
+      const int pslot = prof_begin(C);
       MV_CHECK(apply_op<C>(m, op, mask, w.p, w.q, true));
+      prof_end(pslot);
       if (dist) {
         MV_CHECK(allreduce_sum_dev(w.scal + SC(S_PQ, 0), C));
-        k_pcg_update<C, false><<<ge, MV_BLOCK, 0, g_stream>>>(n, w.p, w.q, dinv, mask, x, w.r, w.flags, m->red.partials,
+        MV_L k_pcg_update<C, false><<<ge, MV_BLOCK, 0, g_stream>>>(n, w.p, w.q, dinv, mask, x, w.r, w.flags, m->red.partials,
                                                               m->red.counter, w.scal, dpd, coupled);
         MV_CHECK(allreduce_sum_dev(w.scal + SC(S_RZNEW, 0), C));
-        k_pcg_post_update<<<1, 1, 0, g_stream>>>(C, w.scal, w.flags);
+        MV_L k_pcg_post_update<<<1, 1, 0, g_stream>>>(C, w.scal, w.flags);
       } else {
-        k_pcg_update<C, true><<<ge, MV_BLOCK, 0, g_stream>>>(n, w.p, w.q, dinv, mask, x, w.r, w.flags, m->red.partials,
+        MV_L k_pcg_update<C, true><<<ge, MV_BLOCK, 0, g_stream>>>(n, w.p, w.q, dinv, mask, x, w.r, w.flags, m->red.partials,
                                                              m->red.counter, w.scal, dpd, coupled);
       }
-      k_pcg_dir<C><<<ge, MV_BLOCK, 0, g_stream>>>(n, w.r, dinv, mask, w.p, w.flags, w.scal, dpd);
+      MV_L k_pcg_dir<C><<<ge, MV_BLOCK, 0, g_stream>>>(n, w.r, dinv, mask, w.p, w.flags, w.scal, dpd);
     }
     MV_KERNEL_CHECK();
     it += nb;
     if (batch < 64) batch *= 2;
   }
   const int done = w.h_flags[0], niter = w.h_flags[1], breakdown = w.h_flags[2];
+  g_prof.pcg_iters[C & 15] += niter;
   if (project_mean) {
-    k_comp_sum<C><<<gv, MV_BLOCK, 0, g_stream>>>(n, x, m->red.partials, m->red.counter, w.scal);
+    MV_L k_comp_sum<C><<<gv, MV_BLOCK, 0, g_stream>>>(n, x, m->red.partials, m->red.counter, w.scal);
     if (dist) MV_CHECK(allreduce_sum_dev(w.scal + SC(S_SUM, 0), C));
-    k_sub_mean<C><<<ge, MV_BLOCK, 0, g_stream>>>(n, x, w.scal, inv_ng);
+    MV_L k_sub_mean<C><<<ge, MV_BLOCK, 0, g_stream>>>(n, x, w.scal, inv_ng);
     MV_KERNEL_CHECK();
   }
   if (iters) *iters = niter;

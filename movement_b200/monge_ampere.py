@@ -265,25 +265,39 @@ class MongeAmpereMover_Relaxation(MongeAmpereMover_Base):
         self.phi_old.written()
         self.H_old.written()
 
+    def _begin(self):
+        """Entry of move(): computational coordinates, host edits flushed, monitor mode resolved."""
+        self.to_computational_coordinates()
+        self._sync()
+        self._fused = self._resolve_monitor()
+
+    def _evaluate(self):
+        """First half of one relaxation iteration (monge_ampere.py:501-517): L2-project grad(phi_old),
+        x = xi + grad(phi), monitor at x, theta / residual / volume diagnostics.  Returns the residual."""
+        n1 = self._l2_project()
+        self._update_physical_coordinates()
+        if not self._fused:
+            self.to_physical_coordinates()
+            self._resolve_monitor()
+            self.to_computational_coordinates()
+            self._sync()
+        self._n1 = n1
+        return self._diagnostics(use_H_old=True)
+
+    def _advance_potential(self):
+        """Second half (monge_ampere.py:535-538): pseudo-timestep, Hessian recovery, phi_old/H_old."""
+        n2 = self._pseudotimestep()
+        n3 = self._equidistribute()
+        self._advance()
+        self.cg_iterations.append((self._n1, n2, n3))
+
     def move(self):
         """Run the relaxation to convergence; returns the iteration count ``i`` at the break
         (movement/monge_ampere.py:488-540)."""
-        self.to_computational_coordinates()
-        self._sync()
-        fused = self._resolve_monitor()
+        self._begin()
         i = 0
         for i in range(self.maxiter):
-            n1 = self._l2_project()
-            self._update_physical_coordinates()
-
-            if not fused:
-                self.to_physical_coordinates()
-                self._resolve_monitor()
-                self.to_computational_coordinates()
-                self._sync()
-
-            # theta, residual and the volume diagnostic in one pass over the mesh
-            residual = self._diagnostics(use_H_old=True)
+            residual = self._evaluate()
             if i == 0:
                 initial_norm = residual
             _print(f"{i:4d}"
@@ -297,11 +311,7 @@ class MongeAmpereMover_Relaxation(MongeAmpereMover_Base):
                 self._divergence_error(i + 1)
             if i == self.maxiter - 1:
                 self._convergence_error(i + 1)
-
-            n2 = self._pseudotimestep()
-            n3 = self._equidistribute()
-            self._advance()
-            self.cg_iterations.append((n1, n2, n3))
+            self._advance_potential()
         self.to_physical_coordinates()
         return i
 
