@@ -189,7 +189,7 @@ def run_ours(args):
     quiet = mv.mover  # silence the per-iteration prints inside the timed region
     quiet._print = lambda *a, **k: None
     mv.monge_ampere._print = quiet._print
-    mv.MongeAmpereMover_Base.inner_rtol = args.inner_rtol
+    mv.monge_ampere.MongeAmpereMover_Base.inner_rtol = args.inner_rtol
 
     def barrier():
         torch.cuda.synchronize()
