@@ -1,0 +1,80 @@
+"""CPU-side checks of the drop-in boundary: the C-ABI library loads, exports every symbol that
+include/movement_b200.h declares, the ctypes table covers them, and the product path refuses to
+run without a GPU (no CPU fallback, nothing under movement_b200/ touches oracle/)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    src = open(os.path.join(ROOT, "include", "movement_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(mv_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    from movement_b200 import _lib as L
+
+    lib = L.load()
+    names = _declared()
+    assert len(names) >= 45
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in movement_b200.h but not exported"
+        assert n in L.SIGNATURES, f"{n} has no ctypes signature"
+    assert set(L.SIGNATURES) <= set(names), "ctypes table binds undeclared symbols"
+    assert lib.mv_version() >= 100
+
+
+def test_no_cpu_fallback():
+    from movement_b200 import _lib as L
+
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    lib = L.load()
+    assert lib.mv_device_count() == 0
+    coords = np.array([[0.0, 0.0], [1.0, 0.0], [0.0, 1.0]])
+    cells = np.array([[0, 1, 2]], dtype=np.int32)
+    h = C.c_void_p()
+    st = lib.mv_mesh_create(2, 3, 1, L.ptr(coords), L.ptr(cells), 0, None, None, 3, 1, C.byref(h))
+    assert st == L.MV_ERR_CUDA and b"no CPU fallback" in lib.mv_last_error()
+    import movement_b200 as mv
+
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        mv.MongeAmpereMover(mv.UnitSquareMesh(2, 2), mv.ConstantMonitorBuilder(2)())
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        mv.LaplacianSmoother(mv.UnitSquareMesh(2, 2), 1.0)
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "movement_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, f), encoding="utf-8").read()
+                assert "movement_oracle" not in text and "oracle_c" not in text, f
+
+
+def test_host_mesh_surface_without_gpu():
+    import movement_b200 as mv
+
+    mesh = mv.UnitCubeMesh(3, 3, 3)
+    assert mesh.num_vertices() == 64 and mesh.num_cells() == 162 and mesh.topological_dimension == 3
+    assert mesh.exterior_facets.unique_markers == [1, 2, 3, 4, 5, 6]
+    bc = mv.DirichletBC(mesh.coordinates.function_space(), 0, "on_boundary")
+    assert len(bc.nodes) == 64 - 8
+    f = mv.Function(mesh.coordinates.function_space()).interpolate([1.0, 0.0, 0.0])
+    assert np.allclose(f.dat.data[:, 0], 1.0)
+    copy = mv.Mesh(mesh.coordinates.copy(deepcopy=True))
+    copy.coordinates.dat.data[:] += 1.0
+    assert np.allclose(copy.coordinates.dat.data - mesh.coordinates.dat.data, 1.0)
+    for b in (mv.GradientMonitorBuilder, mv.HessianMonitorBuilder):
+        with pytest.raises(NotImplementedError):
+            b(None, None)
+    spec = mv.RingMonitorBuilder((0.5, 0.5), 0.4, 20.0, 200.0)()(mesh)
+    assert spec.params == (0.5, 0.5, 0.0, 0.4, 20.0, 200.0)

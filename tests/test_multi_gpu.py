@@ -1,0 +1,21 @@
+"""Partitioned run over NCCL (2 ranks) against the global-mesh oracle; needs two B200s."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("dim,n", [(3, 8), (2, 16)])
+def test_two_rank_relaxation_matches_oracle(dim, n):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29517",
+                          os.path.join(ROOT, "tests", "dist", "run_ma_2rank.py"), str(dim), str(n)],
+                         capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "DIST-OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]

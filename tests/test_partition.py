@@ -1,0 +1,95 @@
+"""Host-side multi-GPU logic on the CPU: the vertex-owner partition and its halo plan, single
+process and world_size-2 over gloo (the N>1 path of SURVEY 8e without a GPU)."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from movement_b200.mesh import cube_arrays, square_arrays
+from movement_b200.partition import block_ranges, partition_mesh
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("arrays", [cube_arrays(5, 4, 6), square_arrays(7, 9), cube_arrays(2, 2, 2)])
+@pytest.mark.parametrize("size", [1, 2, 3, 8])
+def test_partition_covers_mesh_and_halo_plan_is_consistent(arrays, size):
+    c, ce, bf, bt = arrays
+    if size > c.shape[0]:
+        pytest.skip("more ranks than vertices")
+    parts = [partition_mesh(c, ce, bf, bt, r, size) for r in range(size)]
+    assert sum(p.n_owned_vertices for p in parts) == c.shape[0]
+    assert sum(p.n_owned_cells for p in parts) == ce.shape[0]
+    owned_cells = np.concatenate([p.global_cell[: p.n_owned_cells] for p in parts])
+    assert np.array_equal(np.sort(owned_cells), np.arange(ce.shape[0]))        # every cell owned exactly once
+    for p in parts:
+        lo, hi = p.vertex_starts[p.rank], p.vertex_starts[p.rank + 1]
+        assert np.array_equal(p.global_vertex[: p.n_owned_vertices], np.arange(lo, hi))
+        # every cell touching an owned vertex is local, with its vertices renumbered consistently
+        touch = ((ce >= lo) & (ce < hi)).any(axis=1)
+        assert touch.sum() == p.cells.shape[0]
+        assert np.array_equal(p.global_vertex[p.cells], ce[p.global_cell])
+        assert np.array_equal(p.coords, c[p.global_vertex])
+        # boundary facets: exactly those with an owned vertex
+        ftouch = ((bf >= lo) & (bf < hi)).any(axis=1)
+        assert ftouch.sum() == p.bfacets.shape[0]
+        for k, q in enumerate(p.neighbours):
+            sent = p.global_vertex[p.send_idx[p.send_ptr[k]:p.send_ptr[k + 1]]]
+            Q = parts[q]
+            kk = list(Q.neighbours).index(p.rank)
+            recv = Q.global_vertex[Q.n_owned_vertices + Q.recv_ptr[kk]: Q.n_owned_vertices + Q.recv_ptr[kk + 1]]
+            assert np.array_equal(sent, recv)
+        assert p.n_owned_vertices + p.recv_ptr[-1] == p.coords.shape[0]
+
+
+def test_block_ranges():
+    assert block_ranges(10, 3).tolist() == [0, 4, 7, 10]
+    assert block_ranges(4, 4).tolist() == [0, 1, 2, 3, 4]
+
+
+_WORKER = r'''
+import os, sys
+import numpy as np, torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+from movement_b200 import parallel
+from movement_b200.mesh import UnitCubeMesh, cube_arrays
+assert parallel.init(backend="gloo")
+rank, size = parallel.rank(), parallel.size()
+mesh = UnitCubeMesh(4, 4, 4)                       # distributed because parallel is active
+p = mesh.part
+assert p is not None and p.size == size and mesh.n_owned_vertices == p.n_owned_vertices
+# emulate mv_halo_exchange with gloo point-to-point: owned values = global id, ghosts must receive them
+vec = torch.full((mesh.num_vertices(),), -1.0, dtype=torch.float64)
+vec[: p.n_owned_vertices] = torch.from_numpy(p.global_vertex[: p.n_owned_vertices].astype(np.float64))
+reqs, bufs = [], []
+for k, q in enumerate(p.neighbours):
+    send = vec[torch.from_numpy(p.send_idx[p.send_ptr[k]:p.send_ptr[k + 1]].astype(np.int64))].contiguous()
+    recv = torch.empty(int(p.recv_ptr[k + 1] - p.recv_ptr[k]), dtype=torch.float64)
+    reqs += [dist.isend(send, int(q)), dist.irecv(recv, int(q))]
+    bufs.append((k, recv))
+for r in reqs: r.wait()
+for k, recv in bufs:
+    vec[p.n_owned_vertices + p.recv_ptr[k]: p.n_owned_vertices + p.recv_ptr[k + 1]] = recv
+assert np.array_equal(vec.numpy(), p.global_vertex.astype(np.float64)), "halo exchange plan wrong"
+# global reductions used by the host logic
+nv = parallel.allreduce_host(p.n_owned_vertices, "sum"); nc = parallel.allreduce_host(p.n_owned_cells, "sum")
+assert nv == 125 and nc == 384
+tags = [None] * size
+dist.all_gather_object(tags, mesh.exterior_facets.unique_markers)
+assert sorted(set(t for ts in tags for t in ts)) == [1, 2, 3, 4, 5, 6]
+parallel.finalize()
+print("GLOO-OK")
+'''
+
+
+def test_world_size_2_gloo(tmp_path):
+    script = tmp_path / "worker.py"
+    script.write_text(_WORKER)
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29533", str(script), ROOT],
+                         capture_output=True, text=True, timeout=300, env=env)
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
+    assert out.stdout.count("GLOO-OK") == 2
