@@ -175,6 +175,22 @@ int mv_ma_advance(mv_ma* ma);
  * iteration counts (l2 projection, poisson, hessian).                                */
 int mv_ma_relax_iterate(mv_ma* ma, double pseudo_dt, int niter, double* trace, int* cg_iters);
 
+/* ---- quasi-Newton (replaces: PETSc SNES newtonls + KSP gmres + PC fieldsplit behind
+ * movement/monge_ampere.py:640-645,670-675,686-700 and movement/solver_parameters.py:1-47).
+ * Vectors F, Y, z are device arrays of n_owned_vertices*(1+d*d) doubles laid out [phi | H].
+ * mv_qn_residual: F(phi,H) with the bound monitor: F_psi = -(a - theta m_l), F_tau = M H - S phi;
+ *   out[0..2] = ||F||^2, theta, relative l2 residual.  The caller performs update_monitor
+ *   (monge_ampere.py:648-662) first with mv_ma_l2_project / mv_ma_update_coordinates.
+ * mv_qn_solve: J Y = F by flexible GMRES(restart) right-preconditioned with the multiplicative
+ *   fieldsplit [(M+K)^-1 ; M^-1] (inexact inner PCG: pc_rtol, pc_maxit); info[0..1] = iterations,
+ *   relative residual.  mv_qn_save / mv_qn_set_iterate: (phi,H) = saved - lambda*Y (line search). */
+int mv_qn_residual(mv_ma* ma, double* F, double* out);
+int mv_qn_jacobian_apply(mv_ma* ma, const double* z, double* y);
+int mv_qn_solve(mv_ma* ma, const double* F, double* Y, double ksp_rtol, int ksp_maxit, int restart,
+                double pc_rtol, int pc_maxit, double* info);
+int mv_qn_save(mv_ma* ma);
+int mv_qn_set_iterate(mv_ma* ma, double lambda, const double* Y);
+
 /* raw pieces exposed for parity tests */
 int mv_ma_l2_rhs(mv_mesh* m, const double* phi, double* b);            /* monge_ampere.py:328 */
 int mv_ma_hess_rhs(mv_mesh* m, const double* phi, double* c);          /* monge_ampere.py:477-480 */

@@ -57,6 +57,11 @@ SIGNATURES = {
     "mv_ma_equidistribute": (_i, [_vp, _pi]),
     "mv_ma_advance": (_i, [_vp]),
     "mv_ma_relax_iterate": (_i, [_vp, _d, _i, _pd, _pi]),
+    "mv_qn_residual": (_i, [_vp, _vp, _pd]),
+    "mv_qn_jacobian_apply": (_i, [_vp, _vp, _vp]),
+    "mv_qn_solve": (_i, [_vp, _vp, _vp, _d, _i, _i, _d, _i, _pd]),
+    "mv_qn_save": (_i, [_vp]),
+    "mv_qn_set_iterate": (_i, [_vp, _d, _vp]),
     "mv_ma_l2_rhs": (_i, [_vp, _vp, _vp]),
     "mv_ma_hess_rhs": (_i, [_vp, _vp, _vp]),
     "mv_ma_assemble_a": (_i, [_vp, _vp, _vp, _vp]),

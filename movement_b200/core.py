@@ -67,7 +67,7 @@ class DeviceMesh:
 
     def __del__(self):
         h = getattr(self, "handle", None)
-        if h is not None and L._lib is not None:
+        if h is not None and L is not None and L._lib is not None:
             L._lib.mv_mesh_destroy(h)
             self.handle = None
 
@@ -187,7 +187,7 @@ class MAState:
 
     def __del__(self):
         h = getattr(self, "handle", None)
-        if h is not None and L._lib is not None:
+        if h is not None and L is not None and L._lib is not None:
             L._lib.mv_ma_destroy(h)
             self.handle = None
 

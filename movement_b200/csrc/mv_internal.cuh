@@ -179,6 +179,13 @@ struct mv_ma {
   double mon_params[8] = {0};
   double rtol = 1e-12, atol = 1e-50;
   int maxit_mass = 500, maxit_poisson = 100000;
+  // quasi-Newton workspace (lazy, mv_qn.cu)
+  double* qn_basis = nullptr;   // V_0..V_m then Z_0..Z_{m-1}, each Vown*(1+d*d)
+  int qn_restart = 0;
+  double *qn_w = nullptr, *qn_gphi = nullptr, *qn_gH = nullptr, *qn_t1 = nullptr, *qn_t2 = nullptr;
+  double* qn_base = nullptr;    // iterate saved by mv_qn_save
+  double* qn_dots = nullptr;    // device [64]
+  double* qn_hdots = nullptr;   // pinned [64]
 };
 
 namespace mv {
@@ -211,6 +218,10 @@ int allreduce_dev(double* dscal, int n, int op);  // op: 0 sum, 1 max, 2 min
 int allreduce_volstats_dev(double* dout);  // [0] sum, [1] max, [2] min
 int volume_stats_device(mv_mesh* m, const double* x, const double* mon, const double* vol0, double* volume,
                         double* dout, int64_t global_cells);
+int l2_rhs_dev(mv_mesh* m, const double* phi, double* b);
+int hess_rhs_dev(mv_mesh* m, const double* phi, double* c);
+int assemble_a_dev(mv_mesh* m, const double* mon, const double* H, double* a, double* dscal);
+int jac_A_dev(mv_mesh* m, const double* mon, const double* H, const double* dH, double sign, double* out);
 bool comm_active();
 int comm_size();
 int grid_for(int64_t nthreads_needed, int blocks_per_sm = 8);

@@ -233,6 +233,81 @@ k_assemble_a(const double* __restrict__ xi, const int* __restrict__ cells, const
   grid_reduce_sum<1>(tot, partials, counter, [&](double(&t)[1]) { dscal[D_SUMA] = t[0]; });
 }
 
+
+// cof(I + h) : dh  (directional derivative of det(I + h) in direction dh)
+__device__ __forceinline__ double cof_contract(const double (&h)[2][2], const double (&dh)[2][2]) {
+  return (1.0 + h[1][1]) * dh[0][0] - h[1][0] * dh[0][1] - h[0][1] * dh[1][0] + (1.0 + h[0][0]) * dh[1][1];
+}
+__device__ __forceinline__ double cof_contract(const double (&h)[3][3], const double (&dh)[3][3]) {
+  double B[3][3];
+#pragma unroll
+  for (int a = 0; a < 3; ++a)
+#pragma unroll
+    for (int b = 0; b < 3; ++b) B[a][b] = h[a][b] + (a == b ? 1.0 : 0.0);
+  double s = 0.0;
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    const int a1 = (a + 1) % 3, a2 = (a + 2) % 3;
+#pragma unroll
+    for (int b = 0; b < 3; ++b) {
+      const int b1 = (b + 1) % 3, b2 = (b + 2) % 3;
+      // cofactor with the cyclic-index identity (sign absorbed by the cyclic order)
+      s = fma(B[a1][b1] * B[a2][b2] - B[a1][b2] * B[a2][b1], dh[a][b], s);
+    }
+  }
+  return s;
+}
+
+// Q2: (A dH)_i = int psi_i m cof(I + H) : dH dxi   (m, theta frozen; same quadrature as A5)
+// replaces: the UFL-derived Jacobian of movement/monge_ampere.py:640-645 (psi-row, H-column block)
+template <int D>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_jac_A(const double* __restrict__ xi, const int* __restrict__ cells, const int* __restrict__ v2c_ptr,
+        const int* __restrict__ v2c, int64_t nrows, const double* __restrict__ mon, const double* __restrict__ H,
+        const double* __restrict__ dH, double sign, double* __restrict__ out) {
+  for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < nrows; v += (int64_t)gridDim.x * blockDim.x) {
+    double acc = 0.0;
+    const int tb = __ldg(&v2c_ptr[v]), te = __ldg(&v2c_ptr[v + 1]);
+    for (int t = tb; t < te; ++t) {
+      const int entry = __ldg(&v2c[t]);
+      const int64_t c = entry / (D + 1);
+      const int loc = entry - (int)c * (D + 1);
+      int cv[D + 1];
+      double xc[D + 1][D];
+      CellGeom<D> g;
+      load_cell<D>(cells, c, cv);
+      load_cell_coords<D>(xi, cv, xc);
+      cell_geom(xc, g);
+      double cell = 0.0;
+#pragma unroll 1
+      for (int q = 0; q < Quad<D>::Q; ++q) {
+        double mq = 0.0, hq[D][D], dq[D][D];
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+#pragma unroll
+          for (int b = 0; b < D; ++b) { hq[a][b] = 0.0; dq[a][b] = 0.0; }
+        double lam_loc = 0.0;
+#pragma unroll
+        for (int j = 0; j <= D; ++j) {
+          const double l = Quad<D>::lam(q, j);
+          if (j == loc) lam_loc = l;
+          mq = fma(l, __ldg(&mon[cv[j]]), mq);
+#pragma unroll
+          for (int a = 0; a < D; ++a)
+#pragma unroll
+            for (int b = 0; b < D; ++b) {
+              hq[a][b] = fma(l, __ldg(&H[(int64_t)cv[j] * D * D + a * D + b]), hq[a][b]);
+              dq[a][b] = fma(l, __ldg(&dH[(int64_t)cv[j] * D * D + a * D + b]), dq[a][b]);
+            }
+        }
+        cell = fma(Quad<D>::w(q) * lam_loc, mq * cof_contract(hq, dq), cell);
+      }
+      acc = fma(g.vol, cell, acc);
+    }
+    out[v] = sign * acc;
+  }
+}
+
 // residual r = a - theta m_l ; sum r^2       (monge_ampere.py:212-223, :409, :514)
 __global__ void __launch_bounds__(MV_BLOCK)
 k_residual(int64_t nrows, const double* __restrict__ a, const double* __restrict__ ml, double inv_total_volume,
@@ -435,6 +510,9 @@ extern "C" int mv_ma_create(mv_mesh* m, mv_ma** out) {
 extern "C" void mv_ma_destroy(mv_ma* ma) {
   if (!ma) return;
   cudaStreamSynchronize(g_stream);
+  dev_free(ma->qn_basis); dev_free(ma->qn_w); dev_free(ma->qn_gphi); dev_free(ma->qn_gH); dev_free(ma->qn_t1);
+  dev_free(ma->qn_t2); dev_free(ma->qn_base); dev_free(ma->qn_dots);
+  if (ma->qn_hdots) cudaFreeHost(ma->qn_hdots);
   dev_free(ma->rhs); dev_free(ma->a); dev_free(ma->dphi); dev_free(ma->dscal); dev_free(ma->bc_mask);
   if (ma->h_scal) cudaFreeHost(ma->h_scal);
   delete ma;
@@ -535,7 +613,8 @@ extern "C" int mv_ma_get_bcmask(mv_ma* ma, uint16_t* dst) {
   return MV_OK;
 }
 
-static int l2_rhs_dev(mv_mesh* m, const double* phi, double* b) {
+namespace mv {
+int l2_rhs_dev(mv_mesh* m, const double* phi, double* b) {
   const int grid = grid_for(m->Vown);
   if (m->dim == 2)
     MV_L k_l2_rhs<2><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->Vown, phi, b);
@@ -544,7 +623,7 @@ static int l2_rhs_dev(mv_mesh* m, const double* phi, double* b) {
   MV_KERNEL_CHECK();
   return MV_OK;
 }
-static int hess_rhs_dev(mv_mesh* m, const double* phi, double* c) {
+int hess_rhs_dev(mv_mesh* m, const double* phi, double* c) {
   const int grid = grid_for(m->Vown);
   if (m->dim == 2)
     MV_L k_hess_rhs<2><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->v2f_ptr, m->v2f, m->bf_cell,
@@ -555,7 +634,7 @@ static int hess_rhs_dev(mv_mesh* m, const double* phi, double* c) {
   MV_KERNEL_CHECK();
   return MV_OK;
 }
-static int assemble_a_dev(mv_mesh* m, const double* mon, const double* H, double* a, double* dscal) {
+int assemble_a_dev(mv_mesh* m, const double* mon, const double* H, double* a, double* dscal) {
   const int grid = grid_for(m->Vown);
   if (m->dim == 2)
     MV_L k_assemble_a<2><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->Vown, mon, H, a,
@@ -566,6 +645,17 @@ static int assemble_a_dev(mv_mesh* m, const double* mon, const double* H, double
   MV_KERNEL_CHECK();
   return MV_OK;
 }
+
+int jac_A_dev(mv_mesh* m, const double* mon, const double* H, const double* dH, double sign, double* out) {
+  const int grid = grid_for(m->Vown);
+  if (m->dim == 2)
+    MV_L k_jac_A<2><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->Vown, mon, H, dH, sign, out);
+  else
+    MV_L k_jac_A<3><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->Vown, mon, H, dH, sign, out);
+  MV_KERNEL_CHECK();
+  return MV_OK;
+}
+}  // namespace mv
 
 extern "C" int mv_ma_l2_rhs(mv_mesh* m, const double* phi, double* b) {
   if (!m || !phi || !b) return MV_ERR_BADARG;

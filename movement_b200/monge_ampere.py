@@ -130,6 +130,14 @@ class MongeAmpereMover_Base(PrimeMover, metaclass=abc.ABCMeta):
         self._monitor_spec = None
         self._resolve_monitor()
 
+    def set_inner_solver(self, rtol=None, maxit_mass=None, maxit_poisson=None):
+        """Tolerance / iteration caps of the inner linear solves (the reference's analogue is
+        mutating movement.solver_parameters.cg_ilu / cg_gamg before building the mover)."""
+        self.inner_rtol = self.inner_rtol if rtol is None else float(rtol)
+        self.inner_maxit_mass = self.inner_maxit_mass if maxit_mass is None else int(maxit_mass)
+        self.inner_maxit_poisson = self.inner_maxit_poisson if maxit_poisson is None else int(maxit_poisson)
+        L.check(L.load().mv_ma_set_solver(self._ma, self.inner_rtol, 1e-300, self.inner_maxit_mass, self.inner_maxit_poisson))
+
     def _describe_bcs(self):
         """One descriptor per (boundary tag, constrained component set), like the DirichletBC list
         the reference builds at monge_ampere.py:331-335."""
@@ -149,7 +157,7 @@ class MongeAmpereMover_Base(PrimeMover, metaclass=abc.ABCMeta):
 
     def __del__(self):
         h = getattr(self, "_ma", None)
-        if h is not None and L._lib is not None:
+        if h is not None and L is not None and L._lib is not None:
             L._lib.mv_ma_destroy(h)
             self._ma = None
 
@@ -195,6 +203,12 @@ class MongeAmpereMover_Base(PrimeMover, metaclass=abc.ABCMeta):
         return False
 
     # ---- pieces of the iteration ---------------------------------------------------------------
+    def _begin(self):
+        """Entry of move(): computational coordinates, host edits flushed, monitor mode resolved."""
+        self.to_computational_coordinates()
+        self._sync()
+        self._fused = self._resolve_monitor()
+
     def apply_initial_guess(self, phi_init, H_init):
         """movement/monge_ampere.py:187-210."""
         if phi_init is not None and H_init is not None:
@@ -265,12 +279,6 @@ class MongeAmpereMover_Relaxation(MongeAmpereMover_Base):
         self.phi_old.written()
         self.H_old.written()
 
-    def _begin(self):
-        """Entry of move(): computational coordinates, host edits flushed, monitor mode resolved."""
-        self.to_computational_coordinates()
-        self._sync()
-        self._fused = self._resolve_monitor()
-
     def _evaluate(self):
         """First half of one relaxation iteration (monge_ampere.py:501-517): L2-project grad(phi_old),
         x = xi + grad(phi), monitor at x, theta / residual / volume diagnostics.  Returns the residual."""
@@ -317,8 +325,23 @@ class MongeAmpereMover_Relaxation(MongeAmpereMover_Base):
 
 
 class MongeAmpereMover_QuasiNewton(MongeAmpereMover_Base):
-    """Elliptic Monge-Ampere by a quasi-Newton iteration (movement/monge_ampere.py:543-750);
-    body filled in below once the device Newton-Krylov pieces are loaded."""
+    """Elliptic Monge-Ampere by a quasi-Newton iteration (movement/monge_ampere.py:543-750).
+
+    Newton with PETSc's ``l2`` line search (damping 0.8, maxstep 1.05, 5 secant steps;
+    movement/solver_parameters.py:16-19); the monitor, theta and the physical coordinates are
+    refreshed before every residual evaluation (``update_monitor``, monge_ampere.py:648-662) and
+    frozen in the Jacobian.  The Newton correction is solved on the device by flexible GMRES with
+    the multiplicative fieldsplit preconditioner of solver_parameters.py:1-21.
+    """
+
+    # PETSc defaults of the reference's option set (solver_parameters.py:1-21)
+    ksp_rtol = 1.0e-05
+    ksp_max_it = 200
+    ksp_gmres_restart = 30
+    snes_rtol = 1.0e-08
+    pc_rtol = 1.0e-03
+    pc_max_it = 400
+    linesearch = {"damping": 0.8, "maxstep": 1.05, "max_it": 5, "steptol": 1.0e-12}
 
     def __init__(self, mesh, monitor_function, phi_init=None, H_init=None, **kwargs):
         if mesh.topological_dimension == 1:
@@ -326,6 +349,101 @@ class MongeAmpereMover_QuasiNewton(MongeAmpereMover_Base):
         super().__init__(mesh, monitor_function=monitor_function, **kwargs)
         if phi_init is not None or H_init is not None:
             self.apply_initial_guess(phi_init, H_init)
+        n = self._dm.Vown * (1 + self.dim * self.dim)
+        self._F = torch.zeros(n, dtype=torch.float64, device=self.mesh.device)
+        self._Y = torch.zeros(n, dtype=torch.float64, device=self.mesh.device)
+        self.snes_iterations = 0
+        self.ksp_iterations = []
+        self.function_evaluations = 0
+
+    # -- update_monitor + residual (monge_ampere.py:640-662) ------------------------------------
+    def _func(self):
+        """F at the current (phi, H): copies the iterate into (phi_old, H_old), L2-projects
+        grad(phi_old), moves x, re-evaluates the monitor and theta, assembles F.  Returns ||F||^2."""
+        self._call(L.load().mv_ma_advance)
+        self.phi_old.written(); self.H_old.written()
+        self._l2_project()
+        self._update_physical_coordinates()
+        if not self._fused:
+            self.to_physical_coordinates()
+            self._resolve_monitor()
+            self.to_computational_coordinates()
+            self._sync()
+        out = (C.c_double * 3)()
+        self._call(L.load().mv_qn_residual, L.ptr(self._F), out)
+        self.function_evaluations += 1
+        self.theta = out[1]
+        self._relres = out[2]
+        return out[0]
+
+    def _set_iterate(self, lam):
+        self._call(L.load().mv_qn_set_iterate, float(lam), L.ptr(self._Y))
+        self.phi.written(); self.H.written()
+
+    def _l2_linesearch(self, fnorm2):
+        """PETSc SNESLineSearchL2 as restated in SURVEY 8a-QN."""
+        ls = self.linesearch
+        lam, lam_old = ls["damping"], 0.0
+        f_old = fnorm2
+        lam_mid = 0.5 * (lam + lam_old)
+        for _ in range(ls["max_it"]):
+            self._set_iterate(lam_mid)
+            f_mid = self._func()
+            self._set_iterate(lam)
+            f = self._func()
+            delta = lam - lam_old
+            d1 = (3 * f - 4 * f_mid + f_old) / delta
+            d1_old = (-3 * f_old + 4 * f_mid - f) / delta
+            d2 = (d1 - d1_old) / delta
+            if d2 > 0:
+                lam_new = lam - d1 / d2
+            elif d2 < 0:
+                lam_new = lam + d1 / d2
+            else:
+                break
+            if lam_new < ls["steptol"]:
+                lam_new = 0.5 * (lam + lam_old)
+            if not np.isfinite(lam_new) or lam_new > ls["maxstep"]:
+                break
+            lam_old, lam, f_old = lam, lam_new, f
+            lam_mid = 0.5 * (lam + lam_old)
+        return lam
+
+    def _monitor_line(self, i):
+        """The SNES monitor callback (monge_ampere.py:702-723)."""
+        residual = self._diagnostics(use_H_old=True)
+        _print(f"{i:4d}"
+               f"   Volume ratio {self.volume_ratio:5.2f}"
+               f"   Variation (σ/μ) {self.coefficient_of_variation:8.2e}"
+               f"   Residual {residual:8.2e}")
 
     def move(self):
-        raise NotImplementedError("quasi-Newton device path not built yet")
+        """Run the quasi-Newton method to convergence; returns the SNES iteration count
+        (movement/monge_ampere.py:729-750)."""
+        self._begin()
+        lib = L.load()
+        f2 = self._func()
+        fnorm0 = np.sqrt(f2)
+        it = 0
+        while True:
+            fnorm = np.sqrt(f2)
+            self._monitor_line(it)
+            if fnorm < self.rtol or fnorm < self.snes_rtol * fnorm0:      # snes_atol = rtol (monge_ampere.py:691)
+                self._convergence_message(it)
+                break
+            if it >= self.maxiter or not np.isfinite(fnorm):
+                self.snes_iterations = it
+                self.to_physical_coordinates()
+                self._convergence_error(it)
+            info = (C.c_double * 2)()
+            self._call(lib.mv_qn_solve, L.ptr(self._F), L.ptr(self._Y), self.ksp_rtol, self.ksp_max_it,
+                       self.ksp_gmres_restart, self.pc_rtol, self.pc_max_it, info)
+            self.ksp_iterations.append(int(info[0]))
+            self._call(lib.mv_qn_save)
+            lam = self._l2_linesearch(f2)
+            self._set_iterate(lam)
+            f2 = self._func()
+            it += 1
+        self.snes_iterations = it
+        self.to_physical_coordinates()
+        return it

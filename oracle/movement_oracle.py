@@ -558,10 +558,12 @@ class OracleQuasiNewton:
     """movement/monge_ampere.py:543-750 + PETSc newtonls / l2 line search as restated in
     SURVEY §8a-QN (exact Jacobian solve, mean-zero constraint on delta-phi)."""
 
-    def __init__(self, mesh: OMesh, monitor, maxiter=1000, rtol=1e-8, fixed_boundary_segments=(), verbose=False):
+    def __init__(self, mesh: OMesh, monitor, maxiter=1000, rtol=1e-8, fixed_boundary_segments=(), verbose=False,
+                 snes_rtol=1e-8):
         self.ops = MAOperators(mesh, fixed_boundary_segments)
         self.monitor = monitor
         self.maxiter, self.rtol = maxiter, rtol
+        self.snes_rtol = snes_rtol  # solver_parameters.py:15
         d, V = self.ops.dim, self.ops.V
         self.xi = self.ops.xi
         self.x = self.xi.copy()
@@ -701,7 +703,7 @@ class OracleQuasiNewton:
             self.trace.append(line)
             if self.verbose:
                 print(f"{it:4d}   Volume ratio {line[1]:5.2f}   Variation (σ/μ) {line[2]:8.2e}   Residual {line[3]:8.2e}")
-            if fnorm < self.rtol or fnorm < 1e-8 * fnorm0:
+            if fnorm < self.rtol or fnorm < self.snes_rtol * fnorm0:
                 break
             if it == self.maxiter:
                 raise ConvergenceError(f"Solver failed to converge in {it} iteration{plural(it)}.")

@@ -401,3 +401,75 @@ def test_spring_stiffness_boundary_conditions(which):
     mask = mover._mask.copy()
     L.check(L.load().mv_spring_apply(mover._dm.handle, L.ptr(mover.mesh.coordinates.tensor), L.ptr(mask), L.ptr(x), L.ptr(y)))
     assert np.abs(y - Kd @ x).max() < 1e-12
+
+
+# ------------------------------------------------------------------ quasi-Newton
+def test_qn_residual_and_jacobian_match_oracle():
+    """F and J from the device against the numpy oracle's func()/jacobian() at a non-trivial state."""
+    import ctypes as C
+
+    from movement_b200 import _lib as L
+
+    mv = _mv()
+    n = 8
+    mover = mv.MongeAmpereMover(mv.UnitSquareMesh(n, n), mv.helmholtz_hessian_monitor(), method="quasi_newton")
+    omesh = mo.unit_square_mesh(n)
+    q = mo.OracleQuasiNewton(omesh, mo.monitor_helmholtz_exact)
+    V = omesh.num_vertices
+    rng = np.random.default_rng(3)
+    phi = 1e-3 * rng.standard_normal(V)
+    H = 5e-2 * rng.standard_normal((V, 2, 2))
+    mover.phi.assign(phi); mover.H.assign(H)
+    mover._begin()
+    f2 = mover._func()
+    u = np.concatenate([phi, H.ravel()])
+    Fref = q.func(u)
+    F = mover._F.cpu().numpy()
+    assert abs(f2 - Fref @ Fref) < 1e-10 * (Fref @ Fref)
+    assert np.abs(F - Fref).max() < 1e-12 * max(1.0, np.abs(Fref).max())
+    J = q.jacobian(u)
+    z = rng.standard_normal(u.size)
+    z[:V] -= z[:V].mean()
+    y = np.empty_like(z)
+    zt = torch.as_tensor(z).cuda(); yt = torch.empty_like(zt)
+    L.check(L.load().mv_qn_jacobian_apply(mover._ma, L.ptr(zt), L.ptr(yt)))
+    ref = J @ z
+    ref[:V] -= ref[:V].mean()
+    assert np.abs(yt.cpu().numpy() - ref).max() < 1e-11 * np.abs(ref).max()
+
+
+@pytest.mark.parametrize("dim,n", [(2, 20), (3, 6)])
+def test_qn_converges_to_the_oracle_fixed_point(dim, n, capsys):
+    """Both Newton iterations are driven to ||F|| < 2e-16 (the map F -> x amplifies by ~1e3 at this h); the moved meshes must then coincide
+    (north_star: coordinates within 1e-10), and the 2D run reproduces the reference's 17 SNES
+    iterations at rtol 1e-8 (demos/monge_ampere_helmholtz.py:175-177)."""
+    mv = _mv()
+    mesh = mv.UnitSquareMesh(n, n) if dim == 2 else mv.UnitCubeMesh(n, n, n)
+    mon = mv.helmholtz_hessian_monitor() if dim == 2 else mv.ring_test_monitor(3)
+    ref_mon = mo.monitor_helmholtz_exact if dim == 2 else mo.monitor_test_ring
+    mover = mv.MongeAmpereMover(mesh, mon, method="quasi_newton", rtol=1e-8)
+    mover.ksp_rtol = 1e-9
+    nit = mover.move()
+    omesh = mo.unit_square_mesh(n) if dim == 2 else mo.unit_cube_mesh(n)
+    q = mo.OracleQuasiNewton(omesh, ref_mon, rtol=1e-8)
+    ref_nit = q.move()
+    assert abs(nit - ref_nit) <= 1
+    if dim == 2:
+        assert ref_nit == 17
+        lines = _lines(capsys)
+        blk = GOLD["demos/monge_ampere_helmholtz.py"][0]
+        assert lines[0].split()[3] == blk["text"][0][0] and lines[-1].split()[6] == blk["text"][-1][1]
+    # tighten both to the fixed point
+    mover.rtol = 2e-16; mover.snes_rtol = 0.0; mover.maxiter = 40
+    mover.move()
+    q2 = mo.OracleQuasiNewton(omesh, ref_mon, rtol=2e-16, maxiter=60, snes_rtol=0.0)
+    q2.move()
+    err = np.abs(mover.mesh.coordinates.dat.data - q2.x).max()
+    assert err < 1e-10, err
+
+
+def test_qn_maxiter_message():
+    mv = _mv()
+    mover = mv.MongeAmpereMover(mv.UnitSquareMesh(4, 4), mv.ring_test_monitor(2), method="quasi_newton", maxiter=1)
+    with pytest.raises(mv.ConvergenceError, match=r"^Solver failed to converge in 1 iteration\.$"):
+        mover.move()
