@@ -44,6 +44,9 @@ typedef struct mv_ma mv_ma;     /* Monge-Ampere mover state */
 
 /* operators a linear-algebra call can name */
 enum { MV_OP_MASS = 0, MV_OP_STIFFNESS = 1, MV_OP_MASS_PLUS_STIFFNESS = 2 };
+/* preconditioner of the stiffness-type operators (the mass solves always use Jacobi):
+ * replaces the `pc_type` choices of movement/solver_parameters.py:62-71 (bjacobi/ilu, gamg) */
+enum { MV_PC_JACOBI = 0, MV_PC_AMG = 1 };
 
 /* built-in (fused) monitor functions -- replaces: movement/monitor.py:138-143,
  * test/monitors.py:9-16, demos/monge_ampere_helmholtz.py:54-61,115-122,
@@ -141,6 +144,22 @@ int mv_spmv(mv_mesh* m, int op, int ncomp, const double* x, double* y);
 int mv_pcg_solve(mv_mesh* m, int op, int ncomp, const double* rhs, double* x,
                  const uint16_t* mask, double rtol, double atol, int maxit, int project_mean,
                  int* iters, double* relres);
+/* Preconditioner for MV_OP_STIFFNESS / MV_OP_MASS_PLUS_STIFFNESS solves: MV_PC_AMG (default) is a
+ * smoothed-aggregation multigrid V-cycle whose hierarchy is built on the device at the first
+ * solve and cached per (operator, constrained vertex set) -- replaces: PETSc `gamg`,
+ * movement/solver_parameters.py:68-71 (monge_ampere.py:441-448), and the ILU of
+ * laplacian_smoothing.py:55-77.  With MV_PC_AMG the stopping norm of mv_pcg_solve is
+ * sqrt(r.M^-1 r), M^-1 = one V-cycle.                                                      */
+int mv_set_preconditioner(mv_mesh* m, int kind);
+/* Hierarchy of the cached multigrid preconditioner of `op` (after a solve): info[0] = levels
+ * (0 = none built), info[1] = rows of the coarsest level, info[2] = 1 if that level is solved
+ * densely, then (rows, nnz) per level; rho[l] = bound of spec(D^-1 A_l); both may be NULL.   */
+int mv_amg_info(mv_mesh* m, int op, int64_t* info, int max_levels, double* rho, double* setup_ms);
+/* Copy out one SELL-32 matrix of the hierarchy (inspection / tests): which = 0 operator A_l,
+ * 1 prolongator P_l, 2 restriction R_l = P_l^T.  size[0..3] = rows, slices, padded length, nnz;
+ * the destination pointers (host or device) may be NULL (call once for the sizes).          */
+int mv_amg_level_get(mv_mesh* m, int op, int level, int which, int64_t* size, int64_t* slice_ptr,
+                     int32_t* cols, double* vals, int32_t* row_nnz);
 
 /* ---- Monge-Ampere pieces ---------------------------------------------------------- */
 int mv_ma_create(mv_mesh* m, mv_ma** out);

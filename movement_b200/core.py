@@ -135,6 +135,47 @@ class DeviceMesh:
                                       1 if project_mean else 0, C.byref(it), rel))
         return it.value, np.array(rel[:])
 
+    def set_preconditioner(self, kind):
+        """"amg" (default) or "jacobi" for the stiffness-type solves (mass solves are always Jacobi)."""
+        k = {"amg": L.MV_PC_AMG, "jacobi": L.MV_PC_JACOBI}.get(kind, kind)
+        L.check(L.load().mv_set_preconditioner(self.handle, int(k)))
+
+    def amg_info(self, op=L.MV_OP_STIFFNESS):
+        """Hierarchy of the cached multigrid preconditioner of `op` (None before its first solve)."""
+        info = (C.c_int64 * 40)()
+        rho = (C.c_double * 16)()
+        ms = C.c_double(0.0)
+        L.check(L.load().mv_amg_info(self.handle, op, info, 16, rho, C.byref(ms)))
+        nl = int(info[0])
+        if nl == 0:
+            return None
+        return {"levels": nl, "coarsest_rows": int(info[1]), "dense_coarse_solve": bool(info[2]),
+                "rows": [int(info[3 + 2 * l]) for l in range(nl)], "nnz": [int(info[4 + 2 * l]) for l in range(nl)],
+                "rho": [float(rho[l]) for l in range(nl)], "setup_ms": float(ms.value)}
+
+    def amg_matrix(self, level, which="A", op=L.MV_OP_STIFFNESS, ncols=None):
+        """One matrix of the cached hierarchy as scipy CSR (tests / inspection): "A", "P" or "R"."""
+        import scipy.sparse as sp
+
+        w = {"A": 0, "P": 1, "R": 2}[which]
+        size = (C.c_int64 * 4)()
+        lib = L.load()
+        L.check(lib.mv_amg_level_get(self.handle, op, level, w, size, None, None, None, None))
+        nrows, nslices, ln = int(size[0]), int(size[1]), int(size[2])
+        sptr = np.empty(nslices + 1, np.int64); cols = np.empty(ln, np.int32)
+        vals = np.empty(ln, np.float64); nnz = np.empty(nrows, np.int32)
+        L.check(lib.mv_amg_level_get(self.handle, op, level, w, size, L.ptr(sptr), L.ptr(cols), L.ptr(vals), L.ptr(nnz)))
+        rows = np.arange(nrows)
+        base = sptr[rows // 32] + rows % 32
+        ri, ci, vi = [], [], []
+        for k in range(int(nnz.max()) if nrows else 0):
+            sel = nnz > k
+            pos = base[sel] + k * 32
+            ri.append(rows[sel]); ci.append(cols[pos]); vi.append(vals[pos])
+        if ncols is None:
+            ncols = int(max(c.max() for c in ci)) + 1
+        return sp.csr_matrix((np.concatenate(vi), (np.concatenate(ri), np.concatenate(ci))), shape=(nrows, ncols))
+
     # ---- tangling ---------------------------------------------------------------------
     def tangle_init(self, coords):
         detJ0 = self.empty(self.C)

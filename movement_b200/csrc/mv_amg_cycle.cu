@@ -1,0 +1,291 @@
+// Smoothed-aggregation multigrid: the V-cycle (solve phase), used as the PCG preconditioner.
+//
+// replaces: the PCApply of PETSc `gamg` (movement/solver_parameters.py:68-71) inside the KSP at
+//           movement/monge_ampere.py:441-448, and of the ILU/gamg sub-solves at
+//           movement/laplacian_smoothing.py:75 and solver_parameters.py:26-33.
+//
+// One cycle = per level: Chebyshev(k) pre-smoothing from a zero guess, residual, restriction;
+// dense solve on the coarsest level; prolongation + Chebyshev(k) post-smoothing on the way up.
+// Every kernel is a streaming SELL-32 pass (one warp per 32-row slice, matrix read once with
+// evict-first loads, vectors gathered through the read-only path) with the vector updates of the
+// smoother fused into the SpMV epilogue, so a Chebyshev step costs one matrix stream:
+//   k_smooth_first   r = b - A x ; d = D^-1 r / theta ; x' = x + d           12 nnz + 4 + 40c B/row
+//   k_smooth_next    r -= A d ; d' = c1 d + c2 D^-1 r ; x += d'               12 nnz + 4 + 56c B/row
+//   k_residual       r = b - A x                                              12 nnz + 4 + 24c B/row
+//   k_sell_apply     y (+)= S x  for the transfer operators P and R = P^T
+// The smoother is a fixed polynomial in D^-1 A and pre/post smoothing are equal, so the cycle is a
+// symmetric positive definite operator, as PCG needs.  Kernels turn into no-ops once the solve's
+// `done` flag is set (the host polls it once per batch of iterations).
+#include "mv_internal.cuh"
+
+namespace mv {
+
+template <int C>
+__device__ __forceinline__ void sell_dot(const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
+                                         const double* __restrict__ val, const double* __restrict__ x, int64_t s, int lane,
+                                         double (&acc)[C]) {
+  const int64_t base = __ldg(&slice_ptr[s]);
+  const int w = (int)((__ldg(&slice_ptr[s + 1]) - base) >> 5);
+  const int* cp = cols + base + lane;
+  const double* vp = val + base + lane;
+#pragma unroll
+  for (int c = 0; c < C; ++c) acc[c] = 0.0;
+#pragma unroll 4
+  for (int k = 0; k < w; ++k) {
+    const int col = __ldcs(cp + k * MV_SLICE);
+    const double a = __ldcs(vp + k * MV_SLICE);
+    const double* xp = x + (int64_t)col * C;
+#pragma unroll
+    for (int c = 0; c < C; ++c) acc[c] = fma(a, __ldg(xp + c), acc[c]);
+  }
+}
+
+#define SLICE_LOOP                                                                         \
+  const int lane = threadIdx.x & 31;                                                       \
+  const int64_t warp0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;             \
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;                           \
+  for (int64_t s = warp0; s < nslices; s += nwarps)
+
+// x = d = D^-1 b / theta (zero initial guess)
+template <int C>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_smooth_zero(int64_t n, const double* __restrict__ b, const double* __restrict__ dinv, double sc, double* __restrict__ x,
+              double* __restrict__ d, const int* __restrict__ done) {
+  if (done && *done) return;
+  const int64_t ne = n * C;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < ne; i += (int64_t)gridDim.x * blockDim.x) {
+    const double t = sc * __ldg(&dinv[i / C]) * b[i];
+    x[i] = t;
+    if (d) d[i] = t;
+  }
+}
+
+template <int C>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_smooth_first(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
+               const double* __restrict__ val, const double* __restrict__ b, const double* __restrict__ xin,
+               const double* __restrict__ dinv, double sc, double* __restrict__ xout, double* __restrict__ d,
+               double* __restrict__ r, const int* __restrict__ done) {
+  if (done && *done) return;
+  SLICE_LOOP {
+    double acc[C];
+    sell_dot<C>(slice_ptr, cols, val, xin, s, lane, acc);
+    const int64_t row = s * MV_SLICE + lane;
+    if (row < nrows) {
+      const double di = __ldg(&dinv[row]);
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        const int64_t i = row * C + c;
+        const double t = di != 0.0 ? b[i] - acc[c] : 0.0;
+        const double dd = sc * di * t;
+        xout[i] = xin[i] + dd;
+        if (d) d[i] = dd;
+        if (r) r[i] = t;
+      }
+    }
+  }
+}
+
+template <int C>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_smooth_next(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
+              const double* __restrict__ val, const double* __restrict__ din, double* __restrict__ dout,
+              const double* __restrict__ rin, double* __restrict__ rout, const double* __restrict__ dinv, double c1, double c2,
+              double* __restrict__ x, const int* __restrict__ done) {
+  if (done && *done) return;
+  SLICE_LOOP {
+    double acc[C];
+    sell_dot<C>(slice_ptr, cols, val, din, s, lane, acc);
+    const int64_t row = s * MV_SLICE + lane;
+    if (row < nrows) {
+      const double di = __ldg(&dinv[row]);
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        const int64_t i = row * C + c;
+        const double t = di != 0.0 ? rin[i] - acc[c] : 0.0;
+        const double dd = c1 * din[i] + c2 * di * t;
+        dout[i] = dd;
+        x[i] += dd;
+        if (rout) rout[i] = t;
+      }
+    }
+  }
+}
+
+template <int C>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_residual(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
+           const double* __restrict__ val, const double* __restrict__ b, const double* __restrict__ x,
+           const double* __restrict__ dinv, double* __restrict__ r, const int* __restrict__ done) {
+  if (done && *done) return;
+  SLICE_LOOP {
+    double acc[C];
+    sell_dot<C>(slice_ptr, cols, val, x, s, lane, acc);
+    const int64_t row = s * MV_SLICE + lane;
+    if (row < nrows) {
+      const bool free_row = __ldg(&dinv[row]) != 0.0;
+#pragma unroll
+      for (int c = 0; c < C; ++c) r[row * C + c] = free_row ? b[row * C + c] - acc[c] : 0.0;
+    }
+  }
+}
+
+// y = S x (ADD = false) or y += S x (ADD = true) for the rectangular transfer operators
+template <int C, bool ADD>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_sell_apply(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
+             const double* __restrict__ val, const double* __restrict__ x, double* __restrict__ y, const int* __restrict__ done) {
+  if (done && *done) return;
+  SLICE_LOOP {
+    double acc[C];
+    sell_dot<C>(slice_ptr, cols, val, x, s, lane, acc);
+    const int64_t row = s * MV_SLICE + lane;
+    if (row < nrows) {
+#pragma unroll
+      for (int c = 0; c < C; ++c) y[row * C + c] = ADD ? y[row * C + c] + acc[c] : acc[c];
+    }
+  }
+}
+
+// x = Ainv b on the coarsest level: one warp per row, lanes stride the columns, fixed-order shuffle sum
+template <int C>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_dense_apply(int n, const double* __restrict__ inv, const double* __restrict__ b, double* __restrict__ x,
+              const int* __restrict__ done) {
+  if (done && *done) return;
+  const int lane = threadIdx.x & 31;
+  const int row = (int)((blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5);
+  if (row >= n) return;
+  double acc[C];
+#pragma unroll
+  for (int c = 0; c < C; ++c) acc[c] = 0.0;
+  for (int j = lane; j < n; j += 32) {
+    const double a = inv[(size_t)row * n + j];
+#pragma unroll
+    for (int c = 0; c < C; ++c) acc[c] = fma(a, b[(size_t)j * C + c], acc[c]);
+  }
+#pragma unroll
+  for (int c = 0; c < C; ++c) {
+    const double t = warp_sum(acc[c]);
+    if (lane == 0) x[(size_t)row * C + c] = t;
+  }
+}
+
+int amg_ensure_work(Amg* a, int C) {
+  for (size_t l = 0; l < a->lv.size(); ++l) {
+    AmgLevel& L = a->lv[l];
+    if (L.work_C >= C) continue;
+    if (l > 0) { dev_free(L.x0); dev_free(L.b); }
+    else dev_free(L.x0);
+    dev_free(L.x1); dev_free(L.r); dev_free(L.d0); dev_free(L.d1);
+    const size_t nt = (size_t)L.ntot * C;
+    MV_CHECK(dev_alloc(&L.x0, nt));
+    MV_CUDA(cudaMemsetAsync(L.x0, 0, nt * sizeof(double), g_stream));
+    if (l > 0) {
+      MV_CHECK(dev_alloc(&L.b, (size_t)L.n * C));
+      MV_CHECK(dev_alloc(&L.x1, nt));
+      MV_CUDA(cudaMemsetAsync(L.x1, 0, nt * sizeof(double), g_stream));
+    }
+    MV_CHECK(dev_alloc(&L.r, (size_t)L.n * C));
+    if (L.degree > 1) {
+      MV_CHECK(dev_alloc(&L.d0, nt));
+      MV_CHECK(dev_alloc(&L.d1, nt));
+      MV_CUDA(cudaMemsetAsync(L.d0, 0, nt * sizeof(double), g_stream));
+      MV_CUDA(cudaMemsetAsync(L.d1, 0, nt * sizeof(double), g_stream));
+    }
+    L.work_C = C;
+  }
+  if (a->z_C < C) {
+    dev_free(a->z);
+    MV_CHECK(dev_alloc(&a->z, (size_t)a->lv[0].ntot * C));
+    MV_CUDA(cudaMemsetAsync(a->z, 0, (size_t)a->lv[0].ntot * C * sizeof(double), g_stream));
+    a->z_C = C;
+  }
+  return MV_OK;
+}
+
+static inline int slice_grid(const Sell& p) { return grid_for(p.nslices * MV_SLICE, 8); }
+
+// Chebyshev(L.degree) on D^-1 A over [rho/ratio, rho].  xin == nullptr: zero initial guess.  Result in xout
+// (xout != xin).
+template <int C>
+static int smooth(AmgLevel& L, const double* b, const double* xin, double* xout, const int* done) {
+  const int deg = L.degree;
+  const double ratio = deg <= 1 ? 4.0 : 8.0;
+  const double lmax = L.rho, lmin = L.rho / ratio;
+  const double theta = 0.5 * (lmax + lmin), delta = 0.5 * (lmax - lmin), sigma = theta / delta;
+  const Sell& p = L.pat;
+  const int grid = slice_grid(p);
+  double* dcur = deg > 1 ? L.d0 : nullptr;
+  double* dnext = L.d1;
+  const double* rin = b;
+  if (!xin) {
+    MV_L k_smooth_zero<C><<<grid_for(L.n * C), MV_BLOCK, 0, g_stream>>>(L.n, b, L.dinv, 1.0 / theta, xout, dcur, done);
+  } else {
+    MV_L k_smooth_first<C><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, L.n, p.slice_ptr, p.cols, L.val, b, xin, L.dinv, 1.0 / theta, xout,
+                                                       dcur, deg > 1 ? L.r : nullptr, done);
+    rin = L.r;
+  }
+  double rho_k = 1.0 / sigma;
+  for (int k = 1; k < deg; ++k) {
+    const double rho_n = 1.0 / (2.0 * sigma - rho_k);
+    const bool last = k == deg - 1;
+    // TODO(multi-GPU): halo exchange of dcur
+    MV_L k_smooth_next<C><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, L.n, p.slice_ptr, p.cols, L.val, dcur, dnext, rin, last ? nullptr : L.r,
+                                                      L.dinv, rho_n * rho_k, 2.0 * rho_n / delta, xout, done);
+    rin = L.r;
+    rho_k = rho_n;
+    double* t = dcur; dcur = dnext; dnext = t;
+  }
+  MV_KERNEL_CHECK();
+  return MV_OK;
+}
+
+template <int C>
+static int vcycle(mv_mesh* m, Amg* a, const double* rfine, double* z, const int* done) {
+  const int nl = (int)a->lv.size();
+  const double* b = rfine;
+  for (int l = 0; l + 1 < nl; ++l) {
+    AmgLevel& L = a->lv[l];
+    AmgLevel& N = a->lv[l + 1];
+    MV_CHECK(smooth<C>(L, b, nullptr, L.x0, done));
+    // TODO(multi-GPU): halo exchange of L.x0
+    MV_L k_residual<C><<<slice_grid(L.pat), MV_BLOCK, 0, g_stream>>>(L.pat.nslices, L.n, L.pat.slice_ptr, L.pat.cols, L.val, b, L.x0, L.dinv,
+                                                                L.r, done);
+    MV_L k_sell_apply<C, false><<<slice_grid(L.R), MV_BLOCK, 0, g_stream>>>(L.R.nslices, N.n, L.R.slice_ptr, L.R.cols, L.Rval, L.r, N.b, done);
+    b = N.b;
+  }
+  AmgLevel& Lc = a->lv[nl - 1];
+  double* xc = nl == 1 ? z : Lc.x0;
+  if (a->coarse_inv) {
+    const int64_t threads = (int64_t)Lc.n * 32;
+    MV_L k_dense_apply<C><<<(unsigned)((threads + MV_BLOCK - 1) / MV_BLOCK), MV_BLOCK, 0, g_stream>>>((int)Lc.n, a->coarse_inv, b, xc, done);
+  } else {
+    MV_CHECK(smooth<C>(Lc, b, nullptr, xc, done));
+  }
+  MV_KERNEL_CHECK();
+  const double* xcoarse = xc;
+  for (int l = nl - 2; l >= 0; --l) {
+    AmgLevel& L = a->lv[l];
+    MV_L k_sell_apply<C, true><<<slice_grid(L.P), MV_BLOCK, 0, g_stream>>>(L.P.nslices, L.n, L.P.slice_ptr, L.P.cols, L.Pval, xcoarse, L.x0, done);
+    double* out = l == 0 ? z : L.x1;
+    // TODO(multi-GPU): halo exchange of L.x0
+    MV_CHECK(smooth<C>(L, l == 0 ? rfine : L.b, L.x0, out, done));
+    xcoarse = out;
+  }
+  (void)m;
+  return MV_OK;
+}
+
+int amg_apply(mv_mesh* m, Amg* a, int C, const double* r, double* z, const int* done) {
+  MV_CHECK(amg_ensure_work(a, C));
+  switch (C) {
+    case 1: return vcycle<1>(m, a, r, z, done);
+    case 2: return vcycle<2>(m, a, r, z, done);
+    case 3: return vcycle<3>(m, a, r, z, done);
+  }
+  set_error("amg: unsupported number of right-hand sides %d", C);
+  return MV_ERR_UNSUPPORTED;
+}
+
+}  // namespace mv

@@ -60,7 +60,7 @@ int exclusive_scan_i32(const int* in, int* out, int64_t n) {
   MV_CUDA(cudaFreeAsync(tmp, g_stream));
   return MV_OK;
 }
-static int exclusive_scan_i64(const int64_t* in, int64_t* out, int64_t n) {
+int exclusive_scan_i64(const int64_t* in, int64_t* out, int64_t n) {
   void* tmp = nullptr;
   size_t bytes = 0;
   MV_CUDA(cub::DeviceScan::ExclusiveSum(tmp, bytes, in, out, (int)n, g_stream));
@@ -490,6 +490,7 @@ extern "C" void mv_mesh_destroy(mv_mesh* m) {
   if (m->pcg.h_scal) cudaFreeHost(m->pcg.h_scal);
   dev_free(m->halo.send_idx); dev_free(m->halo.send_buf);
   dev_free(m->tmp_vec);
+  mv::amg_release(m);
   delete m;
 }
 

@@ -126,6 +126,47 @@ struct PcgWork {
   double* h_scal = nullptr; // pinned host mirror
 };
 
+// ---------------------------------------------------------------------------------
+// smoothed-aggregation multigrid hierarchy (mv_amg.cu builds it, mv_amg_cycle.cu applies it)
+// ---------------------------------------------------------------------------------
+struct Csr {
+  int64_t nrows = 0, ncols = 0, nnz = 0;
+  int64_t* ptr = nullptr;   // [nrows+1]
+  int* col = nullptr;       // sorted ascending inside a row
+  double* val = nullptr;
+  void release();
+};
+
+struct AmgLevel {
+  int64_t n = 0;            // owned rows
+  int64_t ntot = 0;         // owned + ghost columns of A
+  Sell pat;                 // operator of this level (level 0 borrows the mesh pattern)
+  const double* val = nullptr;
+  bool owns_A = false;
+  double* dinv = nullptr;   // [n]; 0 at constrained vertices
+  const uint16_t* mask = nullptr;  // level 0 only: bit 0 set = constrained vertex
+  double rho = 0.0;         // upper bound of spec(D^-1 A)
+  int degree = 1;           // Chebyshev smoother degree
+  Sell P;  double* Pval = nullptr;   // [n x n_coarse]
+  Sell R;  double* Rval = nullptr;   // [n_coarse x n] = P^T
+  double *x0 = nullptr, *x1 = nullptr, *b = nullptr, *r = nullptr, *d0 = nullptr, *d1 = nullptr;  // [ntot*C]
+  int work_C = 0;
+};
+
+struct Amg {
+  std::vector<AmgLevel> lv;
+  int op = 0;
+  int singular = 0;
+  uint64_t mask_hash = 0;
+  uint16_t* mask_copy = nullptr;  // level-0 constrained set (bit 0), owned by the hierarchy
+  int64_t nc = 0;                 // coarsest size
+  double* coarse_inv = nullptr;   // dense [nc*nc] inverse (shifted if singular), or nullptr -> smoother only
+  double* z = nullptr;            // [n0*C] preconditioned residual for PCG
+  int z_C = 0;
+  double setup_ms = 0.0;
+  ~Amg();
+};
+
 }  // namespace mv
 
 struct mv_mesh {
@@ -162,6 +203,9 @@ struct mv_mesh {
   mv::PcgWork pcg;
   mv::Halo halo;
   double* tmp_vec = nullptr;   // [V*MV_MAX_COMP]
+  // preconditioner of the stiffness-type operators: MV_PC_JACOBI or MV_PC_AMG
+  int pc_kind = 1;
+  std::vector<mv::Amg*> amg;   // cached hierarchies (one per operator / constrained set)
 };
 
 struct mv_ma {
@@ -225,6 +269,12 @@ int jac_A_dev(mv_mesh* m, const double* mon, const double* H, const double* dH, 
 bool comm_active();
 int comm_size();
 int grid_for(int64_t nthreads_needed, int blocks_per_sm = 8);
+int exclusive_scan_i64(const int64_t* in, int64_t* out, int64_t n);
+// multigrid (mv_amg.cu / mv_amg_cycle.cu)
+int amg_get(mv_mesh* m, int op, const uint16_t* mask, int ncomp, int singular, Amg** out);  // *out = nullptr -> use Jacobi
+int amg_apply(mv_mesh* m, Amg* a, int ncomp, const double* r, double* z, const int* done);
+int amg_ensure_work(Amg* a, int ncomp);
+void amg_release(mv_mesh* m);
 
 // ---------------------------------------------------------------------------------
 // device helpers
