@@ -22,8 +22,8 @@ namespace mv {
 
 template <int C>
 __device__ __forceinline__ void sell_dot(const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
-                                         const double* __restrict__ val, const double* __restrict__ x, int64_t s, int lane,
-                                         double (&acc)[C]) {
+                                         const double* __restrict__ val, const double* __restrict__ x, int64_t ldx, int64_t s,
+                                         int lane, double (&acc)[C]) {
   const int64_t base = __ldg(&slice_ptr[s]);
   const int w = (int)((__ldg(&slice_ptr[s + 1]) - base) >> 5);
   const int* cp = cols + base + lane;
@@ -34,9 +34,9 @@ __device__ __forceinline__ void sell_dot(const int64_t* __restrict__ slice_ptr, 
   for (int k = 0; k < w; ++k) {
     const int col = __ldcs(cp + k * MV_SLICE);
     const double a = __ldcs(vp + k * MV_SLICE);
-    const double* xp = x + (int64_t)col * C;
+    const double* xp = x + col;
 #pragma unroll
-    for (int c = 0; c < C; ++c) acc[c] = fma(a, __ldg(xp + c), acc[c]);
+    for (int c = 0; c < C; ++c) acc[c] = fma(a, __ldg(xp + c * ldx), acc[c]);
   }
 }
 
@@ -49,33 +49,36 @@ __device__ __forceinline__ void sell_dot(const int64_t* __restrict__ slice_ptr, 
 // x = d = D^-1 b / theta (zero initial guess)
 template <int C>
 __global__ void __launch_bounds__(MV_BLOCK)
-k_smooth_zero(int64_t n, const double* __restrict__ b, const double* __restrict__ dinv, double sc, double* __restrict__ x,
+k_smooth_zero(int64_t n, int64_t ld, const double* __restrict__ b, const double* __restrict__ dinv, double sc, double* __restrict__ x,
               double* __restrict__ d, const int* __restrict__ done) {
   if (done && *done) return;
-  const int64_t ne = n * C;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < ne; i += (int64_t)gridDim.x * blockDim.x) {
-    const double t = sc * __ldg(&dinv[i / C]) * b[i];
-    x[i] = t;
-    if (d) d[i] = t;
+  for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < n; v += (int64_t)gridDim.x * blockDim.x) {
+    const double di = sc * __ldg(&dinv[v]);
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const double t = di * b[c * ld + v];
+      x[c * ld + v] = t;
+      if (d) d[c * ld + v] = t;
+    }
   }
 }
 
 template <int C>
 __global__ void __launch_bounds__(MV_BLOCK)
-k_smooth_first(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
+k_smooth_first(int64_t nslices, int64_t nrows, int64_t ld, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
                const double* __restrict__ val, const double* __restrict__ b, const double* __restrict__ xin,
                const double* __restrict__ dinv, double sc, double* __restrict__ xout, double* __restrict__ d,
                double* __restrict__ r, const int* __restrict__ done) {
   if (done && *done) return;
   SLICE_LOOP {
     double acc[C];
-    sell_dot<C>(slice_ptr, cols, val, xin, s, lane, acc);
+    sell_dot<C>(slice_ptr, cols, val, xin, ld, s, lane, acc);
     const int64_t row = s * MV_SLICE + lane;
     if (row < nrows) {
       const double di = __ldg(&dinv[row]);
 #pragma unroll
       for (int c = 0; c < C; ++c) {
-        const int64_t i = row * C + c;
+        const int64_t i = c * ld + row;
         const double t = di != 0.0 ? b[i] - acc[c] : 0.0;
         const double dd = sc * di * t;
         xout[i] = xin[i] + dd;
@@ -88,20 +91,20 @@ k_smooth_first(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice
 
 template <int C>
 __global__ void __launch_bounds__(MV_BLOCK)
-k_smooth_next(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
+k_smooth_next(int64_t nslices, int64_t nrows, int64_t ld, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
               const double* __restrict__ val, const double* __restrict__ din, double* __restrict__ dout,
               const double* __restrict__ rin, double* __restrict__ rout, const double* __restrict__ dinv, double c1, double c2,
               double* __restrict__ x, const int* __restrict__ done) {
   if (done && *done) return;
   SLICE_LOOP {
     double acc[C];
-    sell_dot<C>(slice_ptr, cols, val, din, s, lane, acc);
+    sell_dot<C>(slice_ptr, cols, val, din, ld, s, lane, acc);
     const int64_t row = s * MV_SLICE + lane;
     if (row < nrows) {
       const double di = __ldg(&dinv[row]);
 #pragma unroll
       for (int c = 0; c < C; ++c) {
-        const int64_t i = row * C + c;
+        const int64_t i = c * ld + row;
         const double t = di != 0.0 ? rin[i] - acc[c] : 0.0;
         const double dd = c1 * din[i] + c2 * di * t;
         dout[i] = dd;
@@ -114,18 +117,18 @@ k_smooth_next(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_
 
 template <int C>
 __global__ void __launch_bounds__(MV_BLOCK)
-k_residual(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
+k_residual(int64_t nslices, int64_t nrows, int64_t ld, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
            const double* __restrict__ val, const double* __restrict__ b, const double* __restrict__ x,
            const double* __restrict__ dinv, double* __restrict__ r, const int* __restrict__ done) {
   if (done && *done) return;
   SLICE_LOOP {
     double acc[C];
-    sell_dot<C>(slice_ptr, cols, val, x, s, lane, acc);
+    sell_dot<C>(slice_ptr, cols, val, x, ld, s, lane, acc);
     const int64_t row = s * MV_SLICE + lane;
     if (row < nrows) {
       const bool free_row = __ldg(&dinv[row]) != 0.0;
 #pragma unroll
-      for (int c = 0; c < C; ++c) r[row * C + c] = free_row ? b[row * C + c] - acc[c] : 0.0;
+      for (int c = 0; c < C; ++c) r[c * ld + row] = free_row ? b[c * ld + row] - acc[c] : 0.0;
     }
   }
 }
@@ -134,15 +137,16 @@ k_residual(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_ptr
 template <int C, bool ADD>
 __global__ void __launch_bounds__(MV_BLOCK)
 k_sell_apply(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
-             const double* __restrict__ val, const double* __restrict__ x, double* __restrict__ y, const int* __restrict__ done) {
+             const double* __restrict__ val, const double* __restrict__ x, int64_t ldx, double* __restrict__ y, int64_t ldy,
+             const int* __restrict__ done) {
   if (done && *done) return;
   SLICE_LOOP {
     double acc[C];
-    sell_dot<C>(slice_ptr, cols, val, x, s, lane, acc);
+    sell_dot<C>(slice_ptr, cols, val, x, ldx, s, lane, acc);
     const int64_t row = s * MV_SLICE + lane;
     if (row < nrows) {
 #pragma unroll
-      for (int c = 0; c < C; ++c) y[row * C + c] = ADD ? y[row * C + c] + acc[c] : acc[c];
+      for (int c = 0; c < C; ++c) y[c * ldy + row] = ADD ? y[c * ldy + row] + acc[c] : acc[c];
     }
   }
 }
@@ -150,7 +154,7 @@ k_sell_apply(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_p
 // x = Ainv b on the coarsest level: one warp per row, lanes stride the columns, fixed-order shuffle sum
 template <int C>
 __global__ void __launch_bounds__(MV_BLOCK)
-k_dense_apply(int n, const double* __restrict__ inv, const double* __restrict__ b, double* __restrict__ x,
+k_dense_apply(int n, int64_t ld, const double* __restrict__ inv, const double* __restrict__ b, double* __restrict__ x,
               const int* __restrict__ done) {
   if (done && *done) return;
   const int lane = threadIdx.x & 31;
@@ -162,12 +166,12 @@ k_dense_apply(int n, const double* __restrict__ inv, const double* __restrict__ 
   for (int j = lane; j < n; j += 32) {
     const double a = inv[(size_t)row * n + j];
 #pragma unroll
-    for (int c = 0; c < C; ++c) acc[c] = fma(a, b[(size_t)j * C + c], acc[c]);
+    for (int c = 0; c < C; ++c) acc[c] = fma(a, b[c * ld + j], acc[c]);
   }
 #pragma unroll
   for (int c = 0; c < C; ++c) {
     const double t = warp_sum(acc[c]);
-    if (lane == 0) x[(size_t)row * C + c] = t;
+    if (lane == 0) x[c * ld + row] = t;
   }
 }
 
@@ -182,11 +186,11 @@ int amg_ensure_work(Amg* a, int C) {
     MV_CHECK(dev_alloc(&L.x0, nt));
     MV_CUDA(cudaMemsetAsync(L.x0, 0, nt * sizeof(double), g_stream));
     if (l > 0) {
-      MV_CHECK(dev_alloc(&L.b, (size_t)L.n * C));
+      MV_CHECK(dev_alloc(&L.b, nt));
       MV_CHECK(dev_alloc(&L.x1, nt));
       MV_CUDA(cudaMemsetAsync(L.x1, 0, nt * sizeof(double), g_stream));
     }
-    MV_CHECK(dev_alloc(&L.r, (size_t)L.n * C));
+    MV_CHECK(dev_alloc(&L.r, nt));
     if (L.degree > 1) {
       MV_CHECK(dev_alloc(&L.d0, nt));
       MV_CHECK(dev_alloc(&L.d1, nt));
@@ -220,9 +224,9 @@ static int smooth(AmgLevel& L, const double* b, const double* xin, double* xout,
   double* dnext = L.d1;
   const double* rin = b;
   if (!xin) {
-    MV_L k_smooth_zero<C><<<grid_for(L.n * C), MV_BLOCK, 0, g_stream>>>(L.n, b, L.dinv, 1.0 / theta, xout, dcur, done);
+    MV_L k_smooth_zero<C><<<grid_for(L.n), MV_BLOCK, 0, g_stream>>>(L.n, L.ntot, b, L.dinv, 1.0 / theta, xout, dcur, done);
   } else {
-    MV_L k_smooth_first<C><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, L.n, p.slice_ptr, p.cols, L.val, b, xin, L.dinv, 1.0 / theta, xout,
+    MV_L k_smooth_first<C><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, L.n, L.ntot, p.slice_ptr, p.cols, L.val, b, xin, L.dinv, 1.0 / theta, xout,
                                                        dcur, deg > 1 ? L.r : nullptr, done);
     rin = L.r;
   }
@@ -231,7 +235,7 @@ static int smooth(AmgLevel& L, const double* b, const double* xin, double* xout,
     const double rho_n = 1.0 / (2.0 * sigma - rho_k);
     const bool last = k == deg - 1;
     // TODO(multi-GPU): halo exchange of dcur
-    MV_L k_smooth_next<C><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, L.n, p.slice_ptr, p.cols, L.val, dcur, dnext, rin, last ? nullptr : L.r,
+    MV_L k_smooth_next<C><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, L.n, L.ntot, p.slice_ptr, p.cols, L.val, dcur, dnext, rin, last ? nullptr : L.r,
                                                       L.dinv, rho_n * rho_k, 2.0 * rho_n / delta, xout, done);
     rin = L.r;
     rho_k = rho_n;
@@ -250,16 +254,16 @@ static int vcycle(mv_mesh* m, Amg* a, const double* rfine, double* z, const int*
     AmgLevel& N = a->lv[l + 1];
     MV_CHECK(smooth<C>(L, b, nullptr, L.x0, done));
     // TODO(multi-GPU): halo exchange of L.x0
-    MV_L k_residual<C><<<slice_grid(L.pat), MV_BLOCK, 0, g_stream>>>(L.pat.nslices, L.n, L.pat.slice_ptr, L.pat.cols, L.val, b, L.x0, L.dinv,
+    MV_L k_residual<C><<<slice_grid(L.pat), MV_BLOCK, 0, g_stream>>>(L.pat.nslices, L.n, L.ntot, L.pat.slice_ptr, L.pat.cols, L.val, b, L.x0, L.dinv,
                                                                 L.r, done);
-    MV_L k_sell_apply<C, false><<<slice_grid(L.R), MV_BLOCK, 0, g_stream>>>(L.R.nslices, N.n, L.R.slice_ptr, L.R.cols, L.Rval, L.r, N.b, done);
+    MV_L k_sell_apply<C, false><<<slice_grid(L.R), MV_BLOCK, 0, g_stream>>>(L.R.nslices, N.n, L.R.slice_ptr, L.R.cols, L.Rval, L.r, L.ntot, N.b, N.ntot, done);
     b = N.b;
   }
   AmgLevel& Lc = a->lv[nl - 1];
   double* xc = nl == 1 ? z : Lc.x0;
   if (a->coarse_inv) {
     const int64_t threads = (int64_t)Lc.n * 32;
-    MV_L k_dense_apply<C><<<(unsigned)((threads + MV_BLOCK - 1) / MV_BLOCK), MV_BLOCK, 0, g_stream>>>((int)Lc.n, a->coarse_inv, b, xc, done);
+    MV_L k_dense_apply<C><<<(unsigned)((threads + MV_BLOCK - 1) / MV_BLOCK), MV_BLOCK, 0, g_stream>>>((int)Lc.n, Lc.ntot, a->coarse_inv, b, xc, done);
   } else {
     MV_CHECK(smooth<C>(Lc, b, nullptr, xc, done));
   }
@@ -267,7 +271,7 @@ static int vcycle(mv_mesh* m, Amg* a, const double* rfine, double* z, const int*
   const double* xcoarse = xc;
   for (int l = nl - 2; l >= 0; --l) {
     AmgLevel& L = a->lv[l];
-    MV_L k_sell_apply<C, true><<<slice_grid(L.P), MV_BLOCK, 0, g_stream>>>(L.P.nslices, L.n, L.P.slice_ptr, L.P.cols, L.Pval, xcoarse, L.x0, done);
+    MV_L k_sell_apply<C, true><<<slice_grid(L.P), MV_BLOCK, 0, g_stream>>>(L.P.nslices, L.n, L.P.slice_ptr, L.P.cols, L.Pval, xcoarse, a->lv[l + 1].ntot, L.x0, L.ntot, done);
     double* out = l == 0 ? z : L.x1;
     // TODO(multi-GPU): halo exchange of L.x0
     MV_CHECK(smooth<C>(L, l == 0 ? rfine : L.b, L.x0, out, done));

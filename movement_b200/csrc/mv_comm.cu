@@ -122,6 +122,33 @@ int halo_exchange(mv_mesh* m, int C, double* vec) {
   return MV_OK;
 }
 
+// component-major vectors ([C][ld]): one contiguous segment per component and neighbour, received in place
+__global__ void k_halo_pack_soa(int64_t nsend, int C, const int* __restrict__ idx, const double* __restrict__ vec, int64_t ld,
+                                double* __restrict__ buf) {
+  const int64_t n = nsend * C;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t c = i / nsend, t = i - c * nsend;
+    buf[i] = vec[c * ld + idx[t]];
+  }
+}
+
+int halo_exchange_soa(const Halo& h, int64_t nown, int C, double* vec, int64_t ld) {
+  if (!comm_active() || h.nn == 0) return MV_OK;
+  const int64_t nsend = h.send_ptr[h.nn];
+  if (nsend > 0) MV_L k_halo_pack_soa<<<grid_for(nsend * C), MV_BLOCK, 0, g_stream>>>(nsend, C, h.send_idx, vec, ld, h.send_buf);
+  MV_KERNEL_CHECK();
+  MV_NCCL(g_nccl.GroupStart());
+  for (int k = 0; k < h.nn; ++k) {
+    const int64_t ns = h.send_ptr[k + 1] - h.send_ptr[k], nr = h.recv_ptr[k + 1] - h.recv_ptr[k];
+    for (int c = 0; c < C; ++c) {
+      if (ns > 0) MV_NCCL(g_nccl.Send(h.send_buf + c * nsend + h.send_ptr[k], (size_t)ns, ncclDouble, h.ranks[k], g_comm, g_stream));
+      if (nr > 0) MV_NCCL(g_nccl.Recv(vec + c * ld + nown + h.recv_ptr[k], (size_t)nr, ncclDouble, h.ranks[k], g_comm, g_stream));
+    }
+  }
+  MV_NCCL(g_nccl.GroupEnd());
+  return MV_OK;
+}
+
 }  // namespace mv
 
 using namespace mv;

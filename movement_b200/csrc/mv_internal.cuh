@@ -120,6 +120,7 @@ struct Reduce {
 
 struct PcgWork {
   double *r = nullptr, *p = nullptr, *q = nullptr;  // [V*MV_MAX_COMP] (p spans ghosts)
+  double* xs = nullptr;     // component-major copy of the iterate (mv_pcg_soa.cu)
   double* scal = nullptr;   // device scalars, see pcg.cu
   int* flags = nullptr;     // device: [0]=done, [1]=iterations, [2]=breakdown
   int* h_flags = nullptr;   // pinned host mirror
@@ -255,6 +256,9 @@ int exclusive_scan_i32(const int* in, int* out, int64_t n);
 int pcg_solve(mv_mesh* m, int op, int ncomp, const double* rhs, double* x, const uint16_t* mask,
               double rtol, double atol, int maxit, int project_mean, int* iters, double* relres);
 int spmv(mv_mesh* m, int op, int ncomp, const double* x, double* y);
+int pcg_solve_soa(mv_mesh* m, int ncomp, const double* val, const double* dinv, const double* rhs, double* x, const uint16_t* mask,
+                  double rtol, double atol, int maxit, int project_mean, int* iters, double* relres, Amg* pc);
+int halo_exchange_soa(const Halo& h, int64_t nown, int C, double* vec, int64_t ld);
 int op_arrays(mv_mesh* m, int op, const double** val, const double** dinv);
 int halo_exchange(mv_mesh* m, int ncomp, double* vec);
 int allreduce_sum_dev(double* dscal, int n);

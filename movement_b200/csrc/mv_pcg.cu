@@ -260,62 +260,6 @@ __global__ void k_dinv_sum(int64_t n, const double* __restrict__ a, const double
   }
 }
 
-// ---- multigrid-preconditioned variant: z comes from the V-cycle, so the update carries no reduction
-template <int C>
-__global__ void __launch_bounds__(MV_BLOCK)
-k_pcg_update_plain(int64_t nrows, const double* __restrict__ p, const double* __restrict__ q, const uint16_t* __restrict__ mask,
-                   double* __restrict__ x, double* __restrict__ r, const int* __restrict__ flags, const double* __restrict__ scal) {
-  if (flags[0]) return;
-  __shared__ double s_alpha[C];
-  if (threadIdx.x < C) {
-    const double pq = scal[SC(S_PQ, threadIdx.x)], rz = scal[SC(S_RZ, threadIdx.x)];
-    s_alpha[threadIdx.x] = pq > 0.0 ? rz / pq : 0.0;
-  }
-  __syncthreads();
-  const int64_t n = nrows * C;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t v = i / C;
-    const int c = (int)(i - v * C);
-    const double al = s_alpha[c];
-    x[i] += al * p[i];
-    r[i] = masked<C>(mask, v, c) ? 0.0 : r[i] - al * __ldcs(&q[i]);
-  }
-}
-// r.z -> slot; POST: also beta / convergence / iteration count
-template <int C, int POST>
-__global__ void __launch_bounds__(MV_BLOCK)
-k_pcg_dot_rz(int64_t nrows, const double* __restrict__ r, const double* __restrict__ z, int* __restrict__ flags,
-             double* __restrict__ partials, unsigned* __restrict__ counter, double* __restrict__ scal, int slot, int slot2) {
-  if (POST && flags[0]) return;
-  double acc[C];
-#pragma unroll
-  for (int c = 0; c < C; ++c) acc[c] = 0.0;
-  for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < nrows; v += (int64_t)gridDim.x * blockDim.x)
-#pragma unroll
-    for (int c = 0; c < C; ++c) acc[c] = fma(r[v * C + c], z[v * C + c], acc[c]);
-  grid_reduce_sum<C>(acc, partials, counter, [&](double(&t)[C]) {
-#pragma unroll
-    for (int c = 0; c < C; ++c) {
-      scal[SC(slot, c)] = t[c];
-      if (slot2 >= 0) scal[SC(slot2, c)] = t[c];
-    }
-    if (POST == 1) pcg_post_update(C, scal, flags);
-  });
-}
-// p = z + beta p  (first = 1: p = z)
-template <int C>
-__global__ void __launch_bounds__(MV_BLOCK)
-k_pcg_dir_z(int64_t nrows, const double* __restrict__ z, double* __restrict__ p, const int* __restrict__ flags,
-            const double* __restrict__ scal, int first) {
-  if (!first && flags[0]) return;
-  __shared__ double s_beta[C];
-  if (threadIdx.x < C) s_beta[threadIdx.x] = first ? 0.0 : scal[SC(S_BETA, threadIdx.x)];
-  __syncthreads();
-  const int64_t n = nrows * C;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    p[i] = first ? z[i] : fma(s_beta[(int)(i % C)], p[i], z[i]);
-}
-
 int op_arrays(mv_mesh* m, int op, const double** val, const double** dinv) {
   switch (op) {
     case MV_OP_MASS: *val = m->Mval; *dinv = m->dinvM; return MV_OK;
@@ -357,9 +301,11 @@ static int ensure_pcg_work(mv_mesh* m) {
   PcgWork& w = m->pcg;
   if (w.r) return MV_OK;
   const size_t maxc = (size_t)m->dim * m->dim;
-  MV_CHECK(dev_alloc(&w.r, m->Vown * maxc));
-  MV_CHECK(dev_alloc(&w.q, m->Vown * maxc));
+  MV_CHECK(dev_alloc(&w.r, m->V * maxc));
+  MV_CHECK(dev_alloc(&w.q, m->V * maxc));
   MV_CHECK(dev_alloc(&w.p, m->V * maxc));
+  MV_CHECK(dev_alloc(&w.xs, m->V * maxc));
+  MV_CUDA(cudaMemsetAsync(w.xs, 0, m->V * maxc * sizeof(double), g_stream));
   MV_CHECK(dev_alloc(&w.scal, S_NSLOTS * 16));
   MV_CHECK(dev_alloc(&w.flags, 4));
   MV_CUDA(cudaMemsetAsync(w.scal, 0, S_NSLOTS * 16 * sizeof(double), g_stream));
@@ -378,7 +324,7 @@ static int apply_op(mv_mesh* m, const LinOp& op, const uint16_t* mask, const dou
 
 template <int C>
 static int pcg_impl(mv_mesh* m, const LinOp& op, const double* rhs, double* x, const uint16_t* mask,
-                    double rtol, double atol, int maxit, int project_mean, int* iters, double* relres, Amg* pc = nullptr) {
+                    double rtol, double atol, int maxit, int project_mean, int* iters, double* relres) {
   MV_CHECK(ensure_pcg_work(m));
   const double* dinv = op.dinv;
   const int dpd = op.dpd, coupled = op.coupled;
@@ -413,18 +359,10 @@ static int pcg_impl(mv_mesh* m, const LinOp& op, const double* rhs, double* x, c
     MV_CHECK(allreduce_sum_dev(w.scal + SC(S_RZ, 0), C));
     MV_CHECK(allreduce_sum_dev(w.scal + SC(S_BB, 0), C));
   }
-  if (pc) {
-    // z0 = M^-1 r0 by one V-cycle; reference norm r0.z0
-    MV_CHECK(amg_ensure_work(pc, C));
-    MV_CHECK(amg_apply(m, pc, C, w.r, pc->z, nullptr));
-    MV_L k_pcg_dot_rz<C, 0><<<gv, MV_BLOCK, 0, g_stream>>>(n, w.r, pc->z, w.flags, m->red.partials, m->red.counter, w.scal, S_RZ, S_BB);
-    MV_L k_pcg_dir_z<C><<<ge, MV_BLOCK, 0, g_stream>>>(n, pc->z, w.p, w.flags, w.scal, 1);
-    MV_KERNEL_CHECK();
-  }
   MV_L k_pcg_setup<<<1, 1, 0, g_stream>>>(C, rtol, atol, w.scal, w.flags);
   MV_KERNEL_CHECK();
 
-  int it = 0, batch = pc ? 4 : 8;
+  int it = 0, batch = 8;
   w.h_flags[0] = 0;
   while (true) {
     MV_CUDA(cudaMemcpyAsync(w.h_flags, w.flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, g_stream));
@@ -437,13 +375,6 @@ static int pcg_impl(mv_mesh* m, const LinOp& op, const double* rhs, double* x, c
       const int pslot = prof_begin(C);
       MV_CHECK(apply_op<C>(m, op, mask, w.p, w.q, true));
       prof_end(pslot);
-      if (pc) {
-        MV_L k_pcg_update_plain<C><<<ge, MV_BLOCK, 0, g_stream>>>(n, w.p, w.q, mask, x, w.r, w.flags, w.scal);
-        MV_CHECK(amg_apply(m, pc, C, w.r, pc->z, w.flags));
-        MV_L k_pcg_dot_rz<C, 1><<<gv, MV_BLOCK, 0, g_stream>>>(n, w.r, pc->z, w.flags, m->red.partials, m->red.counter, w.scal, S_RZNEW, -1);
-        MV_L k_pcg_dir_z<C><<<ge, MV_BLOCK, 0, g_stream>>>(n, pc->z, w.p, w.flags, w.scal, 0);
-        continue;
-      }
       if (dist) {
         MV_CHECK(allreduce_sum_dev(w.scal + SC(S_PQ, 0), C));
         MV_L k_pcg_update<C, false><<<ge, MV_BLOCK, 0, g_stream>>>(n, w.p, w.q, dinv, mask, x, w.r, w.flags, m->red.partials,
@@ -458,7 +389,7 @@ static int pcg_impl(mv_mesh* m, const LinOp& op, const double* rhs, double* x, c
     }
     MV_KERNEL_CHECK();
     it += nb;
-    if (batch < (pc ? 16 : 64)) batch *= 2;
+    if (batch < 64) batch *= 2;
   }
   const int done = w.h_flags[0], niter = w.h_flags[1], breakdown = w.h_flags[2];
   g_prof.pcg_iters[C & 15] += niter;
@@ -498,15 +429,7 @@ int pcg_solve(mv_mesh* m, int op, int ncomp, const double* rhs, double* x, const
   }
   Amg* pc = nullptr;
   if (ncomp <= 3) MV_CHECK(amg_get(m, op, mask, ncomp, project_mean, &pc));
-  switch (ncomp) {
-    case 1: return pcg_impl<1>(m, lop, rhs, x, mask, rtol, atol, maxit, project_mean, iters, relres, pc);
-    case 2: return pcg_impl<2>(m, lop, rhs, x, mask, rtol, atol, maxit, project_mean, iters, relres, pc);
-    case 3: return pcg_impl<3>(m, lop, rhs, x, mask, rtol, atol, maxit, project_mean, iters, relres, pc);
-    case 4: return pcg_impl<4>(m, lop, rhs, x, mask, rtol, atol, maxit, project_mean, iters, relres);
-    case 9: return pcg_impl<9>(m, lop, rhs, x, mask, rtol, atol, maxit, project_mean, iters, relres);
-  }
-  set_error("pcg: unsupported ncomp %d (1,2,3,4,9)", ncomp);
-  return MV_ERR_UNSUPPORTED;
+  return pcg_solve_soa(m, ncomp, lop.val, lop.dinv, rhs, x, mask, rtol, atol, maxit, project_mean, iters, relres, pc);
 }
 
 int pcg_solve_spring(mv_mesh* m, const double* coords, const double* dinv_dof, double* x, const uint16_t* mask,

@@ -1,0 +1,446 @@
+// Preconditioned CG for the assembled (SELL-32) operators with C right-hand sides sharing one
+// matrix stream, working vectors held COMPONENT-MAJOR ([C][ld], "SoA").
+//
+// replaces: PETSc KSP `cg` (movement/solver_parameters.py:62-71) at movement/monge_ampere.py:340
+//           (d mass solves), :441-448 (Poisson, gamg), :483 (d*d mass solves) and
+//           movement/laplacian_smoothing.py:75 (d stiffness solves).
+//
+// Why component-major inside the solve: the user-facing fields are Firedrake's interleaved
+// [V,C] arrays, but a warp that gathers x[col*C + c] for 32 consecutive rows touches 32 sectors per
+// load instruction (stride 8C bytes) and the C = 9 SpMV became LSU-bound at 2.1 TB/s (ncu, round 1).
+// With [C][ld] every gather/stream instruction of a warp covers 256 contiguous bytes, and the
+// per-component dot products need no index arithmetic.  The right-hand side and the initial guess
+// are converted on entry, the solution on exit (two passes per solve, < 1 % of its traffic).
+//
+// One iteration: k_spmv_soa (q = A p, fused p.q) -> k_update_soa (x += a p, r -= a q, fused
+// r.D^-1 r, beta, convergence flag) -> k_dir_soa (p = D^-1 r + b p); with the multigrid
+// preconditioner the update carries no reduction and z = V-cycle(r) follows (mv_amg_cycle.cu).
+// Scalars stay on the device; reductions are deterministic (mv_internal.cuh).
+#include "mv_internal.cuh"
+
+namespace mv {
+
+#define VERTEX_LOOP(v, n) for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < (n); v += (int64_t)gridDim.x * blockDim.x)
+
+template <int C>
+__device__ __forceinline__ bool fixed_dof(const uint16_t* __restrict__ mask, int64_t v, int c) {
+  return mask != nullptr && ((__ldg(&mask[v]) >> c) & 1);
+}
+
+// ------------------------------------------------------------------ layout conversion
+template <int C>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_aos_to_soa(int64_t n, const double* __restrict__ src, double* __restrict__ dst, int64_t ld) {
+  __shared__ double tile[MV_BLOCK * C];
+  for (int64_t v0 = blockIdx.x * (int64_t)MV_BLOCK; v0 < n; v0 += (int64_t)gridDim.x * MV_BLOCK) {
+    const int nv = (int)(n - v0 < MV_BLOCK ? n - v0 : MV_BLOCK);
+    for (int e = threadIdx.x; e < nv * C; e += MV_BLOCK) tile[e] = src[v0 * C + e];
+    __syncthreads();
+    if ((int)threadIdx.x < nv)
+#pragma unroll
+      for (int c = 0; c < C; ++c) dst[c * ld + v0 + threadIdx.x] = tile[threadIdx.x * C + c];
+    __syncthreads();
+  }
+}
+template <int C>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_soa_to_aos(int64_t n, const double* __restrict__ src, int64_t ld, double* __restrict__ dst) {
+  __shared__ double tile[MV_BLOCK * C];
+  for (int64_t v0 = blockIdx.x * (int64_t)MV_BLOCK; v0 < n; v0 += (int64_t)gridDim.x * MV_BLOCK) {
+    const int nv = (int)(n - v0 < MV_BLOCK ? n - v0 : MV_BLOCK);
+    if ((int)threadIdx.x < nv)
+#pragma unroll
+      for (int c = 0; c < C; ++c) tile[threadIdx.x * C + c] = src[c * ld + v0 + threadIdx.x];
+    __syncthreads();
+    for (int e = threadIdx.x; e < nv * C; e += MV_BLOCK) dst[v0 * C + e] = tile[e];
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------ SpMV, component-major
+template <int C, bool DOT>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_spmv_soa(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
+           const double* __restrict__ val, const double* __restrict__ x, int64_t ld, double* __restrict__ y,
+           const int* __restrict__ done, double* __restrict__ partials, unsigned* __restrict__ counter,
+           double* __restrict__ scal, int dot_slot) {
+  if (DOT && done != nullptr && *done) return;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  double dot[C];
+#pragma unroll
+  for (int c = 0; c < C; ++c) dot[c] = 0.0;
+  for (int64_t s = warp0; s < nslices; s += nwarps) {
+    const int64_t base = __ldg(&slice_ptr[s]);
+    const int w = (int)((__ldg(&slice_ptr[s + 1]) - base) >> 5);
+    const int64_t row = s * MV_SLICE + lane;
+    const int* cp = cols + base + lane;
+    const double* vp = val + base + lane;
+    double acc[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) acc[c] = 0.0;
+#pragma unroll 2
+    for (int k = 0; k < w; ++k) {
+      const int col = __ldcs(cp + k * MV_SLICE);
+      const double a = __ldcs(vp + k * MV_SLICE);
+      const double* xp = x + col;
+#pragma unroll
+      for (int c = 0; c < C; ++c) acc[c] = fma(a, __ldg(xp + c * ld), acc[c]);
+    }
+    if (row < nrows) {
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        y[c * ld + row] = acc[c];
+        if (DOT) dot[c] = fma(acc[c], __ldg(&x[c * ld + row]), dot[c]);
+      }
+    }
+  }
+  if (DOT) {
+    grid_reduce_sum<C>(dot, partials, counter, [&](double(&t)[C]) {
+#pragma unroll
+      for (int c = 0; c < C; ++c) scal[SC(dot_slot, c)] = t[c];
+    });
+  }
+}
+
+// ------------------------------------------------------------------ PCG pieces
+// r = P (b - mean - A x), p = z = D^-1 r ; sums r.z and b.D^-1.b over the free dofs.  b is interleaved [n,C].
+template <int C>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_init_soa(int64_t n, int64_t ld, const double* __restrict__ b, const double* __restrict__ q, const double* __restrict__ dinv,
+           const uint16_t* __restrict__ mask, double* __restrict__ r, double* __restrict__ p, double* __restrict__ partials,
+           unsigned* __restrict__ counter, double* __restrict__ scal, double inv_nglobal, int project_mean) {
+  double acc[2 * C];
+#pragma unroll
+  for (int c = 0; c < 2 * C; ++c) acc[c] = 0.0;
+  double mean[C];
+#pragma unroll
+  for (int c = 0; c < C; ++c) mean[c] = project_mean ? scal[SC(S_SUM, c)] * inv_nglobal : 0.0;
+  VERTEX_LOOP(v, n) {
+    const double di = __ldg(&dinv[v]);
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const bool fix = fixed_dof<C>(mask, v, c);
+      const double bb = b ? (b[v * C + c] - mean[c]) : 0.0;
+      const double rr = fix ? 0.0 : bb - q[c * ld + v];
+      const double zz = di * rr;
+      r[c * ld + v] = rr;
+      p[c * ld + v] = zz;
+      acc[c] = fma(rr, zz, acc[c]);
+      acc[C + c] = fix ? acc[C + c] : fma(bb * di, bb, acc[C + c]);
+    }
+  }
+  grid_reduce_sum<2 * C>(acc, partials, counter, [&](double(&t)[2 * C]) {
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      scal[SC(S_RZ, c)] = t[c];
+      scal[SC(S_BB, c)] = t[C + c];
+    }
+  });
+}
+
+__global__ void k_setup_soa(int C, double rtol, double atol, double* __restrict__ scal, int* __restrict__ flags) {
+  bool all = true;
+  for (int c = 0; c < C; ++c) {
+    const double rz = scal[SC(S_RZ, c)], bb = scal[SC(S_BB, c)];
+    const double ref = fmax(rz, bb);
+    scal[SC(S_REF, c)] = ref;
+    const double thr = fmax(rtol * rtol * ref, atol * atol);
+    scal[SC(S_THR, c)] = thr;
+    all = all && (rz <= thr);
+  }
+  flags[0] = all ? 1 : 0;
+  flags[1] = 0;
+  flags[2] = 0;
+}
+
+__device__ __forceinline__ void post_update_soa(int C, double* __restrict__ scal, int* __restrict__ flags) {
+  bool all = true;
+  for (int c = 0; c < C; ++c) {
+    const double rzn = scal[SC(S_RZNEW, c)], rz = scal[SC(S_RZ, c)];
+    scal[SC(S_BETA, c)] = rz > 0.0 ? rzn / rz : 0.0;
+    scal[SC(S_RZ, c)] = rzn;
+    all = all && (rzn <= scal[SC(S_THR, c)]);
+    if (!(rzn == rzn)) flags[2] = 1;  // NaN: breakdown
+  }
+  flags[1] += 1;
+  if (all || flags[2]) flags[0] = 1;
+}
+__global__ void k_post_update_soa(int C, double* __restrict__ scal, int* __restrict__ flags) {
+  if (flags[0]) return;
+  post_update_soa(C, scal, flags);
+}
+
+// x += alpha p ; r -= alpha q ; JACOBI: partial r.D^-1.r (and, single GPU, beta / convergence)
+template <int C, bool JACOBI, bool LOCAL_POST>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_update_soa(int64_t n, int64_t ld, const double* __restrict__ p, const double* __restrict__ q, const double* __restrict__ dinv,
+             const uint16_t* __restrict__ mask, double* __restrict__ x, double* __restrict__ r, int* __restrict__ flags,
+             double* __restrict__ partials, unsigned* __restrict__ counter, double* __restrict__ scal) {
+  if (flags[0]) return;
+  double alpha[C], acc[C];
+#pragma unroll
+  for (int c = 0; c < C; ++c) {
+    const double pq = scal[SC(S_PQ, c)], rz = scal[SC(S_RZ, c)];
+    alpha[c] = pq > 0.0 ? rz / pq : 0.0;
+    acc[c] = 0.0;
+  }
+  VERTEX_LOOP(v, n) {
+    const double di = JACOBI ? __ldg(&dinv[v]) : 0.0;
+    const unsigned mk = mask ? __ldg(&mask[v]) : 0u;
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int64_t i = c * ld + v;
+      const bool fix = (mk >> c) & 1u;
+      x[i] += alpha[c] * p[i];
+      const double rr = fix ? 0.0 : r[i] - alpha[c] * __ldcs(&q[i]);
+      r[i] = rr;
+      if (JACOBI) acc[c] = fma(rr * di, rr, acc[c]);
+    }
+  }
+  if (JACOBI) {
+    grid_reduce_sum<C>(acc, partials, counter, [&](double(&t)[C]) {
+#pragma unroll
+      for (int c = 0; c < C; ++c) scal[SC(S_RZNEW, c)] = t[c];
+      if (LOCAL_POST) post_update_soa(C, scal, flags);
+    });
+  }
+}
+
+// p = D^-1 r + beta p
+template <int C>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_dir_soa(int64_t n, int64_t ld, const double* __restrict__ r, const double* __restrict__ dinv, double* __restrict__ p,
+          const int* __restrict__ flags, const double* __restrict__ scal) {
+  if (flags[0]) return;
+  double beta[C];
+#pragma unroll
+  for (int c = 0; c < C; ++c) beta[c] = scal[SC(S_BETA, c)];
+  VERTEX_LOOP(v, n) {
+    const double di = __ldg(&dinv[v]);
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int64_t i = c * ld + v;
+      p[i] = fma(beta[c], p[i], di * __ldcs(&r[i]));   // r is zero at constrained dofs
+    }
+  }
+}
+
+// multigrid variant: r.z -> slot (POST: beta / convergence / iteration count)
+template <int C, int POST>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_dot_rz_soa(int64_t n, int64_t ld, const double* __restrict__ r, const double* __restrict__ z, int* __restrict__ flags,
+             double* __restrict__ partials, unsigned* __restrict__ counter, double* __restrict__ scal, int slot, int slot2) {
+  if (POST && flags[0]) return;
+  double acc[C];
+#pragma unroll
+  for (int c = 0; c < C; ++c) acc[c] = 0.0;
+  VERTEX_LOOP(v, n)
+#pragma unroll
+    for (int c = 0; c < C; ++c) acc[c] = fma(r[c * ld + v], z[c * ld + v], acc[c]);
+  grid_reduce_sum<C>(acc, partials, counter, [&](double(&t)[C]) {
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      scal[SC(slot, c)] = t[c];
+      if (slot2 >= 0) scal[SC(slot2, c)] = t[c];
+    }
+    if (POST == 1) post_update_soa(C, scal, flags);
+  });
+}
+// p = z + beta p  (first: p = z)
+template <int C>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_dir_z_soa(int64_t n, int64_t ld, const double* __restrict__ z, double* __restrict__ p, const int* __restrict__ flags,
+            const double* __restrict__ scal, int first) {
+  if (!first && flags[0]) return;
+  double beta[C];
+#pragma unroll
+  for (int c = 0; c < C; ++c) beta[c] = first ? 0.0 : scal[SC(S_BETA, c)];
+  VERTEX_LOOP(v, n)
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int64_t i = c * ld + v;
+      p[i] = first ? z[i] : fma(beta[c], p[i], z[i]);
+    }
+}
+
+template <int C>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_comp_sum_aos(int64_t n, const double* __restrict__ x, double* __restrict__ partials, unsigned* __restrict__ counter,
+               double* __restrict__ scal) {
+  double acc[C];
+#pragma unroll
+  for (int c = 0; c < C; ++c) acc[c] = 0.0;
+  VERTEX_LOOP(v, n)
+#pragma unroll
+    for (int c = 0; c < C; ++c) acc[c] += x[v * C + c];
+  grid_reduce_sum<C>(acc, partials, counter, [&](double(&t)[C]) {
+#pragma unroll
+    for (int c = 0; c < C; ++c) scal[SC(S_SUM, c)] = t[c];
+  });
+}
+template <int C>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_sub_mean_aos(int64_t n, double* __restrict__ x, const double* __restrict__ scal, double inv_nglobal) {
+  const int64_t ne = n * C;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < ne; i += (int64_t)gridDim.x * blockDim.x)
+    x[i] -= scal[SC(S_SUM, (int)(i % C))] * inv_nglobal;
+}
+
+}  // namespace mv
+
+namespace mv {
+
+template <int C>
+static int spmv_soa_launch(mv_mesh* m, const double* val, const double* x, double* y, int64_t ld, bool dot) {
+  const Sell& p = m->pat;
+  const int grid = grid_for(p.nslices * MV_SLICE, 8);
+  if (dot)
+    MV_L k_spmv_soa<C, true><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, p.nrows, p.slice_ptr, p.cols, val, x, ld, y, m->pcg.flags,
+                                                         m->red.partials, m->red.counter, m->pcg.scal, S_PQ);
+  else
+    MV_L k_spmv_soa<C, false><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, p.nrows, p.slice_ptr, p.cols, val, x, ld, y, nullptr, nullptr,
+                                                          nullptr, nullptr, 0);
+  MV_KERNEL_CHECK();
+  return MV_OK;
+}
+
+template <int C>
+int pcg_soa(mv_mesh* m, const double* val, const double* dinv, const double* rhs, double* x, const uint16_t* mask, double rtol,
+            double atol, int maxit, int project_mean, int* iters, double* relres, Amg* pc) {
+  MV_CHECK(ensure_pcg_workspace(m));
+  PcgWork& w = m->pcg;
+  const int64_t n = m->Vown, ld = m->V;
+  const bool dist = comm_active();
+  int64_t nglobal = n;
+  if (dist) {
+    double hn = (double)n;
+    MV_CUDA(cudaMemcpyAsync(w.scal + SC(S_SUM, 15), &hn, sizeof(double), cudaMemcpyHostToDevice, g_stream));
+    MV_CHECK(allreduce_sum_dev(w.scal + SC(S_SUM, 15), 1));
+    MV_CUDA(cudaMemcpyAsync(&hn, w.scal + SC(S_SUM, 15), sizeof(double), cudaMemcpyDeviceToHost, g_stream));
+    MV_CUDA(cudaStreamSynchronize(g_stream));
+    nglobal = (int64_t)(hn + 0.5);
+  }
+  const double inv_ng = 1.0 / (double)nglobal;
+  const int gv = grid_for(n);
+  if (project_mean && rhs) {
+    MV_L k_comp_sum_aos<C><<<gv, MV_BLOCK, 0, g_stream>>>(n, rhs, m->red.partials, m->red.counter, w.scal);
+    MV_KERNEL_CHECK();
+    if (dist) MV_CHECK(allreduce_sum_dev(w.scal + SC(S_SUM, 0), C));
+  }
+  // initial guess -> component-major, initial residual
+  double* xs = C == 1 ? x : w.xs;   // one component: the two layouts coincide
+  if (C > 1) MV_L k_aos_to_soa<C><<<grid_for(n), MV_BLOCK, 0, g_stream>>>(n, x, xs, ld);
+  if (dist) MV_CHECK(halo_exchange_soa(m->halo, n, C, xs, ld));
+  MV_CHECK(spmv_soa_launch<C>(m, val, xs, w.q, ld, false));
+  MV_L k_init_soa<C><<<gv, MV_BLOCK, 0, g_stream>>>(n, ld, rhs, w.q, dinv, mask, w.r, w.p, m->red.partials, m->red.counter, w.scal,
+                                               inv_ng, project_mean && rhs ? 1 : 0);
+  MV_KERNEL_CHECK();
+  if (dist) {
+    MV_CHECK(allreduce_sum_dev(w.scal + SC(S_RZ, 0), C));
+    MV_CHECK(allreduce_sum_dev(w.scal + SC(S_BB, 0), C));
+  }
+  if (pc) {
+    // z0 = M^-1 r0 by one V-cycle; reference norm r0.z0
+    MV_CHECK(amg_ensure_work(pc, C));
+    MV_CHECK(amg_apply(m, pc, C, w.r, pc->z, nullptr));
+    MV_L k_dot_rz_soa<C, 0><<<gv, MV_BLOCK, 0, g_stream>>>(n, ld, w.r, pc->z, w.flags, m->red.partials, m->red.counter, w.scal, S_RZ, S_BB);
+    if (dist) {
+      MV_CHECK(allreduce_sum_dev(w.scal + SC(S_RZ, 0), C));
+      MV_CHECK(allreduce_sum_dev(w.scal + SC(S_BB, 0), C));
+    }
+    MV_L k_dir_z_soa<C><<<gv, MV_BLOCK, 0, g_stream>>>(n, ld, pc->z, w.p, w.flags, w.scal, 1);
+    MV_KERNEL_CHECK();
+  }
+  MV_L k_setup_soa<<<1, 1, 0, g_stream>>>(C, rtol, atol, w.scal, w.flags);
+  MV_KERNEL_CHECK();
+
+  int it = 0, batch = pc ? 4 : 8;
+  w.h_flags[0] = 0;
+  while (true) {
+    MV_CUDA(cudaMemcpyAsync(w.h_flags, w.flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, g_stream));
+    MV_CUDA(cudaStreamSynchronize(g_stream));
+    if (g_prof.used) prof_drain();
+    if (w.h_flags[0] || it >= maxit) break;
+    const int nb = batch < maxit - it ? batch : maxit - it;
+    for (int k = 0; k < nb; ++k) {
+      if (dist) MV_CHECK(halo_exchange_soa(m->halo, n, C, w.p, ld));
+      const int pslot = prof_begin(C);
+      MV_CHECK(spmv_soa_launch<C>(m, val, w.p, w.q, ld, true));
+      prof_end(pslot);
+      if (dist) MV_CHECK(allreduce_sum_dev(w.scal + SC(S_PQ, 0), C));
+      if (pc) {
+        MV_L k_update_soa<C, false, false><<<gv, MV_BLOCK, 0, g_stream>>>(n, ld, w.p, w.q, dinv, mask, xs, w.r, w.flags, m->red.partials,
+                                                                     m->red.counter, w.scal);
+        MV_CHECK(amg_apply(m, pc, C, w.r, pc->z, w.flags));
+        if (dist) {
+          MV_L k_dot_rz_soa<C, 2><<<gv, MV_BLOCK, 0, g_stream>>>(n, ld, w.r, pc->z, w.flags, m->red.partials, m->red.counter, w.scal,
+                                                            S_RZNEW, -1);
+          MV_CHECK(allreduce_sum_dev(w.scal + SC(S_RZNEW, 0), C));
+          MV_L k_post_update_soa<<<1, 1, 0, g_stream>>>(C, w.scal, w.flags);
+        } else {
+          MV_L k_dot_rz_soa<C, 1><<<gv, MV_BLOCK, 0, g_stream>>>(n, ld, w.r, pc->z, w.flags, m->red.partials, m->red.counter, w.scal,
+                                                            S_RZNEW, -1);
+        }
+        MV_L k_dir_z_soa<C><<<gv, MV_BLOCK, 0, g_stream>>>(n, ld, pc->z, w.p, w.flags, w.scal, 0);
+      } else {
+        if (dist) {
+          MV_L k_update_soa<C, true, false><<<gv, MV_BLOCK, 0, g_stream>>>(n, ld, w.p, w.q, dinv, mask, xs, w.r, w.flags, m->red.partials,
+                                                                      m->red.counter, w.scal);
+          MV_CHECK(allreduce_sum_dev(w.scal + SC(S_RZNEW, 0), C));
+          MV_L k_post_update_soa<<<1, 1, 0, g_stream>>>(C, w.scal, w.flags);
+        } else {
+          MV_L k_update_soa<C, true, true><<<gv, MV_BLOCK, 0, g_stream>>>(n, ld, w.p, w.q, dinv, mask, xs, w.r, w.flags, m->red.partials,
+                                                                     m->red.counter, w.scal);
+        }
+        MV_L k_dir_soa<C><<<gv, MV_BLOCK, 0, g_stream>>>(n, ld, w.r, dinv, w.p, w.flags, w.scal);
+      }
+    }
+    MV_KERNEL_CHECK();
+    it += nb;
+    if (batch < (pc ? 16 : 64)) batch *= 2;
+  }
+  const int done = w.h_flags[0], niter = w.h_flags[1], breakdown = w.h_flags[2];
+  g_prof.pcg_iters[C & 15] += niter;
+  if (C > 1) MV_L k_soa_to_aos<C><<<grid_for(n), MV_BLOCK, 0, g_stream>>>(n, xs, ld, x);
+  if (project_mean) {
+    MV_L k_comp_sum_aos<C><<<gv, MV_BLOCK, 0, g_stream>>>(n, x, m->red.partials, m->red.counter, w.scal);
+    if (dist) MV_CHECK(allreduce_sum_dev(w.scal + SC(S_SUM, 0), C));
+    MV_L k_sub_mean_aos<C><<<grid_for(n * C), MV_BLOCK, 0, g_stream>>>(n, x, w.scal, inv_ng);
+  }
+  MV_KERNEL_CHECK();
+  if (iters) *iters = niter;
+  if (relres) {
+    MV_CUDA(cudaMemcpyAsync(w.h_scal, w.scal, S_NSLOTS * 16 * sizeof(double), cudaMemcpyDeviceToHost, g_stream));
+    MV_CUDA(cudaStreamSynchronize(g_stream));
+    for (int c = 0; c < C; ++c) {
+      const double ref = w.h_scal[SC(S_REF, c)];
+      relres[c] = ref > 0.0 ? sqrt(w.h_scal[SC(S_RZ, c)] / ref) : 0.0;
+    }
+  }
+  if (breakdown) {
+    set_error("pcg: breakdown (NaN) after %d iterations", niter);
+    return MV_ERR_NOT_CONVERGED;
+  }
+  if (!done) {
+    set_error("pcg: not converged in %d iterations", maxit);
+    return MV_ERR_NOT_CONVERGED;
+  }
+  return MV_OK;
+}
+
+int pcg_solve_soa(mv_mesh* m, int ncomp, const double* val, const double* dinv, const double* rhs, double* x, const uint16_t* mask,
+                  double rtol, double atol, int maxit, int project_mean, int* iters, double* relres, Amg* pc) {
+  switch (ncomp) {
+    case 1: return pcg_soa<1>(m, val, dinv, rhs, x, mask, rtol, atol, maxit, project_mean, iters, relres, pc);
+    case 2: return pcg_soa<2>(m, val, dinv, rhs, x, mask, rtol, atol, maxit, project_mean, iters, relres, pc);
+    case 3: return pcg_soa<3>(m, val, dinv, rhs, x, mask, rtol, atol, maxit, project_mean, iters, relres, pc);
+    case 4: return pcg_soa<4>(m, val, dinv, rhs, x, mask, rtol, atol, maxit, project_mean, iters, relres, pc);
+    case 9: return pcg_soa<9>(m, val, dinv, rhs, x, mask, rtol, atol, maxit, project_mean, iters, relres, pc);
+  }
+  set_error("pcg: unsupported ncomp %d (1,2,3,4,9)", ncomp);
+  return MV_ERR_UNSUPPORTED;
+}
+
+}  // namespace mv
