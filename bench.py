@@ -306,6 +306,7 @@ def run_ours(args):
                            "residual_after_timed_steps": residuals[-1]},
                 "roofline": roofline,
                 "step_model": {"bytes_per_step": step_bytes, "GBs": step_gbs, "frac_of_peak": step_gbs / (peak * world)},
+                "spmv_avg_ms_by_rhs": {str(c): spmv_ms[c] / spmv_cnt[c] for c in range(16) if spmv_cnt[c] > 0},
                 "gpu_launches": int(launches.value), "clocks": clocks, "e2e": e2e}
         if world == 1 and not args.no_cpu_baseline:
             r = cpu_relax(args.cpu_n, args.cpu_steps, 1, args.inner_rtol)

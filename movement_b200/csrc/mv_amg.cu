@@ -55,7 +55,10 @@ Amg::~Amg() {
     dev_free(L.x0);
     if (l > 0) dev_free(L.b);
     dev_free(L.x1); dev_free(L.r); dev_free(L.d0); dev_free(L.d1);
+    if (L.owns_halo) { dev_free(L.halo.send_idx); dev_free(L.halo.send_buf); }
+    dev_free(L.gid);
   }
+  dev_free(cglob);
   dev_free(mask_copy);
   dev_free(coarse_inv);
   dev_free(z);
@@ -448,6 +451,32 @@ __global__ void k_pow_scale(int64_t n, const double* __restrict__ y, const doubl
   GRID_STRIDE(i, n) x[i] = y[i] * s;
 }
 
+int amg_exchange_prolongator(const Halo& H, int64_t n, int64_t ntot, const Csr& P, const std::vector<int64_t>& nc_all,
+                             const std::vector<int64_t>& coff_all, Csr& Pext, Halo& Hc, int64_t* ntot_c, int64_t** gid_c);
+int amg_dense_gather(const AmgLevel& L, double shift, double* a);
+
+// set-up decisions must be identical on every rank: reduce the local status / flags
+static int global_max_int(int v, int* out) {
+  double h = (double)v;
+  MV_CHECK(allreduce_host(&h, 1, 1));
+  *out = (int)h;
+  return MV_OK;
+}
+static int global_sum_i64(int64_t v, int64_t* out) {
+  double h = (double)v;
+  MV_CHECK(allreduce_host(&h, 1, 0));
+  *out = (int64_t)(h + 0.5);
+  return MV_OK;
+}
+// st: local status of a set-up stage; returns the first non-OK status of any rank (as UNSUPPORTED if remote)
+static int agree(int st) {
+  if (!comm_active()) return st;
+  int g = 0;
+  if (global_max_int(st == MV_OK ? 0 : 1, &g) != MV_OK) return MV_ERR_COMM;
+  if (g && st == MV_OK) { set_error("amg: set-up stage failed on another rank"); return MV_ERR_UNSUPPORTED; }
+  return st;
+}
+
 static int estimate_rho(mv_mesh* m, const AmgLevel& L, double* rho) {
   double *x = nullptr, *y = nullptr, *out = nullptr;
   MV_CHECK(dev_alloc(&x, L.ntot));
@@ -458,9 +487,10 @@ static int estimate_rho(mv_mesh* m, const AmgLevel& L, double* rho) {
   MV_L k_pow_init<<<grid, MV_BLOCK, 0, g_stream>>>(L.n, L.dinv, x);
   const int iters = 15;
   for (int k = 0; k < iters; ++k) {
-    // TODO(multi-GPU): halo exchange of x and allreduce of out
+    if (comm_active()) MV_CHECK(halo_exchange_soa(L.halo, L.n, 1, x, L.ntot));
     MV_L k_pow_step<<<grid, MV_BLOCK, 0, g_stream>>>(L.n, L.pat.slice_ptr, L.pat.cols, L.val, L.pat.row_nnz, L.dinv, x, y,
                                                 m->red.partials, m->red.counter, out);
+    if (comm_active()) MV_CHECK(allreduce_sum_dev(out, 2));
     if (k + 1 < iters) MV_L k_pow_scale<<<grid, MV_BLOCK, 0, g_stream>>>(L.n, y, out, x);
   }
   MV_KERNEL_CHECK();
@@ -508,7 +538,7 @@ __global__ void k_mean_diag(int64_t n, const double* __restrict__ diag, double* 
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     double s = 0.0;
     for (int64_t i = 0; i < n; ++i) s += fabs(diag[i]);
-    *out = s / (double)(n > 0 ? n : 1);
+    *out = s;
   }
 }
 
@@ -606,14 +636,21 @@ static int two_phase(Csr& c, Count count, Fill fill, int* err_flag) {
   return MV_OK;
 }
 
-// Build level l+1 from level l.  Returns MV_ERR_UNSUPPORTED when coarsening should stop here.
+// Build level l+1 from level l.  Returns MV_ERR_UNSUPPORTED when coarsening should stop here (same answer on every rank).
 static int coarsen(mv_mesh* m, Amg* a, double theta, double* diag) {
   AmgLevel& L = a->lv.back();
+  const bool dist = comm_active();
   Graph g{L.n, L.pat.slice_ptr, L.pat.cols, L.val, L.pat.row_nnz, diag, L.mask, theta * theta};
   int* agg = nullptr;
   int64_t nc = 0;
-  MV_CHECK(aggregate(m, g, &agg, &nc));
-  if (nc <= 0 || nc * 10 > L.n * 8) {   // stalled
+  int st = agree(aggregate(m, g, &agg, &nc));
+  if (st != MV_OK) { dev_free(agg); return st; }
+  std::vector<int64_t> nc_all, coff_all;
+  MV_CHECK(allgather_i64(nc, nc_all));
+  coff_all.assign(nc_all.size() + 1, 0);
+  for (size_t r = 0; r < nc_all.size(); ++r) coff_all[r + 1] = coff_all[r] + nc_all[r];
+  const int64_t ncg = coff_all.back();
+  if (ncg <= 0 || ncg * 10 > L.nglobal * 8) {   // stalled
     dev_free(agg);
     return MV_ERR_UNSUPPORTED;
   }
@@ -622,28 +659,36 @@ static int coarsen(mv_mesh* m, Amg* a, double theta, double* diag) {
   MV_CUDA(cudaMemsetAsync(err, 0, sizeof(int), g_stream));
   const int grid = grid_for(L.n);
   const double omega = 4.0 / (3.0 * L.rho);
-  Csr P, R, AP, Ac;
-  int st = MV_OK;
+  Csr P, R, Pext, AP, Ac;
+  AmgLevel N;
   P.nrows = L.n; P.ncols = nc;
   st = two_phase(P, [&](int64_t* cnt) { MV_L k_prolongator<false><<<grid, MV_BLOCK, 0, g_stream>>>(g, agg, omega, cnt, nullptr, nullptr, err); },
                  [&]() { MV_L k_prolongator<true><<<grid, MV_BLOCK, 0, g_stream>>>(g, agg, omega, P.ptr, P.col, P.val, err); }, err);
   dev_free(agg);
   if (st == MV_OK) st = csr_transpose(P, R);
+  st = agree(st);
+  int64_t ntot_c = nc;
+  if (st == MV_OK && dist) {
+    st = amg_exchange_prolongator(L.halo, L.n, L.ntot, P, nc_all, coff_all, Pext, N.halo, &ntot_c, &N.gid);
+    N.owns_halo = true;
+    st = agree(st);
+  }
+  const Csr& B = dist ? Pext : P;
   if (st == MV_OK) {
-    AP.nrows = L.n; AP.ncols = nc;
+    AP.nrows = L.n; AP.ncols = ntot_c;
     st = two_phase(AP,
                    [&](int64_t* cnt) {
                      MV_L k_spgemm_sell_csr<false><<<grid, MV_BLOCK, 0, g_stream>>>(L.n, L.pat.slice_ptr, L.pat.cols, L.val, L.pat.row_nnz, L.mask,
-                                                                             P.ptr, P.col, P.val, P.nrows, cnt, nullptr, nullptr, err);
+                                                                             B.ptr, B.col, B.val, B.nrows, cnt, nullptr, nullptr, err);
                    },
                    [&]() {
                      MV_L k_spgemm_sell_csr<true><<<grid, MV_BLOCK, 0, g_stream>>>(L.n, L.pat.slice_ptr, L.pat.cols, L.val, L.pat.row_nnz, L.mask,
-                                                                            P.ptr, P.col, P.val, P.nrows, AP.ptr, AP.col, AP.val, err);
+                                                                            B.ptr, B.col, B.val, B.nrows, AP.ptr, AP.col, AP.val, err);
                    },
                    err);
   }
   if (st == MV_OK) {
-    Ac.nrows = nc; Ac.ncols = nc;
+    Ac.nrows = nc; Ac.ncols = ntot_c;
     const int gc = grid_for(nc);
     st = two_phase(Ac,
                    [&](int64_t* cnt) {
@@ -657,8 +702,8 @@ static int coarsen(mv_mesh* m, Amg* a, double theta, double* diag) {
                    err);
   }
   AP.release();
+  Pext.release();
   dev_free(err);
-  AmgLevel N;
   if (st == MV_OK) st = csr_to_sell(P, L.P, &L.Pval);
   if (st == MV_OK) st = csr_to_sell(R, L.R, &L.Rval);
   if (st == MV_OK) {
@@ -668,12 +713,19 @@ static int coarsen(mv_mesh* m, Amg* a, double theta, double* diag) {
     N.owns_A = true;
   }
   P.release(); R.release(); Ac.release();
+  st = agree(st);
   if (st != MV_OK) {
     sell_free(L.P); sell_free(L.R); dev_free(L.Pval); dev_free(L.Rval);
     L.P = Sell(); L.R = Sell();
+    if (N.owns_A) { sell_free(N.pat); double* v = const_cast<double*>(N.val); dev_free(v); }
+    if (N.owns_halo) { dev_free(N.halo.send_idx); dev_free(N.halo.send_buf); }
+    dev_free(N.gid);
     return st;
   }
-  N.n = N.ntot = nc;
+  N.n = nc;
+  N.ntot = ntot_c;
+  N.nglobal = ncg;
+  N.goff = coff_all[comm_rank()];
   a->lv.push_back(N);
   return MV_OK;
 }
@@ -694,6 +746,15 @@ static int amg_build(mv_mesh* m, int op, const uint16_t* mask_bit0, int singular
   L0.n = m->Vown; L0.ntot = m->V;
   L0.pat = m->pat; L0.val = val; L0.owns_A = false;
   L0.mask = mask_bit0;
+  L0.halo = m->halo;          // borrowed (device lists belong to the mesh)
+  L0.owns_halo = false;
+  L0.nglobal = L0.n;
+  if (comm_active()) {
+    MV_CHECK(global_sum_i64(L0.n, &L0.nglobal));
+    std::vector<int64_t> all;
+    MV_CHECK(allgather_i64(L0.n, all));
+    for (int r = 0; r < comm_rank(); ++r) L0.goff += all[r];
+  }
   a->lv.push_back(L0);
   int st = MV_OK;
   while (true) {
@@ -704,17 +765,20 @@ static int amg_build(mv_mesh* m, int op, const uint16_t* mask_bit0, int singular
     if ((st = dev_alloc(&L.dinv, L.n)) != MV_OK) break;
     MV_L k_amg_diag<<<grid_for(L.n), MV_BLOCK, 0, g_stream>>>(L.n, L.pat.slice_ptr, L.pat.cols, L.val, L.pat.row_nnz, L.mask, diag, L.dinv);
     if ((st = estimate_rho(m, L, &L.rho)) != MV_OK) { dev_free(diag); break; }
-    const bool last = L.n <= dense_max || (int)a->lv.size() >= MV_AMG_MAX_LEVELS;
+    const bool last = L.nglobal <= dense_max || (int)a->lv.size() >= MV_AMG_MAX_LEVELS;
     int cs = last ? MV_ERR_UNSUPPORTED : coarsen(m, a, theta, diag);
     if (cs == MV_OK) { dev_free(diag); continue; }
     if (cs != MV_ERR_UNSUPPORTED) { st = cs; dev_free(diag); break; }
     // this level is the coarsest
     AmgLevel& Lc = a->lv.back();
-    a->nc = Lc.n;
-    if (Lc.n <= MV_AMG_DENSE && Lc.mask == nullptr) {
+    const bool dist = comm_active();
+    const int64_t N = Lc.nglobal;
+    a->nc = N;
+    // gathered dense solve needs the global column ids, which exist from level 1 on
+    if (N <= MV_AMG_DENSE && Lc.mask == nullptr && (!dist || Lc.gid != nullptr)) {
       double* shift = nullptr;
       int* err = nullptr;
-      if ((st = dev_alloc(&a->coarse_inv, (size_t)Lc.n * Lc.n)) != MV_OK) break;
+      if ((st = dev_alloc(&a->coarse_inv, (size_t)N * N)) != MV_OK) break;
       if ((st = dev_alloc(&shift, 1)) != MV_OK) break;
       if ((st = dev_alloc(&err, 1)) != MV_OK) break;
       cudaMemsetAsync(err, 0, sizeof(int), g_stream);
@@ -722,9 +786,14 @@ static int amg_build(mv_mesh* m, int op, const uint16_t* mask_bit0, int singular
       double hs = 0.0;
       cudaMemcpyAsync(&hs, shift, sizeof(double), cudaMemcpyDeviceToHost, g_stream);
       cudaStreamSynchronize(g_stream);
-      hs = singular ? hs / (double)Lc.n : 0.0;   // A + s 1 1^T: exact pseudo-inverse action on vectors orthogonal to 1
-      MV_L k_dense_fill<<<grid_for(Lc.n), MV_BLOCK, 0, g_stream>>>(Lc.n, Lc.pat.slice_ptr, Lc.pat.cols, Lc.val, Lc.pat.row_nnz, hs, a->coarse_inv);
-      MV_L k_gauss_jordan<<<1, 1024, 0, g_stream>>>((int)Lc.n, a->coarse_inv, err);
+      if (dist && (st = allreduce_host(&hs, 1, 0)) != MV_OK) break;
+      hs = singular ? hs / ((double)N * (double)N) : 0.0;   // A + s 1 1^T: exact pseudo-inverse action on vectors orthogonal to 1
+      if (dist) {
+        if ((st = amg_dense_gather(Lc, hs, a->coarse_inv)) != MV_OK) break;
+      } else {
+        MV_L k_dense_fill<<<grid_for(Lc.n), MV_BLOCK, 0, g_stream>>>(Lc.n, Lc.pat.slice_ptr, Lc.pat.cols, Lc.val, Lc.pat.row_nnz, hs, a->coarse_inv);
+      }
+      MV_L k_gauss_jordan<<<1, 1024, 0, g_stream>>>((int)N, a->coarse_inv, err);
       int herr = 0;
       cudaMemcpyAsync(&herr, err, sizeof(int), cudaMemcpyDeviceToHost, g_stream);
       cudaStreamSynchronize(g_stream);
@@ -744,10 +813,12 @@ static int amg_build(mv_mesh* m, int op, const uint16_t* mask_bit0, int singular
   if (st == MV_OK && cudaGetLastError() != cudaSuccess) { set_error("amg: CUDA error during set-up"); st = MV_ERR_CUDA; }
   if (st != MV_OK) { delete a; return st; }
   if (getenv("MV_AMG_VERBOSE")) {
-    fprintf(stderr, "[mv amg] op %d: %zu levels, set-up %.1f ms, singular %d\n", op, a->lv.size(), ms, singular);
+    fprintf(stderr, "[mv amg] rank %d op %d: %zu levels, set-up %.1f ms, singular %d, dense coarse %d\n", comm_rank(), op, a->lv.size(), ms,
+            singular, a->coarse_inv ? 1 : 0);
     for (size_t l = 0; l < a->lv.size(); ++l)
-      fprintf(stderr, "   level %zu: n %lld nnz %lld maxw %d rho %.3f degree %d\n", l, (long long)a->lv[l].n, (long long)a->lv[l].pat.nnz,
-              a->lv[l].pat.maxw, a->lv[l].rho, a->lv[l].degree);
+      fprintf(stderr, "   level %zu: n %lld (+%lld ghosts, global %lld) nnz %lld maxw %d rho %.3f degree %d\n", l, (long long)a->lv[l].n,
+              (long long)(a->lv[l].ntot - a->lv[l].n), (long long)a->lv[l].nglobal, (long long)a->lv[l].pat.nnz, a->lv[l].pat.maxw,
+              a->lv[l].rho, a->lv[l].degree);
   }
   *out = a;
   return MV_OK;
@@ -756,8 +827,10 @@ static int amg_build(mv_mesh* m, int op, const uint16_t* mask_bit0, int singular
 int amg_get(mv_mesh* m, int op, const uint16_t* mask, int ncomp, int singular_hint, Amg** out) {
   *out = nullptr;
   if (m->pc_kind != MV_PC_AMG || op == MV_OP_MASS) return MV_OK;
-  if (comm_active()) return MV_OK;   // rank-local hierarchy with halo exchange: not wired yet -> Jacobi
-  if (m->Vown < 64) return MV_OK;
+  const bool dist = comm_active();
+  int64_t vglobal = m->Vown;
+  if (dist) MV_CHECK(global_sum_i64(m->Vown, &vglobal));
+  if (vglobal < 64) return MV_OK;
   unsigned long long hsig[3] = {0, 0, 0};
   const int allbits = (1 << ncomp) - 1;
   if (mask) {
@@ -769,15 +842,25 @@ int amg_get(mv_mesh* m, int op, const uint16_t* mask, int ncomp, int singular_hi
     MV_CUDA(cudaMemcpyAsync(hsig, sig, sizeof(hsig), cudaMemcpyDeviceToHost, g_stream));
     MV_CUDA(cudaStreamSynchronize(g_stream));
     dev_free(sig);
-    if (hsig[2]) return MV_OK;   // components constrained on different vertex sets: one hierarchy cannot serve them
   }
-  const bool constrained = hsig[1] > 0;
+  double gl[2] = {(double)hsig[1], (double)hsig[2]};
+  if (dist) MV_CHECK(allreduce_host(gl, 2, 0));
+  if (gl[1] > 0) return MV_OK;   // components constrained on different vertex sets: one hierarchy cannot serve them
+  const bool constrained = gl[0] > 0;
   const int singular = (op == MV_OP_STIFFNESS && !constrained) ? 1 : 0;
   (void)singular_hint;
+  Amg* hit = nullptr;
   for (Amg* a : m->amg)
-    if (a->op == op && a->mask_hash == hsig[0] && a->singular == singular) { *out = a; return MV_OK; }
+    if (a->op == op && a->mask_hash == hsig[0] && a->singular == singular) hit = a;
+  int miss = hit ? 0 : 1;
+  if (dist) MV_CHECK(global_max_int(miss, &miss));   // a change of the constrained set on any rank rebuilds everywhere
+  if (!miss) { *out = hit; return MV_OK; }
+  if (hit) {
+    for (size_t k = 0; k < m->amg.size(); ++k)
+      if (m->amg[k] == hit) { delete hit; m->amg.erase(m->amg.begin() + k); break; }
+  }
   uint16_t* mcopy = nullptr;
-  if (constrained) {
+  if (constrained && hsig[1] > 0) {
     MV_CHECK(dev_alloc(&mcopy, m->Vown));
     MV_L k_mask_copy<<<grid_for(m->Vown), MV_BLOCK, 0, g_stream>>>(m->Vown, mask, allbits, mcopy);
     MV_KERNEL_CHECK();

@@ -30,13 +30,23 @@ __device__ __forceinline__ void sell_dot(const int64_t* __restrict__ slice_ptr, 
   const double* vp = val + base + lane;
 #pragma unroll
   for (int c = 0; c < C; ++c) acc[c] = 0.0;
-#pragma unroll 4
-  for (int k = 0; k < w; ++k) {
-    const int col = __ldcs(cp + k * MV_SLICE);
-    const double a = __ldcs(vp + k * MV_SLICE);
-    const double* xp = x + col;
+  // column indices of a chunk first, then the gathers (breaks the index -> gather latency chain)
+  constexpr int KB = 8;
+  for (int k0 = 0; k0 < w; k0 += KB) {
+    int col[KB];
+    double a[KB];
 #pragma unroll
-    for (int c = 0; c < C; ++c) acc[c] = fma(a, __ldg(xp + c * ldx), acc[c]);
+    for (int j = 0; j < KB; ++j) {
+      const bool in = k0 + j < w;
+      col[j] = in ? __ldcs(cp + (k0 + j) * MV_SLICE) : 0;
+      a[j] = in ? __ldcs(vp + (k0 + j) * MV_SLICE) : 0.0;
+    }
+#pragma unroll
+    for (int j = 0; j < KB; ++j) {
+      const double* xp = x + col[j];
+#pragma unroll
+      for (int c = 0; c < C; ++c) acc[c] = fma(a[j], __ldg(xp + c * ldx), acc[c]);
+    }
   }
 }
 
@@ -151,11 +161,12 @@ k_sell_apply(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_p
   }
 }
 
-// x = Ainv b on the coarsest level: one warp per row, lanes stride the columns, fixed-order shuffle sum
+// x = Ainv b on the coarsest level: one warp per owned row (global row goff + row), lanes stride the N
+// columns, fixed-order shuffle sum.  Multi-GPU: b is the gathered right-hand side of all ranks.
 template <int C>
 __global__ void __launch_bounds__(MV_BLOCK)
-k_dense_apply(int n, int64_t ld, const double* __restrict__ inv, const double* __restrict__ b, double* __restrict__ x,
-              const int* __restrict__ done) {
+k_dense_apply(int n, int N, int64_t goff, const double* __restrict__ inv, const double* __restrict__ b, int64_t ldb,
+              double* __restrict__ x, int64_t ldx, const int* __restrict__ done) {
   if (done && *done) return;
   const int lane = threadIdx.x & 31;
   const int row = (int)((blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5);
@@ -163,16 +174,23 @@ k_dense_apply(int n, int64_t ld, const double* __restrict__ inv, const double* _
   double acc[C];
 #pragma unroll
   for (int c = 0; c < C; ++c) acc[c] = 0.0;
-  for (int j = lane; j < n; j += 32) {
-    const double a = inv[(size_t)row * n + j];
+  for (int j = lane; j < N; j += 32) {
+    const double a = inv[(size_t)(goff + row) * N + j];
 #pragma unroll
-    for (int c = 0; c < C; ++c) acc[c] = fma(a, b[c * ld + j], acc[c]);
+    for (int c = 0; c < C; ++c) acc[c] = fma(a, b[c * ldb + j], acc[c]);
   }
 #pragma unroll
   for (int c = 0; c < C; ++c) {
     const double t = warp_sum(acc[c]);
-    if (lane == 0) x[c * ld + row] = t;
+    if (lane == 0) x[c * ldx + row] = t;
   }
+}
+// own segment of the coarse right-hand side into the zeroed global vector [C][N]
+template <int C>
+__global__ void k_coarse_scatter(int n, int N, int64_t goff, const double* __restrict__ b, int64_t ld, double* __restrict__ bg) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+#pragma unroll
+    for (int c = 0; c < C; ++c) bg[(size_t)c * N + goff + i] = b[c * ld + i];
 }
 
 int amg_ensure_work(Amg* a, int C) {
@@ -199,6 +217,10 @@ int amg_ensure_work(Amg* a, int C) {
     }
     L.work_C = C;
   }
+  if (comm_active() && a->coarse_inv && a->z_C < C) {
+    dev_free(a->cglob);
+    MV_CHECK(dev_alloc(&a->cglob, (size_t)a->nc * C));
+  }
   if (a->z_C < C) {
     dev_free(a->z);
     MV_CHECK(dev_alloc(&a->z, (size_t)a->lv[0].ntot * C));
@@ -223,6 +245,7 @@ static int smooth(AmgLevel& L, const double* b, const double* xin, double* xout,
   double* dcur = deg > 1 ? L.d0 : nullptr;
   double* dnext = L.d1;
   const double* rin = b;
+  if (xin && comm_active()) MV_CHECK(halo_exchange_soa(L.halo, L.n, C, const_cast<double*>(xin), L.ntot));
   if (!xin) {
     MV_L k_smooth_zero<C><<<grid_for(L.n), MV_BLOCK, 0, g_stream>>>(L.n, L.ntot, b, L.dinv, 1.0 / theta, xout, dcur, done);
   } else {
@@ -234,7 +257,7 @@ static int smooth(AmgLevel& L, const double* b, const double* xin, double* xout,
   for (int k = 1; k < deg; ++k) {
     const double rho_n = 1.0 / (2.0 * sigma - rho_k);
     const bool last = k == deg - 1;
-    // TODO(multi-GPU): halo exchange of dcur
+    if (comm_active()) MV_CHECK(halo_exchange_soa(L.halo, L.n, C, dcur, L.ntot));
     MV_L k_smooth_next<C><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, L.n, L.ntot, p.slice_ptr, p.cols, L.val, dcur, dnext, rin, last ? nullptr : L.r,
                                                       L.dinv, rho_n * rho_k, 2.0 * rho_n / delta, xout, done);
     rin = L.r;
@@ -253,7 +276,7 @@ static int vcycle(mv_mesh* m, Amg* a, const double* rfine, double* z, const int*
     AmgLevel& L = a->lv[l];
     AmgLevel& N = a->lv[l + 1];
     MV_CHECK(smooth<C>(L, b, nullptr, L.x0, done));
-    // TODO(multi-GPU): halo exchange of L.x0
+    if (comm_active()) MV_CHECK(halo_exchange_soa(L.halo, L.n, C, L.x0, L.ntot));
     MV_L k_residual<C><<<slice_grid(L.pat), MV_BLOCK, 0, g_stream>>>(L.pat.nslices, L.n, L.ntot, L.pat.slice_ptr, L.pat.cols, L.val, b, L.x0, L.dinv,
                                                                 L.r, done);
     MV_L k_sell_apply<C, false><<<slice_grid(L.R), MV_BLOCK, 0, g_stream>>>(L.R.nslices, N.n, L.R.slice_ptr, L.R.cols, L.Rval, L.r, L.ntot, N.b, N.ntot, done);
@@ -263,7 +286,17 @@ static int vcycle(mv_mesh* m, Amg* a, const double* rfine, double* z, const int*
   double* xc = nl == 1 ? z : Lc.x0;
   if (a->coarse_inv) {
     const int64_t threads = (int64_t)Lc.n * 32;
-    MV_L k_dense_apply<C><<<(unsigned)((threads + MV_BLOCK - 1) / MV_BLOCK), MV_BLOCK, 0, g_stream>>>((int)Lc.n, Lc.ntot, a->coarse_inv, b, xc, done);
+    const unsigned blocks = (unsigned)((threads + MV_BLOCK - 1) / MV_BLOCK);
+    if (comm_active()) {
+      // gather the coarse right-hand side of all ranks (each entry is non-zero on one rank: exact sum)
+      const int N = (int)a->nc;
+      MV_CUDA(cudaMemsetAsync(a->cglob, 0, (size_t)N * C * sizeof(double), g_stream));
+      if (Lc.n) MV_L k_coarse_scatter<C><<<grid_for(Lc.n), MV_BLOCK, 0, g_stream>>>((int)Lc.n, N, Lc.goff, b, Lc.ntot, a->cglob);
+      MV_CHECK(allreduce_sum_dev(a->cglob, N * C));
+      if (Lc.n) MV_L k_dense_apply<C><<<blocks, MV_BLOCK, 0, g_stream>>>((int)Lc.n, N, Lc.goff, a->coarse_inv, a->cglob, N, xc, Lc.ntot, done);
+    } else {
+      MV_L k_dense_apply<C><<<blocks, MV_BLOCK, 0, g_stream>>>((int)Lc.n, (int)Lc.n, 0, a->coarse_inv, b, Lc.ntot, xc, Lc.ntot, done);
+    }
   } else {
     MV_CHECK(smooth<C>(Lc, b, nullptr, xc, done));
   }
@@ -273,8 +306,7 @@ static int vcycle(mv_mesh* m, Amg* a, const double* rfine, double* z, const int*
     AmgLevel& L = a->lv[l];
     MV_L k_sell_apply<C, true><<<slice_grid(L.P), MV_BLOCK, 0, g_stream>>>(L.P.nslices, L.n, L.P.slice_ptr, L.P.cols, L.Pval, xcoarse, a->lv[l + 1].ntot, L.x0, L.ntot, done);
     double* out = l == 0 ? z : L.x1;
-    // TODO(multi-GPU): halo exchange of L.x0
-    MV_CHECK(smooth<C>(L, l == 0 ? rfine : L.b, L.x0, out, done));
+    MV_CHECK(smooth<C>(L, l == 0 ? rfine : L.b, L.x0, out, done));   // (exchanges the ghosts of L.x0 first)
     xcoarse = out;
   }
   (void)m;

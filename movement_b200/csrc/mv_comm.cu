@@ -122,6 +122,46 @@ int halo_exchange(mv_mesh* m, int C, double* vec) {
   return MV_OK;
 }
 
+int comm_rank() { return g_rank; }
+
+// Host-visible small collectives for set-up code (sizes, offsets, flags): through a device scratch.
+int allreduce_host(double* h, int n, int op) {
+  if (!comm_active()) return MV_OK;
+  double* d = nullptr;
+  MV_CHECK(dev_alloc(&d, n));
+  MV_CUDA(cudaMemcpyAsync(d, h, n * sizeof(double), cudaMemcpyHostToDevice, g_stream));
+  int st = allreduce_dev(d, n, op);
+  if (st == MV_OK) {
+    MV_CUDA(cudaMemcpyAsync(h, d, n * sizeof(double), cudaMemcpyDeviceToHost, g_stream));
+    MV_CUDA(cudaStreamSynchronize(g_stream));
+  }
+  dev_free(d);
+  return st;
+}
+// all[r] = value of rank r (exact for |value| < 2^53): a zero-padded sum
+int allgather_i64(int64_t mine, std::vector<int64_t>& all) {
+  all.assign(g_nranks, 0);
+  all[g_rank] = mine;
+  if (!comm_active()) return MV_OK;
+  std::vector<double> h(g_nranks, 0.0);
+  h[g_rank] = (double)mine;
+  MV_CHECK(allreduce_host(h.data(), g_nranks, 0));
+  for (int r = 0; r < g_nranks; ++r) all[r] = (int64_t)(h[r] + (h[r] >= 0 ? 0.5 : -0.5));
+  return MV_OK;
+}
+// Neighbour exchange of raw device bytes: neighbour k gets sbuf[k] (sbytes[k]) and fills rbuf[k] (rbytes[k]).
+int neighbor_exchange_bytes(int nn, const int* ranks, const void* const* sbuf, const size_t* sbytes, void* const* rbuf,
+                            const size_t* rbytes) {
+  if (!comm_active() || nn == 0) return MV_OK;
+  MV_NCCL(g_nccl.GroupStart());
+  for (int k = 0; k < nn; ++k) {
+    if (sbytes[k] > 0) MV_NCCL(g_nccl.Send(sbuf[k], sbytes[k], ncclChar, ranks[k], g_comm, g_stream));
+    if (rbytes[k] > 0) MV_NCCL(g_nccl.Recv(rbuf[k], rbytes[k], ncclChar, ranks[k], g_comm, g_stream));
+  }
+  MV_NCCL(g_nccl.GroupEnd());
+  return MV_OK;
+}
+
 // component-major vectors ([C][ld]): one contiguous segment per component and neighbour, received in place
 __global__ void k_halo_pack_soa(int64_t nsend, int C, const int* __restrict__ idx, const double* __restrict__ vec, int64_t ld,
                                 double* __restrict__ buf) {

@@ -152,6 +152,12 @@ struct AmgLevel {
   Sell R;  double* Rval = nullptr;   // [n_coarse x n] = P^T
   double *x0 = nullptr, *x1 = nullptr, *b = nullptr, *r = nullptr, *d0 = nullptr, *d1 = nullptr;  // [ntot*C]
   int work_C = 0;
+  // multi-GPU: forward halo of this level (level 0 borrows the mesh's), global numbering
+  Halo halo;
+  bool owns_halo = false;
+  int64_t nglobal = 0;      // rows over all ranks
+  int64_t goff = 0;         // global index of owned row 0
+  int64_t* gid = nullptr;   // [ntot] global index of every local column (levels >= 1)
 };
 
 struct Amg {
@@ -164,6 +170,7 @@ struct Amg {
   double* coarse_inv = nullptr;   // dense [nc*nc] inverse (shifted if singular), or nullptr -> smoother only
   double* z = nullptr;            // [n0*C] preconditioned residual for PCG
   int z_C = 0;
+  double* cglob = nullptr;        // multi-GPU coarse solve: [2][C][nc] gathered right-hand side / scratch
   double setup_ms = 0.0;
   ~Amg();
 };
@@ -272,6 +279,11 @@ int assemble_a_dev(mv_mesh* m, const double* mon, const double* H, double* a, do
 int jac_A_dev(mv_mesh* m, const double* mon, const double* H, const double* dH, double sign, double* out);
 bool comm_active();
 int comm_size();
+int comm_rank();
+int allreduce_host(double* h, int n, int op);
+int allgather_i64(int64_t mine, std::vector<int64_t>& all);
+int neighbor_exchange_bytes(int nn, const int* ranks, const void* const* sbuf, const size_t* sbytes, void* const* rbuf,
+                            const size_t* rbytes);
 int grid_for(int64_t nthreads_needed, int blocks_per_sm = 8);
 int exclusive_scan_i64(const int64_t* in, int64_t* out, int64_t n);
 // multigrid (mv_amg.cu / mv_amg_cycle.cu)

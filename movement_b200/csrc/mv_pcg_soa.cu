@@ -58,7 +58,7 @@ k_soa_to_aos(int64_t n, const double* __restrict__ src, int64_t ld, double* __re
 }
 
 // ------------------------------------------------------------------ SpMV, component-major
-template <int C, bool DOT>
+template <int C, bool DOT, int VAR>
 __global__ void __launch_bounds__(MV_BLOCK)
 k_spmv_soa(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
            const double* __restrict__ val, const double* __restrict__ x, int64_t ld, double* __restrict__ y,
@@ -80,13 +80,33 @@ k_spmv_soa(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_ptr
     double acc[C];
 #pragma unroll
     for (int c = 0; c < C; ++c) acc[c] = 0.0;
-#pragma unroll 2
-    for (int k = 0; k < w; ++k) {
-      const int col = __ldcs(cp + k * MV_SLICE);
-      const double a = __ldcs(vp + k * MV_SLICE);
-      const double* xp = x + col;
+    // the column indices of a chunk of KB entries are fetched first, so KB*C gathers are in flight
+    // per thread instead of one dependent (index -> gather) chain per entry
+    constexpr int KB = C >= 9 ? 5 : (C >= 3 ? 8 : 8);
+    for (int k0 = 0; k0 < w; k0 += KB) {
+      int col[KB];
+      double a[KB];
 #pragma unroll
-      for (int c = 0; c < C; ++c) acc[c] = fma(a, __ldg(xp + c * ld), acc[c]);
+      for (int j = 0; j < KB; ++j) {
+        const bool in = k0 + j < w;
+        col[j] = in ? __ldcs(cp + (k0 + j) * MV_SLICE) : 0;
+        a[j] = in ? __ldcs(vp + (k0 + j) * MV_SLICE) : 0.0;
+      }
+      if (VAR == 0) {
+#pragma unroll
+        for (int j = 0; j < KB; ++j) {
+          const double* xp = x + col[j];
+#pragma unroll
+          for (int c = 0; c < C; ++c) acc[c] = fma(a[j], __ldg(xp + c * ld), acc[c]);
+        }
+      } else {   // component-outer: neighbouring columns of one component are gathered back to back (L1 reuse)
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          const double* xc = x + c * ld;
+#pragma unroll
+          for (int j = 0; j < KB; ++j) acc[c] = fma(a[j], __ldg(xc + col[j]), acc[c]);
+        }
+      }
     }
     if (row < nrows) {
 #pragma unroll
@@ -189,14 +209,29 @@ k_update_soa(int64_t n, int64_t ld, const double* __restrict__ p, const double* 
   VERTEX_LOOP(v, n) {
     const double di = JACOBI ? __ldg(&dinv[v]) : 0.0;
     const unsigned mk = mask ? __ldg(&mask[v]) : 0u;
+    // all loads first (the compiler cannot move a load of x/r above an earlier store to x/r, which
+    // serialised the C components: 2.7 TB/s at C = 9), then the arithmetic, then all stores
+    double xv[C], rv[C], pv[C], qv[C];
 #pragma unroll
     for (int c = 0; c < C; ++c) {
       const int64_t i = c * ld + v;
+      pv[c] = p[i];
+      qv[c] = __ldcs(&q[i]);
+      xv[c] = x[i];
+      rv[c] = r[i];
+    }
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
       const bool fix = (mk >> c) & 1u;
-      x[i] += alpha[c] * p[i];
-      const double rr = fix ? 0.0 : r[i] - alpha[c] * __ldcs(&q[i]);
-      r[i] = rr;
-      if (JACOBI) acc[c] = fma(rr * di, rr, acc[c]);
+      xv[c] += alpha[c] * pv[c];
+      rv[c] = fix ? 0.0 : rv[c] - alpha[c] * qv[c];
+      if (JACOBI) acc[c] = fma(rv[c] * di, rv[c], acc[c]);
+    }
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int64_t i = c * ld + v;
+      x[i] = xv[c];
+      r[i] = rv[c];
     }
   }
   if (JACOBI) {
@@ -219,11 +254,11 @@ k_dir_soa(int64_t n, int64_t ld, const double* __restrict__ r, const double* __r
   for (int c = 0; c < C; ++c) beta[c] = scal[SC(S_BETA, c)];
   VERTEX_LOOP(v, n) {
     const double di = __ldg(&dinv[v]);
+    double pv[C], rv[C];
 #pragma unroll
-    for (int c = 0; c < C; ++c) {
-      const int64_t i = c * ld + v;
-      p[i] = fma(beta[c], p[i], di * __ldcs(&r[i]));   // r is zero at constrained dofs
-    }
+    for (int c = 0; c < C; ++c) { pv[c] = p[c * ld + v]; rv[c] = __ldcs(&r[c * ld + v]); }
+#pragma unroll
+    for (int c = 0; c < C; ++c) p[c * ld + v] = fma(beta[c], pv[c], di * rv[c]);   // r is zero at constrained dofs
   }
 }
 
@@ -257,12 +292,13 @@ k_dir_z_soa(int64_t n, int64_t ld, const double* __restrict__ z, double* __restr
   double beta[C];
 #pragma unroll
   for (int c = 0; c < C; ++c) beta[c] = first ? 0.0 : scal[SC(S_BETA, c)];
-  VERTEX_LOOP(v, n)
+  VERTEX_LOOP(v, n) {
+    double pv[C], zv[C];
 #pragma unroll
-    for (int c = 0; c < C; ++c) {
-      const int64_t i = c * ld + v;
-      p[i] = first ? z[i] : fma(beta[c], p[i], z[i]);
-    }
+    for (int c = 0; c < C; ++c) { pv[c] = first ? 0.0 : p[c * ld + v]; zv[c] = z[c * ld + v]; }
+#pragma unroll
+    for (int c = 0; c < C; ++c) p[c * ld + v] = fma(beta[c], pv[c], zv[c]);
+  }
 }
 
 template <int C>
@@ -296,12 +332,15 @@ template <int C>
 static int spmv_soa_launch(mv_mesh* m, const double* val, const double* x, double* y, int64_t ld, bool dot) {
   const Sell& p = m->pat;
   const int grid = grid_for(p.nslices * MV_SLICE, 8);
-  if (dot)
-    MV_L k_spmv_soa<C, true><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, p.nrows, p.slice_ptr, p.cols, val, x, ld, y, m->pcg.flags,
-                                                         m->red.partials, m->red.counter, m->pcg.scal, S_PQ);
-  else
-    MV_L k_spmv_soa<C, false><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, p.nrows, p.slice_ptr, p.cols, val, x, ld, y, nullptr, nullptr,
-                                                          nullptr, nullptr, 0);
+  static int variant = -1;
+  if (variant < 0) { const char* e = getenv("MV_SPMV_VARIANT"); variant = e ? atoi(e) : 0; }
+#define SPMV_LAUNCH(D, V)                                                                                                   \
+  MV_L k_spmv_soa<C, D, V><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, p.nrows, p.slice_ptr, p.cols, val, x, ld, y,          \
+                                                       D ? m->pcg.flags : nullptr, D ? m->red.partials : nullptr,        \
+                                                       D ? m->red.counter : nullptr, D ? m->pcg.scal : nullptr, S_PQ)
+  if (dot) { if (variant == 1) SPMV_LAUNCH(true, 1); else SPMV_LAUNCH(true, 0); }
+  else { if (variant == 1) SPMV_LAUNCH(false, 1); else SPMV_LAUNCH(false, 0); }
+#undef SPMV_LAUNCH
   MV_KERNEL_CHECK();
   return MV_OK;
 }

@@ -19,3 +19,14 @@ def test_two_rank_relaxation_matches_oracle(dim, n):
                           os.path.join(ROOT, "tests", "dist", "run_ma_2rank.py"), str(dim), str(n)],
                          capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "DIST-OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
+
+
+@pytest.mark.parametrize("dim,n", [(3, 20), (2, 96)])
+def test_two_rank_multigrid_poisson(dim, n):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29519",
+                          os.path.join(ROOT, "tests", "dist", "run_amg_2rank.py"), str(dim), str(n)],
+                         capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "DIST-AMG-OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
