@@ -455,6 +455,11 @@ int amg_exchange_prolongator(const Halo& H, int64_t n, int64_t ntot, const Csr& 
                              const std::vector<int64_t>& coff_all, Csr& Pext, Halo& Hc, int64_t* ntot_c, int64_t** gid_c);
 int amg_dense_gather(const AmgLevel& L, double shift, double* a);
 
+// While the replicated tail of a multi-GPU hierarchy is being built every rank works on the same
+// gathered operator, so the set-up must not communicate.
+static bool g_serial = false;
+static bool amg_dist() { return comm_active() && !g_serial; }
+
 // set-up decisions must be identical on every rank: reduce the local status / flags
 static int global_max_int(int v, int* out) {
   double h = (double)v;
@@ -470,7 +475,7 @@ static int global_sum_i64(int64_t v, int64_t* out) {
 }
 // st: local status of a set-up stage; returns the first non-OK status of any rank (as UNSUPPORTED if remote)
 static int agree(int st) {
-  if (!comm_active()) return st;
+  if (!amg_dist()) return st;
   int g = 0;
   if (global_max_int(st == MV_OK ? 0 : 1, &g) != MV_OK) return MV_ERR_COMM;
   if (g && st == MV_OK) { set_error("amg: set-up stage failed on another rank"); return MV_ERR_UNSUPPORTED; }
@@ -487,10 +492,10 @@ static int estimate_rho(mv_mesh* m, const AmgLevel& L, double* rho) {
   MV_L k_pow_init<<<grid, MV_BLOCK, 0, g_stream>>>(L.n, L.dinv, x);
   const int iters = 15;
   for (int k = 0; k < iters; ++k) {
-    if (comm_active()) MV_CHECK(halo_exchange_soa(L.halo, L.n, 1, x, L.ntot));
+    if (amg_dist()) MV_CHECK(halo_exchange_soa(L.halo, L.n, 1, x, L.ntot));
     MV_L k_pow_step<<<grid, MV_BLOCK, 0, g_stream>>>(L.n, L.pat.slice_ptr, L.pat.cols, L.val, L.pat.row_nnz, L.dinv, x, y,
                                                 m->red.partials, m->red.counter, out);
-    if (comm_active()) MV_CHECK(allreduce_sum_dev(out, 2));
+    if (amg_dist()) MV_CHECK(allreduce_sum_dev(out, 2));
     if (k + 1 < iters) MV_L k_pow_scale<<<grid, MV_BLOCK, 0, g_stream>>>(L.n, y, out, x);
   }
   MV_KERNEL_CHECK();
@@ -639,14 +644,15 @@ static int two_phase(Csr& c, Count count, Fill fill, int* err_flag) {
 // Build level l+1 from level l.  Returns MV_ERR_UNSUPPORTED when coarsening should stop here (same answer on every rank).
 static int coarsen(mv_mesh* m, Amg* a, double theta, double* diag) {
   AmgLevel& L = a->lv.back();
-  const bool dist = comm_active();
+  const bool dist = amg_dist();
   Graph g{L.n, L.pat.slice_ptr, L.pat.cols, L.val, L.pat.row_nnz, diag, L.mask, theta * theta};
   int* agg = nullptr;
   int64_t nc = 0;
   int st = agree(aggregate(m, g, &agg, &nc));
   if (st != MV_OK) { dev_free(agg); return st; }
   std::vector<int64_t> nc_all, coff_all;
-  MV_CHECK(allgather_i64(nc, nc_all));
+  if (dist) MV_CHECK(allgather_i64(nc, nc_all));
+  else nc_all.assign(1, nc);
   coff_all.assign(nc_all.size() + 1, 0);
   for (size_t r = 0; r < nc_all.size(); ++r) coff_all[r + 1] = coff_all[r] + nc_all[r];
   const int64_t ncg = coff_all.back();
@@ -725,53 +731,157 @@ static int coarsen(mv_mesh* m, Amg* a, double theta, double* diag) {
   N.n = nc;
   N.ntot = ntot_c;
   N.nglobal = ncg;
-  N.goff = coff_all[comm_rank()];
+  N.goff = dist ? coff_all[comm_rank()] : 0;
+  N.dist = dist;
   a->lv.push_back(N);
   return MV_OK;
 }
 
-static int amg_build(mv_mesh* m, int op, const uint16_t* mask_bit0, int singular, Amg** out) {
-  cudaEvent_t e0, e1;
-  cudaEventCreate(&e0); cudaEventCreate(&e1);
-  cudaEventRecord(e0, g_stream);
-  Amg* a = new Amg();
-  a->op = op;
-  a->singular = singular;
-  const double *val, *dinv_unused;
-  MV_CHECK(op_arrays(m, op, &val, &dinv_unused));
-  const double theta = env_double("MV_AMG_THETA", 1e-8);
-  const int deg0 = env_int("MV_AMG_DEG0", 1), degc = env_int("MV_AMG_DEGC", 3);
-  const int64_t dense_max = env_int("MV_AMG_DENSE_MAX", 640);
-  AmgLevel L0;
-  L0.n = m->Vown; L0.ntot = m->V;
-  L0.pat = m->pat; L0.val = val; L0.owns_A = false;
-  L0.mask = mask_bit0;
-  L0.halo = m->halo;          // borrowed (device lists belong to the mesh)
-  L0.owns_halo = false;
-  L0.nglobal = L0.n;
-  if (comm_active()) {
-    MV_CHECK(global_sum_i64(L0.n, &L0.nglobal));
-    std::vector<int64_t> all;
-    MV_CHECK(allgather_i64(L0.n, all));
-    for (int r = 0; r < comm_rank(); ++r) L0.goff += all[r];
+// SELL rows [row0, row0+nrows) -> CSR; gid (optional) maps the local column numbers
+__global__ void k_sell_rows_count(int64_t nrows, int64_t row0, const int* __restrict__ row_nnz, int64_t* __restrict__ cnt) {
+  GRID_STRIDE(i, nrows + 1) cnt[i] = i < nrows ? row_nnz[row0 + i] : 0;
+}
+__global__ void k_sell_rows_fill(int64_t nrows, int64_t row0, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
+                                 const double* __restrict__ val, const int* __restrict__ row_nnz, const int64_t* __restrict__ gid,
+                                 const int64_t* __restrict__ ptr, int* __restrict__ col, double* __restrict__ v) {
+  GRID_STRIDE(i, nrows) {
+    const int64_t o = ptr[i];
+    sell_row(slice_ptr, cols, val, row_nnz, row0 + i, [&](int c, double a, int k) {
+      col[o + k] = gid ? (int)gid[c] : c;
+      v[o + k] = a;
+    });
   }
-  a->lv.push_back(L0);
+}
+static int sell_rows_to_csr(const Sell& p, const double* val, int64_t row0, int64_t nrows, int64_t ncols, const int64_t* gid, Csr& c) {
+  c.nrows = nrows;
+  c.ncols = ncols;
+  int64_t* cnt = nullptr;
+  MV_CHECK(dev_alloc(&cnt, nrows + 1));
+  MV_L k_sell_rows_count<<<grid_for(nrows + 1), MV_BLOCK, 0, g_stream>>>(nrows, row0, p.row_nnz, cnt);
+  MV_KERNEL_CHECK();
+  MV_CHECK(csr_finish_symbolic(c, cnt));
+  dev_free(cnt);
+  MV_L k_sell_rows_fill<<<grid_for(nrows), MV_BLOCK, 0, g_stream>>>(nrows, row0, p.slice_ptr, p.cols, val, p.row_nnz, gid, c.ptr, c.col, c.val);
+  MV_KERNEL_CHECK();
+  return MV_OK;
+}
+__global__ void k_add_i64(int64_t n, int64_t* __restrict__ p, int64_t off) { GRID_STRIDE(i, n) p[i] += off; }
+
+// The rows of a distributed level, gathered on every rank in global numbering (CSR).
+static int gather_level(const AmgLevel& L, Csr& G) {
+  Csr loc;
+  MV_CHECK(sell_rows_to_csr(L.pat, L.val, 0, L.n, L.nglobal, L.gid, loc));
+  std::vector<int64_t> n_all, z_all;
+  MV_CHECK(allgather_i64(L.n, n_all));
+  MV_CHECK(allgather_i64(loc.nnz, z_all));
+  const int R = (int)n_all.size(), me = comm_rank();
+  std::vector<int64_t> roff(R + 1, 0), zoff(R + 1, 0);
+  for (int r = 0; r < R; ++r) { roff[r + 1] = roff[r] + n_all[r]; zoff[r + 1] = zoff[r] + z_all[r]; }
+  G.nrows = G.ncols = roff[R];
+  G.nnz = zoff[R];
+  MV_CHECK(dev_alloc(&G.ptr, G.nrows + 1));
+  MV_CHECK(dev_alloc(&G.col, G.nnz));
+  MV_CHECK(dev_alloc(&G.val, G.nnz));
+  if (L.n) {
+    MV_L k_add_i64<<<grid_for(L.n), MV_BLOCK, 0, g_stream>>>(L.n, loc.ptr, zoff[me]);
+    MV_CUDA(cudaMemcpyAsync(G.ptr + roff[me], loc.ptr, L.n * sizeof(int64_t), cudaMemcpyDeviceToDevice, g_stream));
+    MV_CUDA(cudaMemcpyAsync(G.col + zoff[me], loc.col, loc.nnz * sizeof(int), cudaMemcpyDeviceToDevice, g_stream));
+    MV_CUDA(cudaMemcpyAsync(G.val + zoff[me], loc.val, loc.nnz * sizeof(double), cudaMemcpyDeviceToDevice, g_stream));
+  }
+  MV_CUDA(cudaMemcpyAsync(G.ptr + G.nrows, &G.nnz, sizeof(int64_t), cudaMemcpyHostToDevice, g_stream));
+  for (int r = 0; r < R; ++r) {
+    MV_CHECK(bcast_bytes(G.ptr + roff[r], (size_t)n_all[r] * sizeof(int64_t), r));
+    MV_CHECK(bcast_bytes(G.col + zoff[r], (size_t)z_all[r] * sizeof(int), r));
+    MV_CHECK(bcast_bytes(G.val + zoff[r], (size_t)z_all[r] * sizeof(double), r));
+  }
+  MV_CUDA(cudaStreamSynchronize(g_stream));
+  loc.release();
+  return MV_OK;
+}
+
+struct BuildParams {
+  double theta;
+  int deg0, degc;
+  int64_t dense_max, repl_max;
+};
+static int build_levels(mv_mesh* m, Amg* a, const BuildParams& bp);
+
+// Multi-GPU: from this (distributed) level down, the hierarchy is built from the gathered operator and
+// kept REPLICATED on every rank: coarse levels are tiny, and a rank-local prolongator on them (where the
+// partition interface is a large share of the rows) costs iterations (oracle/amg_prototype.py: 21 -> 30+).
+static int replicate_tail(mv_mesh* m, Amg* a, const BuildParams& bp) {
+  Csr G;
+  MV_CHECK(gather_level(a->lv.back(), G));
+  Amg tail;
+  tail.op = a->op;
+  tail.singular = a->singular;
+  {
+    AmgLevel T0;
+    T0.n = T0.ntot = T0.nglobal = G.nrows;
+    double* v = nullptr;
+    MV_CHECK(csr_to_sell(G, T0.pat, &v));
+    T0.val = v;
+    T0.owns_A = true;
+    tail.lv.push_back(T0);
+  }
+  G.release();
+  g_serial = true;
+  BuildParams tp = bp;
+  tp.deg0 = bp.degc;
+  int st = build_levels(m, &tail, tp);
+  g_serial = false;
+  if (st != MV_OK) return st;
+  AmgLevel& L = a->lv.back();
+  if (tail.lv.size() == 1) {
+    // could not coarsen further: this level is the coarsest; keep the (gathered) dense inverse if there is one
+    a->coarse_inv = tail.coarse_inv;
+    tail.coarse_inv = nullptr;
+    a->nc = L.nglobal;
+    if (!a->coarse_inv) L.degree = 8;
+    return MV_OK;
+  }
+  // own rows of the global prolongator; the restriction is its transpose (partial sums, allreduced in the cycle)
+  const AmgLevel& T0 = tail.lv[0];
+  const int64_t nc = tail.lv[1].n;
+  Csr Ploc, Rpart;
+  MV_CHECK(sell_rows_to_csr(T0.P, T0.Pval, L.goff, L.n, nc, nullptr, Ploc));
+  MV_CHECK(csr_transpose(Ploc, Rpart));
+  MV_CHECK(csr_to_sell(Ploc, L.P, &L.Pval));
+  MV_CHECK(csr_to_sell(Rpart, L.R, &L.Rval));
+  Ploc.release(); Rpart.release();
+  L.reduce_next = true;
+  a->coarse_inv = tail.coarse_inv;
+  tail.coarse_inv = nullptr;
+  a->nc = tail.nc;
+  std::vector<AmgLevel> moved(tail.lv.begin() + 1, tail.lv.end());
+  tail.lv.resize(1);   // the tail's destructor frees the gathered operator and the global P, R
+  for (AmgLevel& N : moved) a->lv.push_back(N);
+  return MV_OK;
+}
+
+// Coarsen from the last level of a->lv until the coarsest level is reached; sets a->nc / a->coarse_inv.
+static int build_levels(mv_mesh* m, Amg* a, const BuildParams& bp) {
   int st = MV_OK;
   while (true) {
     AmgLevel& L = a->lv.back();
-    L.degree = a->lv.size() == 1 ? deg0 : degc;
+    const bool dist = amg_dist();
+    L.dist = dist;
+    L.degree = a->lv.size() == 1 ? bp.deg0 : bp.degc;
     double* diag = nullptr;
     if ((st = dev_alloc(&diag, L.n)) != MV_OK) break;
     if ((st = dev_alloc(&L.dinv, L.n)) != MV_OK) break;
     MV_L k_amg_diag<<<grid_for(L.n), MV_BLOCK, 0, g_stream>>>(L.n, L.pat.slice_ptr, L.pat.cols, L.val, L.pat.row_nnz, L.mask, diag, L.dinv);
     if ((st = estimate_rho(m, L, &L.rho)) != MV_OK) { dev_free(diag); break; }
-    const bool last = L.nglobal <= dense_max || (int)a->lv.size() >= MV_AMG_MAX_LEVELS;
-    int cs = last ? MV_ERR_UNSUPPORTED : coarsen(m, a, theta, diag);
+    const bool last = L.nglobal <= bp.dense_max || (int)a->lv.size() >= MV_AMG_MAX_LEVELS;
+    if (!last && dist && L.gid != nullptr && L.nglobal <= bp.repl_max) {
+      dev_free(diag);
+      return replicate_tail(m, a, bp);
+    }
+    int cs = last ? MV_ERR_UNSUPPORTED : coarsen(m, a, bp.theta, diag);
     if (cs == MV_OK) { dev_free(diag); continue; }
     if (cs != MV_ERR_UNSUPPORTED) { st = cs; dev_free(diag); break; }
     // this level is the coarsest
     AmgLevel& Lc = a->lv.back();
-    const bool dist = comm_active();
     const int64_t N = Lc.nglobal;
     a->nc = N;
     // gathered dense solve needs the global column ids, which exist from level 1 on
@@ -787,7 +897,7 @@ static int amg_build(mv_mesh* m, int op, const uint16_t* mask_bit0, int singular
       cudaMemcpyAsync(&hs, shift, sizeof(double), cudaMemcpyDeviceToHost, g_stream);
       cudaStreamSynchronize(g_stream);
       if (dist && (st = allreduce_host(&hs, 1, 0)) != MV_OK) break;
-      hs = singular ? hs / ((double)N * (double)N) : 0.0;   // A + s 1 1^T: exact pseudo-inverse action on vectors orthogonal to 1
+      hs = a->singular ? hs / ((double)N * (double)N) : 0.0;   // A + s 1 1^T: exact pseudo-inverse action on vectors orthogonal to 1
       if (dist) {
         if ((st = amg_dense_gather(Lc, hs, a->coarse_inv)) != MV_OK) break;
       } else {
@@ -804,6 +914,39 @@ static int amg_build(mv_mesh* m, int op, const uint16_t* mask_bit0, int singular
     dev_free(diag);
     break;
   }
+  return st;
+}
+
+static int amg_build(mv_mesh* m, int op, const uint16_t* mask_bit0, int singular, Amg** out) {
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  cudaEventRecord(e0, g_stream);
+  Amg* a = new Amg();
+  a->op = op;
+  a->singular = singular;
+  const double *val, *dinv_unused;
+  MV_CHECK(op_arrays(m, op, &val, &dinv_unused));
+  BuildParams bp;
+  bp.theta = env_double("MV_AMG_THETA", 1e-8);
+  bp.deg0 = env_int("MV_AMG_DEG0", 1);
+  bp.degc = env_int("MV_AMG_DEGC", 3);
+  bp.dense_max = env_int("MV_AMG_DENSE_MAX", 640);
+  bp.repl_max = (int64_t)env_int("MV_AMG_REPLICATE_MAX", 4000000);
+  AmgLevel L0;
+  L0.n = m->Vown; L0.ntot = m->V;
+  L0.pat = m->pat; L0.val = val; L0.owns_A = false;
+  L0.mask = mask_bit0;
+  L0.halo = m->halo;          // borrowed (device lists belong to the mesh)
+  L0.owns_halo = false;
+  L0.nglobal = L0.n;
+  if (comm_active()) {
+    MV_CHECK(global_sum_i64(L0.n, &L0.nglobal));
+    std::vector<int64_t> all;
+    MV_CHECK(allgather_i64(L0.n, all));
+    for (int r = 0; r < comm_rank(); ++r) L0.goff += all[r];
+  }
+  a->lv.push_back(L0);
+  int st = build_levels(m, a, bp);
   cudaEventRecord(e1, g_stream);
   cudaEventSynchronize(e1);
   float ms = 0.f;
@@ -816,9 +959,9 @@ static int amg_build(mv_mesh* m, int op, const uint16_t* mask_bit0, int singular
     fprintf(stderr, "[mv amg] rank %d op %d: %zu levels, set-up %.1f ms, singular %d, dense coarse %d\n", comm_rank(), op, a->lv.size(), ms,
             singular, a->coarse_inv ? 1 : 0);
     for (size_t l = 0; l < a->lv.size(); ++l)
-      fprintf(stderr, "   level %zu: n %lld (+%lld ghosts, global %lld) nnz %lld maxw %d rho %.3f degree %d\n", l, (long long)a->lv[l].n,
-              (long long)(a->lv[l].ntot - a->lv[l].n), (long long)a->lv[l].nglobal, (long long)a->lv[l].pat.nnz, a->lv[l].pat.maxw,
-              a->lv[l].rho, a->lv[l].degree);
+      fprintf(stderr, "   level %zu: n %lld (+%lld ghosts, global %lld, %s) nnz %lld maxw %d rho %.3f degree %d\n", l, (long long)a->lv[l].n,
+              (long long)(a->lv[l].ntot - a->lv[l].n), (long long)a->lv[l].nglobal, a->lv[l].dist ? "distributed" : "replicated/serial",
+              (long long)a->lv[l].pat.nnz, a->lv[l].pat.maxw, a->lv[l].rho, a->lv[l].degree);
   }
   *out = a;
   return MV_OK;

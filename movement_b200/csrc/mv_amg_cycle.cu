@@ -217,7 +217,7 @@ int amg_ensure_work(Amg* a, int C) {
     }
     L.work_C = C;
   }
-  if (comm_active() && a->coarse_inv && a->z_C < C) {
+  if (a->lv.back().dist && a->coarse_inv && a->z_C < C) {
     dev_free(a->cglob);
     MV_CHECK(dev_alloc(&a->cglob, (size_t)a->nc * C));
   }
@@ -245,7 +245,7 @@ static int smooth(AmgLevel& L, const double* b, const double* xin, double* xout,
   double* dcur = deg > 1 ? L.d0 : nullptr;
   double* dnext = L.d1;
   const double* rin = b;
-  if (xin && comm_active()) MV_CHECK(halo_exchange_soa(L.halo, L.n, C, const_cast<double*>(xin), L.ntot));
+  if (xin && L.dist) MV_CHECK(halo_exchange_soa(L.halo, L.n, C, const_cast<double*>(xin), L.ntot));
   if (!xin) {
     MV_L k_smooth_zero<C><<<grid_for(L.n), MV_BLOCK, 0, g_stream>>>(L.n, L.ntot, b, L.dinv, 1.0 / theta, xout, dcur, done);
   } else {
@@ -257,7 +257,7 @@ static int smooth(AmgLevel& L, const double* b, const double* xin, double* xout,
   for (int k = 1; k < deg; ++k) {
     const double rho_n = 1.0 / (2.0 * sigma - rho_k);
     const bool last = k == deg - 1;
-    if (comm_active()) MV_CHECK(halo_exchange_soa(L.halo, L.n, C, dcur, L.ntot));
+    if (L.dist) MV_CHECK(halo_exchange_soa(L.halo, L.n, C, dcur, L.ntot));
     MV_L k_smooth_next<C><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, L.n, L.ntot, p.slice_ptr, p.cols, L.val, dcur, dnext, rin, last ? nullptr : L.r,
                                                       L.dinv, rho_n * rho_k, 2.0 * rho_n / delta, xout, done);
     rin = L.r;
@@ -276,10 +276,11 @@ static int vcycle(mv_mesh* m, Amg* a, const double* rfine, double* z, const int*
     AmgLevel& L = a->lv[l];
     AmgLevel& N = a->lv[l + 1];
     MV_CHECK(smooth<C>(L, b, nullptr, L.x0, done));
-    if (comm_active()) MV_CHECK(halo_exchange_soa(L.halo, L.n, C, L.x0, L.ntot));
+    if (L.dist) MV_CHECK(halo_exchange_soa(L.halo, L.n, C, L.x0, L.ntot));
     MV_L k_residual<C><<<slice_grid(L.pat), MV_BLOCK, 0, g_stream>>>(L.pat.nslices, L.n, L.ntot, L.pat.slice_ptr, L.pat.cols, L.val, b, L.x0, L.dinv,
                                                                 L.r, done);
     MV_L k_sell_apply<C, false><<<slice_grid(L.R), MV_BLOCK, 0, g_stream>>>(L.R.nslices, N.n, L.R.slice_ptr, L.R.cols, L.Rval, L.r, L.ntot, N.b, N.ntot, done);
+    if (L.reduce_next) MV_CHECK(allreduce_sum_dev(N.b, (int)(N.ntot * C)));   // replicated coarse level: sum of the ranks' partial restrictions
     b = N.b;
   }
   AmgLevel& Lc = a->lv[nl - 1];
@@ -287,7 +288,7 @@ static int vcycle(mv_mesh* m, Amg* a, const double* rfine, double* z, const int*
   if (a->coarse_inv) {
     const int64_t threads = (int64_t)Lc.n * 32;
     const unsigned blocks = (unsigned)((threads + MV_BLOCK - 1) / MV_BLOCK);
-    if (comm_active()) {
+    if (Lc.dist) {
       // gather the coarse right-hand side of all ranks (each entry is non-zero on one rank: exact sum)
       const int N = (int)a->nc;
       MV_CUDA(cudaMemsetAsync(a->cglob, 0, (size_t)N * C * sizeof(double), g_stream));

@@ -22,6 +22,7 @@ struct NcclApi {
   ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
   ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*GroupStart)() = nullptr;
@@ -59,6 +60,7 @@ static int load_nccl(const char* path) {
   SYM(CommInitRank, "ncclCommInitRank");
   SYM(CommDestroy, "ncclCommDestroy");
   SYM(AllReduce, "ncclAllReduce");
+  SYM(Broadcast, "ncclBroadcast");
   SYM(Send, "ncclSend");
   SYM(Recv, "ncclRecv");
   SYM(GroupStart, "ncclGroupStart");
@@ -147,6 +149,12 @@ int allgather_i64(int64_t mine, std::vector<int64_t>& all) {
   h[g_rank] = (double)mine;
   MV_CHECK(allreduce_host(h.data(), g_nranks, 0));
   for (int r = 0; r < g_nranks; ++r) all[r] = (int64_t)(h[r] + (h[r] >= 0 ? 0.5 : -0.5));
+  return MV_OK;
+}
+// In-place broadcast of raw device bytes from `root`.
+int bcast_bytes(void* buf, size_t bytes, int root) {
+  if (!comm_active() || bytes == 0) return MV_OK;
+  MV_NCCL(g_nccl.Broadcast(buf, buf, bytes, ncclChar, root, g_comm, g_stream));
   return MV_OK;
 }
 // Neighbour exchange of raw device bytes: neighbour k gets sbuf[k] (sbytes[k]) and fills rbuf[k] (rbytes[k]).

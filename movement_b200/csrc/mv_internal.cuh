@@ -155,6 +155,8 @@ struct AmgLevel {
   // multi-GPU: forward halo of this level (level 0 borrows the mesh's), global numbering
   Halo halo;
   bool owns_halo = false;
+  bool dist = false;        // operator rows are spread over the ranks (halo exchange before every gather of a vector)
+  bool reduce_next = false; // next level is replicated on every rank: its right-hand side is the allreduce of the partial restrictions
   int64_t nglobal = 0;      // rows over all ranks
   int64_t goff = 0;         // global index of owned row 0
   int64_t* gid = nullptr;   // [ntot] global index of every local column (levels >= 1)
@@ -282,6 +284,7 @@ int comm_size();
 int comm_rank();
 int allreduce_host(double* h, int n, int op);
 int allgather_i64(int64_t mine, std::vector<int64_t>& all);
+int bcast_bytes(void* buf, size_t bytes, int root);
 int neighbor_exchange_bytes(int nn, const int* ranks, const void* const* sbuf, const size_t* sbytes, void* const* rbuf,
                             const size_t* rbytes);
 int grid_for(int64_t nthreads_needed, int blocks_per_sm = 8);
