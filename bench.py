@@ -210,6 +210,9 @@ def run_ours(args):
         host = arrays
         Vglobal, Cglobal = arrays[0].shape[0], arrays[1].shape[0]
     del arrays
+    # the caller's buffers live in pinned host memory (numpy views of pinned torch tensors)
+    pinned = [torch.from_numpy(np.ascontiguousarray(a)).pin_memory() for a in host]
+    host = tuple(t.numpy() for t in pinned)
     h2d_bytes = sum(int(a.nbytes) for a in host)
 
     def make_mover():
@@ -252,19 +255,32 @@ def run_ours(args):
     cg = np.array(mover.cg_iterations[-args.steps:])
     value = Vglobal * args.steps / (ms * 1e-3)
 
-    # ---- roofline of the dominant kernel: k_spmv<1,DOT> on K inside the Poisson PCG -----------------
+    # ---- roofline of the dominant kernel: the SELL-32 SpMV of the PCG solves, timed live per launch with CUDA
+    # events on the launching stream (mv_prof_*), by number of right-hand sides C: 3 = L2 projection (mass),
+    # 1 = Poisson (stiffness), 9 = Hessian recovery (mass).  Algorithmic bytes per launch:
+    # 12 B per stored non-zero + 4 B slice pointer per row + read p / write q: 16*C B per row.
     dm = mover._dm
     peak, peak_src = peaks()
-    alg_bytes = 12.0 * dm.nnz + 20.0 * dm.Vown     # cols+vals of every stored nonzero, slice ptr, read p, write q
-    avg_ms = spmv_ms[1] / max(spmv_cnt[1], 1)
-    achieved = alg_bytes / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
+    classes = {}
+    for c in (1, 3, 9):
+        if spmv_cnt[c] > 0:
+            alg = 12.0 * dm.nnz + (4.0 + 16.0 * c) * dm.Vown
+            avg = spmv_ms[c] / spmv_cnt[c]
+            classes[c] = {"rhs": c, "launches_timed": int(spmv_cnt[c]), "avg_launch_ms": avg, "algorithmic_bytes_per_launch": alg,
+                          "achieved_GBs": alg / (avg * 1e-3) / 1e9, "share_of_step": spmv_ms[c] / ms}
+    dom = max(classes, key=lambda c: classes[c]["share_of_step"])
     traffic = ncu_traffic()
-    roofline = {"bound": "hbm", "kernel": "k_spmv<1,true> (SELL-32 SpMV + p.q, stiffness matrix, Poisson PCG)",
-                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
-                "frac_of_nominal_8TBs": achieved / 8000.0,
-                "algorithmic_bytes_per_launch": alg_bytes, "avg_launch_ms": avg_ms, "launches_timed": int(spmv_cnt[1]),
-                "share_of_step": spmv_ms[1] / ms if ms > 0 else None,
-                "traffic": (traffic or {}).get("dram_bytes_per_launch"), "traffic_source": (traffic or {}).get("source")}
+    kname = {1: "k_spmv_soa<1,true> (stiffness matrix, Poisson PCG)", 3: "k_spmv_soa<3,true> (mass matrix, L2 projection of grad phi)",
+             9: "k_spmv_soa<9,true> (mass matrix, Hessian recovery)"}[dom]
+    tr = (traffic or {}).get(str(dom)) or {}
+    roofline = {"bound": "hbm", "kernel": "SELL-32 SpMV + fused p.q, " + kname,
+                "achieved": classes[dom]["achieved_GBs"], "peak": peak, "unit": "GB/s", "frac": classes[dom]["achieved_GBs"] / peak,
+                "peak_source": peak_src, "frac_of_nominal_8TBs": classes[dom]["achieved_GBs"] / 8000.0,
+                "algorithmic_bytes_per_launch": classes[dom]["algorithmic_bytes_per_launch"],
+                "avg_launch_ms": classes[dom]["avg_launch_ms"], "launches_timed": classes[dom]["launches_timed"],
+                "share_of_step": classes[dom]["share_of_step"],
+                "traffic": tr.get("dram_bytes_per_launch"), "traffic_source": tr.get("source"),
+                "all_spmv_classes": [classes[c] for c in sorted(classes)]}
     # whole-step accounting with the SURVEY 8d byte model B_cg(c) = 12 nnz + 4 + 104 c per vertex per PCG iteration
     nnzv = dm.nnz / dm.Vown
     d = 3
@@ -280,18 +296,22 @@ def run_ours(args):
         barrier()
         t0 = time.perf_counter()
         m2 = make_mover()
+        torch.cuda.synchronize(); t1 = time.perf_counter()
         m2._begin()
         for _ in range(args.steps):
             step(m2)
+        torch.cuda.synchronize(); t2 = time.perf_counter()
         m2.to_physical_coordinates()
         out = m2.mesh.coordinates.tensor[: m2._dm.Vown].cpu()     # D2H of the moved (owned) coordinates
         barrier()
-        t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        t3 = time.perf_counter()
+        t = torch.tensor([t3 - t0], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e = {"value": Vglobal * args.steps / float(t.item()), "unit": UNIT,
                "h2d_bytes_per_step": h2d_bytes / args.steps, "d2h_bytes_per_step": (out.numel() * 8 + 6 * 8 * args.steps) / args.steps,
                "seconds": float(t.item()),
+               "breakdown_s": {"h2d+ingest+assembly": t1 - t0, "iterations (incl. multigrid set-up)": t2 - t1, "d2h": t3 - t2},
                "what": "MongeAmpereMover(host mesh).move-equivalent: H2D mesh + ingest/assembly + K iterations + D2H coordinates"}
         del m2
 
@@ -306,7 +326,6 @@ def run_ours(args):
                            "residual_after_timed_steps": residuals[-1]},
                 "roofline": roofline,
                 "step_model": {"bytes_per_step": step_bytes, "GBs": step_gbs, "frac_of_peak": step_gbs / (peak * world)},
-                "spmv_avg_ms_by_rhs": {str(c): spmv_ms[c] / spmv_cnt[c] for c in range(16) if spmv_cnt[c] > 0},
                 "gpu_launches": int(launches.value), "clocks": clocks, "e2e": e2e}
         if world == 1 and not args.no_cpu_baseline:
             r = cpu_relax(args.cpu_n, args.cpu_steps, 1, args.inner_rtol)

@@ -18,6 +18,8 @@
 //   6. rho(D^-1 A)      power iteration, 12 steps, x1.1
 // The coarsest operator (<= MV_AMG_DENSE rows) is inverted densely by Gauss-Jordan in one CTA.
 // oracle/amg_prototype.py is the numpy statement of the same algorithm.
+#include <cub/device/device_radix_sort.cuh>
+
 #include "mv_internal.cuh"
 
 #define MV_AMG_DENSE 1024       // coarsest level is inverted densely when it has at most this many rows
@@ -52,6 +54,7 @@ Amg::~Amg() {
     sell_free(L.R);
     dev_free(L.Pval);
     dev_free(L.Rval);
+    L.Rc.release();
     dev_free(L.x0);
     if (l > 0) dev_free(L.b);
     dev_free(L.x1); dev_free(L.r); dev_free(L.d0); dev_free(L.d1);
@@ -409,6 +412,17 @@ static int csr_finish_symbolic(Csr& c, int64_t* counts) {
   return MV_OK;
 }
 
+// (column << 32 | row) keys of every stored entry, in storage order
+__global__ void k_tr_keys(int64_t nrows, const int64_t* __restrict__ ptr, const int* __restrict__ col,
+                          unsigned long long* __restrict__ key) {
+  GRID_STRIDE(i, nrows)
+    for (int64_t t = ptr[i]; t < ptr[i + 1]; ++t) key[t] = ((unsigned long long)(unsigned)col[t] << 32) | (unsigned long long)(unsigned)i;
+}
+__global__ void k_tr_unpack(int64_t nnz, const unsigned long long* __restrict__ key, int* __restrict__ tcol) {
+  GRID_STRIDE(t, nnz) tcol[t] = (int)(key[t] & 0xffffffffull);
+}
+
+// Transpose by one radix sort of (column, row) keys: rows of the result come out sorted, no atomics on values.
 static int csr_transpose(const Csr& a, Csr& t) {
   t.nrows = a.ncols;
   t.ncols = a.nrows;
@@ -418,14 +432,29 @@ static int csr_transpose(const Csr& a, Csr& t) {
   if (a.nnz) MV_L k_tr_count<<<grid_for(a.nnz), MV_BLOCK, 0, g_stream>>>(a.nnz, a.col, cnt);
   MV_KERNEL_CHECK();
   MV_CHECK(csr_finish_symbolic(t, (int64_t*)cnt));
-  MV_CUDA(cudaMemsetAsync(cnt, 0, (t.nrows + 1) * sizeof(unsigned long long), g_stream));
-  MV_L k_tr_fill<<<grid_for(a.nrows), MV_BLOCK, 0, g_stream>>>(a.nrows, a.ptr, a.col, a.val, t.ptr, cnt, t.col, t.val);
-  MV_L k_csr_sort_rows<<<grid_for(t.nrows), MV_BLOCK, 0, g_stream>>>(t.nrows, t.ptr, t.col, t.val);
-  MV_KERNEL_CHECK();
   dev_free(cnt);
+  if (a.nnz == 0) return MV_OK;
+  unsigned long long *k0 = nullptr, *k1 = nullptr;
+  MV_CHECK(dev_alloc(&k0, a.nnz));
+  MV_CHECK(dev_alloc(&k1, a.nnz));
+  MV_L k_tr_keys<<<grid_for(a.nrows), MV_BLOCK, 0, g_stream>>>(a.nrows, a.ptr, a.col, k0);
+  MV_KERNEL_CHECK();
+  int bits_row = 1, bits_col = 1;
+  while ((1ll << bits_row) < a.nrows) ++bits_row;
+  while ((1ll << bits_col) < a.ncols) ++bits_col;
+  void* tmp = nullptr;
+  size_t bytes = 0;
+  MV_CUDA(cub::DeviceRadixSort::SortPairs(tmp, bytes, k0, k1, a.val, t.val, (int)a.nnz, 0, 32 + bits_col, g_stream));
+  MV_CUDA(cudaMalloc(&tmp, bytes));
+  MV_CUDA(cub::DeviceRadixSort::SortPairs(tmp, bytes, k0, k1, a.val, t.val, (int)a.nnz, 0, 32 + bits_col, g_stream));
+  MV_L k_tr_unpack<<<grid_for(a.nnz), MV_BLOCK, 0, g_stream>>>(a.nnz, k1, t.col);
+  MV_KERNEL_CHECK();
+  MV_CUDA(cudaStreamSynchronize(g_stream));
+  cudaFree(tmp);
+  dev_free(k0); dev_free(k1);
+  (void)bits_row;
   return MV_OK;
 }
-
 
 // ------------------------------------------------------------------ rho(D^-1 A) by power iteration
 __global__ void k_pow_init(int64_t n, const double* __restrict__ dinv, double* __restrict__ x) {
@@ -718,6 +747,7 @@ static int coarsen(mv_mesh* m, Amg* a, double theta, double* diag) {
     N.val = v;
     N.owns_A = true;
   }
+  if (st == MV_OK && R.nrows > 0 && R.nnz > 48 * R.nrows) { L.Rc = R; R = Csr(); }   // long rows: keep CSR for the warp-per-row kernel
   P.release(); R.release(); Ac.release();
   st = agree(st);
   if (st != MV_OK) {
@@ -848,6 +878,7 @@ static int replicate_tail(mv_mesh* m, Amg* a, const BuildParams& bp) {
   MV_CHECK(csr_transpose(Ploc, Rpart));
   MV_CHECK(csr_to_sell(Ploc, L.P, &L.Pval));
   MV_CHECK(csr_to_sell(Rpart, L.R, &L.Rval));
+  if (Rpart.nrows > 0 && Rpart.nnz > 48 * Rpart.nrows) { L.Rc = Rpart; Rpart = Csr(); }
   Ploc.release(); Rpart.release();
   L.reduce_next = true;
   a->coarse_inv = tail.coarse_inv;

@@ -161,6 +161,35 @@ k_sell_apply(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_p
   }
 }
 
+// y = S x with S in CSR, one warp per row (long rows: restriction on the coarse levels); the lanes' partial
+// sums are combined by a fixed-order shuffle tree, so the result is deterministic
+template <int C>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_csr_apply_warp(int64_t nrows, const int64_t* __restrict__ ptr, const int* __restrict__ col, const double* __restrict__ val,
+                 const double* __restrict__ x, int64_t ldx, double* __restrict__ y, int64_t ldy, const int* __restrict__ done) {
+  if (done && *done) return;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t row = warp0; row < nrows; row += nwarps) {
+    double acc[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) acc[c] = 0.0;
+    const int64_t b = ptr[row], e = ptr[row + 1];
+    for (int64_t t = b + lane; t < e; t += 32) {
+      const double a = val[t];
+      const double* xp = x + col[t];
+#pragma unroll
+      for (int c = 0; c < C; ++c) acc[c] = fma(a, __ldg(xp + c * ldx), acc[c]);
+    }
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const double t = warp_sum(acc[c]);
+      if (lane == 0) y[c * ldy + row] = t;
+    }
+  }
+}
+
 // x = Ainv b on the coarsest level: one warp per owned row (global row goff + row), lanes stride the N
 // columns, fixed-order shuffle sum.  Multi-GPU: b is the gathered right-hand side of all ranks.
 template <int C>
@@ -279,7 +308,11 @@ static int vcycle(mv_mesh* m, Amg* a, const double* rfine, double* z, const int*
     if (L.dist) MV_CHECK(halo_exchange_soa(L.halo, L.n, C, L.x0, L.ntot));
     MV_L k_residual<C><<<slice_grid(L.pat), MV_BLOCK, 0, g_stream>>>(L.pat.nslices, L.n, L.ntot, L.pat.slice_ptr, L.pat.cols, L.val, b, L.x0, L.dinv,
                                                                 L.r, done);
-    MV_L k_sell_apply<C, false><<<slice_grid(L.R), MV_BLOCK, 0, g_stream>>>(L.R.nslices, N.n, L.R.slice_ptr, L.R.cols, L.Rval, L.r, L.ntot, N.b, N.ntot, done);
+    if (L.Rc.ptr)
+      MV_L k_csr_apply_warp<C><<<grid_for(L.Rc.nrows * 32), MV_BLOCK, 0, g_stream>>>(L.Rc.nrows, L.Rc.ptr, L.Rc.col, L.Rc.val, L.r, L.ntot, N.b,
+                                                                              N.ntot, done);
+    else
+      MV_L k_sell_apply<C, false><<<slice_grid(L.R), MV_BLOCK, 0, g_stream>>>(L.R.nslices, N.n, L.R.slice_ptr, L.R.cols, L.Rval, L.r, L.ntot, N.b, N.ntot, done);
     if (L.reduce_next) MV_CHECK(allreduce_sum_dev(N.b, (int)(N.ntot * C)));   // replicated coarse level: sum of the ranks' partial restrictions
     b = N.b;
   }

@@ -244,18 +244,17 @@ __global__ void k_assemble_MK(const double* __restrict__ x, const int* __restric
   }
 }
 
-// Sum of `n` values with a fixed order (single block) -> out[slot]; optional squares.
-__global__ void k_sum_fixed(const double* __restrict__ v, int64_t n, double* __restrict__ out, double* __restrict__ out_sq) {
-  __shared__ double s1[MV_BLOCK], s2[MV_BLOCK];
-  double a = 0.0, b = 0.0;
-  for (int64_t i = threadIdx.x; i < n; i += blockDim.x) { double t = v[i]; a += t; b += t * t; }
-  s1[threadIdx.x] = a; s2[threadIdx.x] = b;
-  __syncthreads();
-  for (int o = blockDim.x / 2; o > 0; o >>= 1) {
-    if (threadIdx.x < o) { s1[threadIdx.x] += s1[threadIdx.x + o]; s2[threadIdx.x] += s2[threadIdx.x + o]; }
-    __syncthreads();
+// Sum of `n` values (and of their squares) in a fixed order: per-block partials + last-block ticket.
+__global__ void __launch_bounds__(MV_BLOCK)
+k_sum_fixed(const double* __restrict__ v, int64_t n, double* __restrict__ out, double* __restrict__ out_sq,
+            double* __restrict__ partials, unsigned* __restrict__ counter) {
+  double acc[2] = {0.0, 0.0};
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const double t = v[i];
+    acc[0] += t;
+    acc[1] = fma(t, t, acc[1]);
   }
-  if (threadIdx.x == 0) { out[0] = s1[0]; if (out_sq) out_sq[0] = s2[0]; }
+  grid_reduce_sum<2>(acc, partials, counter, [&](double(&t)[2]) { out[0] = t[0]; if (out_sq) out_sq[0] = t[1]; });
 }
 
 // ------------------------------------------------------------------ boundary facets
@@ -372,8 +371,12 @@ static int ingest_impl(mv_mesh* m) {
   // scalars (fixed-order sums)
   double* d_s = nullptr;
   MV_CHECK(dev_alloc(&d_s, 4));
-  MV_L k_sum_fixed<<<1, MV_BLOCK, 0, g_stream>>>(m->vol, m->Cown, d_s, nullptr);
-  MV_L k_sum_fixed<<<1, MV_BLOCK, 0, g_stream>>>(m->ml, Vown, d_s + 1, d_s + 2);
+  // work buffers of the deterministic grid reductions
+  MV_CHECK(dev_alloc(&m->red.partials, (size_t)MV_MAX_BLOCKS * MV_RED_SLOTS));
+  MV_CHECK(dev_alloc(&m->red.counter, 4));
+  MV_CUDA(cudaMemsetAsync(m->red.counter, 0, 4 * sizeof(unsigned), g_stream));
+  MV_L k_sum_fixed<<<grid_for(m->Cown), MV_BLOCK, 0, g_stream>>>(m->vol, m->Cown, d_s, nullptr, m->red.partials, m->red.counter);
+  MV_L k_sum_fixed<<<grid_for(Vown), MV_BLOCK, 0, g_stream>>>(m->ml, Vown, d_s + 1, d_s + 2, m->red.partials, m->red.counter);
   MV_KERNEL_CHECK();
   double h_s[3];
   int h_nnz_dummy = 0;
@@ -406,10 +409,6 @@ static int ingest_impl(mv_mesh* m) {
     MV_KERNEL_CHECK();
   }
   MV_CHECK(build_inverse_map(m->bf_verts, F * D, Vown, &m->v2f_ptr, &m->v2f));
-  // work buffers
-  MV_CHECK(dev_alloc(&m->red.partials, (size_t)MV_MAX_BLOCKS * MV_RED_SLOTS));
-  MV_CHECK(dev_alloc(&m->red.counter, 4));
-  MV_CUDA(cudaMemsetAsync(m->red.counter, 0, 4 * sizeof(unsigned), g_stream));
   MV_CUDA(cudaStreamSynchronize(g_stream));
   (void)V;
   return MV_OK;
@@ -490,6 +489,7 @@ extern "C" void mv_mesh_destroy(mv_mesh* m) {
   if (m->pcg.h_scal) cudaFreeHost(m->pcg.h_scal);
   dev_free(m->halo.send_idx); dev_free(m->halo.send_buf);
   dev_free(m->tmp_vec);
+  dev_free(m->cell_tmp);
   mv::amg_release(m);
   delete m;
 }

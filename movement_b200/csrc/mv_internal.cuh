@@ -150,6 +150,7 @@ struct AmgLevel {
   int degree = 1;           // Chebyshev smoother degree
   Sell P;  double* Pval = nullptr;   // [n x n_coarse]
   Sell R;  double* Rval = nullptr;   // [n_coarse x n] = P^T
+  Csr Rc;                   // the same in CSR when its rows are long (coarse levels): applied one warp per row
   double *x0 = nullptr, *x1 = nullptr, *b = nullptr, *r = nullptr, *d0 = nullptr, *d1 = nullptr;  // [ntot*C]
   int work_C = 0;
   // multi-GPU: forward halo of this level (level 0 borrows the mesh's), global numbering
@@ -213,6 +214,7 @@ struct mv_mesh {
   mv::PcgWork pcg;
   mv::Halo halo;
   double* tmp_vec = nullptr;   // [V*MV_MAX_COMP]
+  double* cell_tmp = nullptr;  // [C*(dim+1)] per-cell vertex contributions of the cell-major assemblies
   // preconditioner of the stiffness-type operators: MV_PC_JACOBI or MV_PC_AMG
   int pc_kind = 1;
   std::vector<mv::Amg*> amg;   // cached hierarchies (one per operator / constrained set)

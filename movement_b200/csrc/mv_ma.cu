@@ -234,6 +234,72 @@ k_assemble_a(const double* __restrict__ xi, const int* __restrict__ cells, const
 }
 
 
+// Cell-major variant of the same assembly: one thread per cell evaluates the quadrature ONCE and stores the
+// d+1 vertex contributions; a vertex pass then adds them in ascending cell order (the order of v2c), so the
+// result is deterministic and every (m, H) value is gathered once per cell instead of once per (vertex, cell)
+// pair: 4x (3D) less gather traffic than k_assemble_a, which ncu showed to be bound by it (24 ms at 256^3).
+template <int D>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_assemble_a_cells(const int* __restrict__ cells, const double* __restrict__ vol, int64_t ncells, const double* __restrict__ mon,
+                   const double* __restrict__ H, double* __restrict__ contrib) {
+  for (int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; c < ncells; c += (int64_t)gridDim.x * blockDim.x) {
+    int cv[D + 1];
+    load_cell<D>(cells, c, cv);
+    double mj[D + 1], Hj[D + 1][D][D];
+#pragma unroll
+    for (int j = 0; j <= D; ++j) {
+      mj[j] = __ldg(&mon[cv[j]]);
+#pragma unroll
+      for (int a = 0; a < D; ++a)
+#pragma unroll
+        for (int b = 0; b < D; ++b) Hj[j][a][b] = __ldg(&H[(int64_t)cv[j] * D * D + a * D + b]);
+    }
+    double cell[D + 1];
+#pragma unroll
+    for (int j = 0; j <= D; ++j) cell[j] = 0.0;
+#pragma unroll 2
+    for (int q = 0; q < Quad<D>::Q; ++q) {
+      double mq = 0.0, hq[D][D];
+#pragma unroll
+      for (int a = 0; a < D; ++a)
+#pragma unroll
+        for (int b = 0; b < D; ++b) hq[a][b] = 0.0;
+      double lam[D + 1];
+#pragma unroll
+      for (int j = 0; j <= D; ++j) {
+        const double l = Quad<D>::lam(q, j);
+        lam[j] = l;
+        mq = fma(l, mj[j], mq);
+#pragma unroll
+        for (int a = 0; a < D; ++a)
+#pragma unroll
+          for (int b = 0; b < D; ++b) hq[a][b] = fma(l, Hj[j][a][b], hq[a][b]);
+      }
+      const double f = mq * det_I_plus(hq);
+      const double wq = Quad<D>::w(q);
+#pragma unroll
+      for (int j = 0; j <= D; ++j) cell[j] = fma(wq * lam[j], f, cell[j]);
+    }
+    const double vk = __ldg(&vol[c]);
+#pragma unroll
+    for (int j = 0; j <= D; ++j) contrib[c * (D + 1) + j] = vk * cell[j];
+  }
+}
+__global__ void __launch_bounds__(MV_BLOCK)
+k_assemble_a_gather(const int* __restrict__ v2c_ptr, const int* __restrict__ v2c, int64_t nrows, const double* __restrict__ contrib,
+                    double* __restrict__ a_out, double* __restrict__ partials, unsigned* __restrict__ counter,
+                    double* __restrict__ dscal) {
+  double tot[1] = {0.0};
+  for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < nrows; v += (int64_t)gridDim.x * blockDim.x) {
+    double acc = 0.0;
+    const int tb = __ldg(&v2c_ptr[v]), te = __ldg(&v2c_ptr[v + 1]);
+    for (int t = tb; t < te; ++t) acc += __ldg(&contrib[__ldg(&v2c[t])]);
+    a_out[v] = acc;
+    tot[0] += acc;
+  }
+  grid_reduce_sum<1>(tot, partials, counter, [&](double(&t)[1]) { dscal[D_SUMA] = t[0]; });
+}
+
 // cof(I + h) : dh  (directional derivative of det(I + h) in direction dh)
 __device__ __forceinline__ double cof_contract(const double (&h)[2][2], const double (&dh)[2][2]) {
   return (1.0 + h[1][1]) * dh[0][0] - h[1][0] * dh[0][1] - h[0][1] * dh[1][0] + (1.0 + h[0][0]) * dh[1][1];
@@ -635,13 +701,14 @@ int hess_rhs_dev(mv_mesh* m, const double* phi, double* c) {
   return MV_OK;
 }
 int assemble_a_dev(mv_mesh* m, const double* mon, const double* H, double* a, double* dscal) {
-  const int grid = grid_for(m->Vown);
+  if (!m->cell_tmp) MV_CHECK(dev_alloc(&m->cell_tmp, (size_t)m->C * (m->dim + 1)));
+  const int gc = grid_for(m->C), gv = grid_for(m->Vown);
   if (m->dim == 2)
-    MV_L k_assemble_a<2><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->Vown, mon, H, a,
-                                                     m->red.partials, m->red.counter, dscal);
+    MV_L k_assemble_a_cells<2><<<gc, MV_BLOCK, 0, g_stream>>>(m->cells, m->vol, m->C, mon, H, m->cell_tmp);
   else
-    MV_L k_assemble_a<3><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->Vown, mon, H, a,
-                                                     m->red.partials, m->red.counter, dscal);
+    MV_L k_assemble_a_cells<3><<<gc, MV_BLOCK, 0, g_stream>>>(m->cells, m->vol, m->C, mon, H, m->cell_tmp);
+  MV_L k_assemble_a_gather<<<gv, MV_BLOCK, 0, g_stream>>>(m->v2c_ptr, m->v2c, m->Vown, m->cell_tmp, a, m->red.partials, m->red.counter,
+                                                     dscal);
   MV_KERNEL_CHECK();
   return MV_OK;
 }
