@@ -45,6 +45,8 @@ def parse():
     ap.add_argument("--cpu-steps", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--mass-solver", default="chebyshev", choices=["chebyshev", "pcg"],
+                    help="solver of the consistent-mass systems (A1, A8): fused Chebyshev (default) or Jacobi-PCG")
     return ap.parse_args()
 
 
@@ -185,6 +187,8 @@ def run_ours(args):
     rank, world = parallel.rank(), parallel.size()
     dev = torch.cuda.current_device()
     lib = L.load()
+    cheb = args.mass_solver == "chebyshev"
+    L.check(lib.mv_set_mass_solver(L.MV_MASS_CHEBYSHEV if cheb else L.MV_MASS_PCG))
     n = args.n
     quiet = mv.mover  # silence the per-iteration prints inside the timed region
     quiet._print = lambda *a, **k: None
@@ -255,37 +259,51 @@ def run_ours(args):
     cg = np.array(mover.cg_iterations[-args.steps:])
     value = Vglobal * args.steps / (ms * 1e-3)
 
-    # ---- roofline of the dominant kernel: the SELL-32 SpMV of the PCG solves, timed live per launch with CUDA
-    # events on the launching stream (mv_prof_*), by number of right-hand sides C: 3 = L2 projection (mass),
-    # 1 = Poisson (stiffness), 9 = Hessian recovery (mass).  Algorithmic bytes per launch:
-    # 12 B per stored non-zero + 4 B slice pointer per row + read p / write q: 16*C B per row.
+    # ---- roofline of the dominant kernel: the matrix-streaming kernels of the inner solves, timed live per launch with
+    # CUDA events on the launching stream (mv_prof_*), by number of right-hand sides C: 3 = L2 projection (mass),
+    # 1 = Poisson (stiffness, SpMV of the multigrid-preconditioned CG), 9 = Hessian recovery (mass).
+    # Algorithmic bytes per launch: 12 B per stored non-zero + 4 B slice pointer per row, plus
+    #   SpMV (+ fused p.q):            read p, write q                               = 16 C B per row
+    #   fused Chebyshev iteration:     dinv, b, x_{k-1} in, x_{k+1} out, own x_k     = 8 + 32 C B per row (+2 B mask)
     dm = mover._dm
     peak, peak_src = peaks()
+    have_mask = bool(getattr(mover, "_have_bc", True))
     classes = {}
     for c in (1, 3, 9):
         if spmv_cnt[c] > 0:
-            alg = 12.0 * dm.nnz + (4.0 + 16.0 * c) * dm.Vown
+            fused = cheb and c != 1
+            per_row = (4.0 + 8.0 + 32.0 * c + (2.0 if (c == 3 and have_mask) else 0.0)) if fused else (4.0 + 16.0 * c)
+            alg = 12.0 * dm.nnz + per_row * dm.Vown
             avg = spmv_ms[c] / spmv_cnt[c]
-            classes[c] = {"rhs": c, "launches_timed": int(spmv_cnt[c]), "avg_launch_ms": avg, "algorithmic_bytes_per_launch": alg,
+            classes[c] = {"rhs": c, "kernel": "k_cheb_soa" if fused else "k_spmv_soa", "launches_timed": int(spmv_cnt[c]),
+                          "avg_launch_ms": avg, "algorithmic_bytes_per_launch": alg,
                           "achieved_GBs": alg / (avg * 1e-3) / 1e9, "share_of_step": spmv_ms[c] / ms}
     dom = max(classes, key=lambda c: classes[c]["share_of_step"])
     traffic = ncu_traffic()
-    kname = {1: "k_spmv_soa<1,true> (stiffness matrix, Poisson PCG)", 3: "k_spmv_soa<3,true> (mass matrix, L2 projection of grad phi)",
-             9: "k_spmv_soa<9,true> (mass matrix, Hessian recovery)"}[dom]
-    tr = (traffic or {}).get(str(dom)) or {}
-    roofline = {"bound": "hbm", "kernel": "SELL-32 SpMV + fused p.q, " + kname,
+    if cheb:
+        kname = {1: "SELL-32 SpMV + fused p.q, k_spmv_soa<1,true> (stiffness matrix, Poisson PCG)",
+                 3: "fused Chebyshev iteration, k_cheb_soa<3,...> (mass matrix, L2 projection of grad phi)",
+                 9: "fused Chebyshev iteration, k_cheb_soa<9,...> (mass matrix, Hessian recovery)"}[dom]
+    else:
+        kname = "SELL-32 SpMV + fused p.q, " + {1: "k_spmv_soa<1,true> (stiffness matrix, Poisson PCG)",
+                                                 3: "k_spmv_soa<3,true> (mass matrix, L2 projection of grad phi)",
+                                                 9: "k_spmv_soa<9,true> (mass matrix, Hessian recovery)"}[dom]
+    tr = (traffic or {}).get(("cheb" if cheb and dom != 1 else "spmv") + str(dom)) or {}
+    roofline = {"bound": "hbm", "kernel": kname,
                 "achieved": classes[dom]["achieved_GBs"], "peak": peak, "unit": "GB/s", "frac": classes[dom]["achieved_GBs"] / peak,
                 "peak_source": peak_src, "frac_of_nominal_8TBs": classes[dom]["achieved_GBs"] / 8000.0,
                 "algorithmic_bytes_per_launch": classes[dom]["algorithmic_bytes_per_launch"],
                 "avg_launch_ms": classes[dom]["avg_launch_ms"], "launches_timed": classes[dom]["launches_timed"],
                 "share_of_step": classes[dom]["share_of_step"],
                 "traffic": tr.get("dram_bytes_per_launch"), "traffic_source": tr.get("source"),
-                "all_spmv_classes": [classes[c] for c in sorted(classes)]}
-    # whole-step accounting with the SURVEY 8d byte model B_cg(c) = 12 nnz + 4 + 104 c per vertex per PCG iteration
+                "all_matrix_streaming_classes": [classes[c] for c in sorted(classes)]}
+    # whole-step accounting with the SURVEY 8d byte model per vertex per inner iteration: B_cg(c) = 12 nnz + 4 + 104 c
+    # for a CG iteration, B_cheb(c) = 12 nnz + 12 + 32 c for a fused Chebyshev iteration
     nnzv = dm.nnz / dm.Vown
     d = 3
     bcg = lambda c: 12 * nnzv + 4 + 104 * c  # noqa: E731
-    step_bytes = float(np.mean(cg[:, 0] * bcg(d) + cg[:, 1] * bcg(1) + cg[:, 2] * bcg(d * d))) * Vglobal
+    bmass = (lambda c: 12 * nnzv + 12 + 32 * c) if cheb else bcg  # noqa: E731
+    step_bytes = float(np.mean(cg[:, 0] * bmass(d) + cg[:, 1] * bcg(1) + cg[:, 2] * bmass(d * d))) * Vglobal
     step_gbs = step_bytes / (ms / args.steps * 1e-3) / 1e9
 
     # ---- end to end through the public API from host buffers ---------------------------------------
@@ -322,7 +340,8 @@ def run_ours(args):
                 "config": {"workload": workload_name(n), "n": n, "vertices": Vglobal, "cells": Cglobal,
                            "parallelism": f"vertex-owner slab partition x{world}" if world > 1 else "single GPU",
                            "l2": "inputs larger than L2 (matrix stream %.1f GB per SpMV)" % (12.0 * dm.nnz / 1e9),
-                           "cg_iterations_per_step(l2,poisson,hessian)": [float(x) for x in cg.mean(axis=0)],
+                           "mass_solver": "fused Chebyshev (Wathen interval), measured stop at rtol 1e-12" if cheb else "Jacobi-PCG",
+                           "inner_iterations_per_step(l2,poisson,hessian)": [float(x) for x in cg.mean(axis=0)],
                            "residual_after_timed_steps": residuals[-1]},
                 "roofline": roofline,
                 "step_model": {"bytes_per_step": step_bytes, "GBs": step_gbs, "frac_of_peak": step_gbs / (peak * world)},

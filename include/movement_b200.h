@@ -47,6 +47,7 @@ enum { MV_OP_MASS = 0, MV_OP_STIFFNESS = 1, MV_OP_MASS_PLUS_STIFFNESS = 2 };
 /* preconditioner of the stiffness-type operators (the mass solves always use Jacobi):
  * replaces the `pc_type` choices of movement/solver_parameters.py:62-71 (bjacobi/ilu, gamg) */
 enum { MV_PC_JACOBI = 0, MV_PC_AMG = 1 };
+enum { MV_MASS_PCG = 0, MV_MASS_CHEBYSHEV = 1 };
 
 /* built-in (fused) monitor functions -- replaces: movement/monitor.py:138-143,
  * test/monitors.py:9-16, demos/monge_ampere_helmholtz.py:54-61,115-122,
@@ -151,6 +152,12 @@ int mv_pcg_solve(mv_mesh* m, int op, int ncomp, const double* rhs, double* x,
  * laplacian_smoothing.py:55-77.  With MV_PC_AMG the stopping norm of mv_pcg_solve is
  * sqrt(r.M^-1 r), M^-1 = one V-cycle.                                                      */
 int mv_set_preconditioner(mv_mesh* m, int kind);
+/* Solver behind MV_OP_MASS in mv_pcg_solve and the Monge-Ampere mass solves (replaces: KSP cg + bjacobi/ilu,
+ * movement/solver_parameters.py:62-66 at monge_ampere.py:340,483).  MV_MASS_CHEBYSHEV (default): one fused kernel
+ * per iteration on Wathen's a-priori interval [1/2, 1 + d/2] of diag(M)^-1 M for P1 simplices, same measured
+ * stopping rule as the PCG (sqrt(r.D^-1 r) <= max(rtol*ref, atol)); MV_MASS_PCG: Jacobi-preconditioned CG.
+ * Process-wide.                                                                                              */
+int mv_set_mass_solver(int kind);
 /* Hierarchy of the cached multigrid preconditioner of `op` (after a solve): info[0] = levels
  * (0 = none built), info[1] = rows of the coarsest level, info[2] = 1 if that level is solved
  * densely, then (rows, nnz) per level; rho[l] = bound of spec(D^-1 A_l); both may be NULL.   */

@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libmovement_b200.so")
 MV_OK, MV_ERR_BADARG, MV_ERR_CUDA, MV_ERR_NOT_CONVERGED, MV_ERR_VALENCE, MV_ERR_COMM, MV_ERR_UNSUPPORTED = range(7)
 MV_OP_MASS, MV_OP_STIFFNESS, MV_OP_MASS_PLUS_STIFFNESS = 0, 1, 2
 MV_PC_JACOBI, MV_PC_AMG = 0, 1
+MV_MASS_PCG, MV_MASS_CHEBYSHEV = 0, 1
 MV_MON_CONST, MV_MON_BALL, MV_MON_BALL_RAW, MV_MON_GAUSS_HESS, MV_MON_SINATAN3, MV_MON_USER = 0, 1, 2, 3, 4, 100
 (MV_F_XI, MV_F_X, MV_F_PHI, MV_F_PHI_OLD, MV_F_H, MV_F_H_OLD, MV_F_GRAD_PHI, MV_F_MONITOR, MV_F_VOLUME,
  MV_F_ORIG_VOLUME, MV_F_RESIDUAL) = range(11)
@@ -44,6 +45,7 @@ SIGNATURES = {
     "mv_spmv": (_i, [_vp, _i, _i, _vp, _vp]),
     "mv_pcg_solve": (_i, [_vp, _i, _i, _vp, _vp, _vp, _d, _d, _i, _i, _pi, _pd]),
     "mv_set_preconditioner": (_i, [_vp, _i]),
+    "mv_set_mass_solver": (_i, [_i]),
     "mv_amg_info": (_i, [_vp, _i, _pi64, _i, _pd, _pd]),
     "mv_amg_level_get": (_i, [_vp, _i, _i, _i, _pi64, _vp, _vp, _vp, _vp]),
     "mv_ma_create": (_i, [_vp, C.POINTER(_vp)]),

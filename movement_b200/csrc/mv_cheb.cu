@@ -1,0 +1,340 @@
+// Consistent-mass solves by a FUSED Chebyshev iteration: one kernel per iteration, no inner products.
+//
+// replaces: PETSc KSP `cg` + `bjacobi/ilu` (movement/solver_parameters.py:62-66) at
+//           movement/monge_ampere.py:340 (d mass solves, L2 projection of grad(phi)) and :483
+//           (d*d mass solves, Hessian recovery).
+//
+// Why not CG here: for P1 simplices the Jacobi-scaled consistent mass matrix has its spectrum inside
+// [1/2, 1 + d/2] on ANY mesh (Wathen 1987, element-by-element bound; a principal submatrix -- Dirichlet
+// rows removed -- interlaces, so the bound survives the masks of monge_ampere.py:258-272).  With the
+// interval known a priori the optimal polynomial is Chebyshev's, whose coefficients are host constants:
+//     x_{k+1} = x_k + a_k (x_k - x_{k-1}) + c_k D^-1 (b - M x_k)
+// Every term is local to the row except the gather of x_k, so the whole iteration is ONE kernel that
+// streams the matrix once and touches 32 B per component per vertex (b, x_{k-1} in, x_{k+1} out over
+// x_{k-1}, own x_k) against 104 B for a CG iteration (SpMV + update + direction): per vertex and
+// iteration  B_cheb(c) = 12 nnz + 4 + 8 + 32 c  (3D: 480 B at c = 9; CG: 1120 B).  Chebyshev needs
+// ~25 % more iterations than CG for the same reduction (it cannot exploit the discrete spectrum), so a
+// solve moves about half the bytes, launches a third of the kernels, and on several GPUs needs no
+// allreduce except at the sampled convergence checks.
+//
+// Convergence is MEASURED, not assumed: checked launches also reduce r_k . D^-1 r_k per component
+// (the residual of their input iterate, deterministic grid reduction) and apply the stopping rule of
+// mv_pcg_solve, sqrt(r.D^-1 r) <= max(rtol * ref, atol), ref = max(b.D^-1 b, r_0.D^-1 r_0).  The iterate
+// returned is the one whose residual passed the test.
+#include <math.h>
+
+#include "mv_internal.cuh"
+
+namespace mv {
+
+// Solver selection for MV_OP_MASS (mv_set_mass_solver): 1 = fused Chebyshev (default), 0 = Jacobi-PCG.
+int g_mass_solver = 1;
+
+enum { CHEB_PLAIN = 0, CHEB_CHECK = 1, CHEB_FIRST = 2 };
+
+// flags: [0] done, [1] index k of the verified iterate, [2] breakdown (NaN)
+template <int C>
+__device__ __forceinline__ void cheb_decide(int k, double* __restrict__ scal, int* __restrict__ flags) {
+  bool all = true;
+  for (int c = 0; c < C; ++c) {
+    const double rz = scal[SC(S_RZ, c)];
+    all = all && (rz <= scal[SC(S_THR, c)]);
+    if (!(rz == rz)) flags[2] = 1;
+  }
+  if (all || flags[2]) { flags[0] = 1; flags[1] = k; }
+}
+template <int C>
+__device__ __forceinline__ void cheb_setup(double rtol, double atol, double* __restrict__ scal) {
+  for (int c = 0; c < C; ++c) {
+    const double ref = fmax(scal[SC(S_RZ, c)], scal[SC(S_BB, c)]);
+    scal[SC(S_REF, c)] = ref;
+    scal[SC(S_THR, c)] = fmax(rtol * rtol * ref, atol * atol);
+  }
+}
+// multi-GPU: the sums were allreduced, now decide
+template <int C>
+__global__ void k_cheb_post(int k, int first, double rtol, double atol, double* __restrict__ scal, int* __restrict__ flags) {
+  if (flags[0]) return;
+  if (first) cheb_setup<C>(rtol, atol, scal);
+  cheb_decide<C>(k, scal, flags);
+}
+
+// One Chebyshev iteration.  xin = x_k ([C][ld], ghosts valid), xout holds x_{k-1} on entry and x_{k+1} on exit
+// (owned rows), b is component-major [C][ld].  MODE: CHEB_CHECK also sums r_k.D^-1 r_k, CHEB_FIRST (k = 0,
+// a = 0, xout not read) sums b.D^-1 b as well and fixes the thresholds.  LOCAL: single GPU, decide in-kernel.
+//
+// Work split: a CTA of 32*NG*SPB threads owns SPB consecutive slices; the NG = C/CG warps of one slice each
+// carry CG components (ncu, round 1: with all 9 components in one thread the kernel needs 64 registers,
+// 4 CTAs/SM, and keeps too few gathers in flight -- 35 % of any unit, long-scoreboard bound).  The warps of a
+// slice read the same column/value stream; the first one brings it from HBM, the others hit L1.
+template <int C, int CG, int SPB, int MINB, int MODE, bool LOCAL>
+__global__ void __launch_bounds__(32 * (C / CG) * SPB, MINB)
+k_cheb_soa(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
+           const double* __restrict__ val, const double* __restrict__ dinv, const uint16_t* __restrict__ mask,
+           const double* __restrict__ b, const double* __restrict__ xin, double* __restrict__ xout, int64_t ld,
+           double ak, double ck, int k, double rtol, double atol, int* __restrict__ flags,
+           double* __restrict__ partials, unsigned* __restrict__ counter, double* __restrict__ scal) {
+  constexpr int NG = C / CG, NW = NG * SPB;
+  static_assert(C % CG == 0, "component groups must tile C");
+  if (MODE != CHEB_FIRST && *flags) return;
+  constexpr int NS = MODE == CHEB_FIRST ? 2 * CG : (MODE == CHEB_CHECK ? CG : 1);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int g = wid % NG, sl = wid / NG;
+  const int64_t cb = (int64_t)g * CG * ld;   // offset of this warp's first component
+  b += cb; xin += cb; xout += cb;
+  double sum[NS];
+#pragma unroll
+  for (int c = 0; c < NS; ++c) sum[c] = 0.0;
+  const int64_t ngroups = (nslices + SPB - 1) / SPB;
+  for (int64_t sg = blockIdx.x; sg < ngroups; sg += gridDim.x) {
+    const int64_t s = sg * SPB + sl;
+    if (s >= nslices) continue;
+    const int64_t base = __ldg(&slice_ptr[s]);
+    const int w = (int)((__ldg(&slice_ptr[s + 1]) - base) >> 5);
+    const int64_t row = s * MV_SLICE + lane;
+    const bool live = row < nrows;
+    const int64_t rr = live ? row : nrows - 1;
+    const int* cp = cols + base + lane;
+    const double* vp = val + base + lane;
+    // the streamed operands of this row are requested before the gathers so that they are in flight together
+    double bv[CG], xo[CG];
+#pragma unroll
+    for (int c = 0; c < CG; ++c) {
+      bv[c] = __ldcs(&b[c * ld + rr]);
+      xo[c] = MODE == CHEB_FIRST ? 0.0 : __ldcs(&xout[c * ld + rr]);
+    }
+    const double di = __ldg(&dinv[rr]);
+    const unsigned mk = mask ? (unsigned)__ldg(&mask[rr]) >> (g * CG) : 0u;
+    double acc[CG];
+#pragma unroll
+    for (int c = 0; c < CG; ++c) acc[c] = 0.0;
+    constexpr int KB = CG >= 3 ? 5 : 8;
+    for (int k0 = 0; k0 < w; k0 += KB) {
+      int col[KB];
+      double a[KB];
+#pragma unroll
+      for (int j = 0; j < KB; ++j) {
+        const bool in = k0 + j < w;
+        // NG > 1: default caching, the sibling warps of this slice re-read the stream from L1
+        col[j] = in ? (NG > 1 ? __ldg(cp + (k0 + j) * MV_SLICE) : __ldcs(cp + (k0 + j) * MV_SLICE)) : 0;
+        a[j] = in ? (NG > 1 ? __ldg(vp + (k0 + j) * MV_SLICE) : __ldcs(vp + (k0 + j) * MV_SLICE)) : 0.0;
+      }
+#pragma unroll
+      for (int j = 0; j < KB; ++j) {
+        const double* xp = xin + col[j];
+#pragma unroll
+        for (int c = 0; c < CG; ++c) acc[c] = fma(a[j], __ldg(xp + c * ld), acc[c]);
+      }
+    }
+    if (live) {
+#pragma unroll
+      for (int c = 0; c < CG; ++c) {
+        const bool fix = (mk >> c) & 1u;
+        const double xk = __ldg(&xin[c * ld + row]);
+        const double r = fix ? 0.0 : bv[c] - acc[c];
+        const double z = di * r;
+        // x_{k+1} = x_k + a_k (x_k - x_{k-1}) + c_k z_k ; a constrained dof keeps its value
+        const double xn = fix ? xk : xk + (MODE == CHEB_FIRST ? 0.0 : ak * (xk - xo[c])) + ck * z;
+        xout[c * ld + row] = xn;
+        if (MODE != CHEB_PLAIN) sum[c] = fma(r, z, sum[c]);
+        if (MODE == CHEB_FIRST) sum[CG + c] = fix ? sum[CG + c] : fma(bv[c] * di, bv[c], sum[CG + c]);
+      }
+    }
+  }
+  if (MODE == CHEB_PLAIN) return;
+  // deterministic grid reduction (same scheme as grid_reduce_sum, with the component of a slot depending on the warp)
+  constexpr int NT = MODE == CHEB_FIRST ? 2 * C : C;   // totals: [kind][component]
+  __shared__ double s_w[NW][NS];
+  __shared__ double s_tot[MV_RED_SLOTS];
+  __shared__ bool s_last;
+#pragma unroll
+  for (int n = 0; n < NS; ++n) {
+    const double t = warp_sum(sum[n]);
+    if (lane == 0) s_w[wid][n] = t;
+  }
+  __syncthreads();
+  if (threadIdx.x < NT) {
+    const int kind = threadIdx.x / C, c = threadIdx.x % C, gg = c / CG, j = c % CG;
+    double t = 0.0;
+    for (int q = 0; q < SPB; ++q) t += s_w[q * NG + gg][kind * CG + j];
+    partials[(size_t)blockIdx.x * MV_RED_SLOTS + threadIdx.x] = t;
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(counter, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  // last block: warp n sums slot n over the blocks in a fixed order
+  for (int n = wid; n < NT; n += NW) {
+    double t = 0.0;
+    for (unsigned q = lane; q < gridDim.x; q += 32) t += __ldcg(&partials[(size_t)q * MV_RED_SLOTS + n]);
+    t = warp_sum(t);
+    if (lane == 0) s_tot[n] = t;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    *counter = 0u;
+    for (int c = 0; c < C; ++c) {
+      scal[SC(S_RZ, c)] = s_tot[c];
+      if (MODE == CHEB_FIRST) scal[SC(S_BB, c)] = s_tot[C + c];
+    }
+    if (LOCAL) {
+      if (MODE == CHEB_FIRST) cheb_setup<C>(rtol, atol, scal);
+      cheb_decide<C>(k, scal, flags);
+    }
+  }
+}
+
+
+// Wathen's interval for diag(M)^-1 M, P1 simplices in d dimensions.
+static inline void mass_spectrum(int dim, double* lmin, double* lmax) {
+  *lmin = 0.5;
+  *lmax = 1.0 + 0.5 * dim;
+}
+
+template <int C, int CG, int SPB, int MINB>
+struct ChebLaunch {
+  static int grid(int64_t nslices) {
+    static int per_sm = 0;
+    if (per_sm == 0) {
+      int nb = 0;
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_cheb_soa<C, CG, SPB, MINB, CHEB_CHECK, true>, 32 * (C / CG) * SPB, 0) !=
+              cudaSuccess || nb < 1)
+        nb = 1;
+      per_sm = nb;
+    }
+    const int64_t need = (nslices + SPB - 1) / SPB;
+    int64_t g = (int64_t)g_nsm * per_sm;
+    if (g > MV_MAX_BLOCKS) g = MV_MAX_BLOCKS;
+    if (g > need) g = need;
+    return (int)(g < 1 ? 1 : g);
+  }
+  static int run(mv_mesh* m, const double* val, const double* dinv, const uint16_t* mask, const double* b, const double* xin,
+                 double* xout, int64_t ld, double ak, double ck, int k, int mode, bool local, double rtol, double atol) {
+    const Sell& p = m->pat;
+    const int gr = grid(p.nslices);
+    constexpr int NT = 32 * (C / CG) * SPB;
+    PcgWork& w = m->pcg;
+#define CHEB_GO(MODE, LOC)                                                                                                  \
+  MV_L k_cheb_soa<C, CG, SPB, MINB, MODE, LOC><<<gr, NT, 0, g_stream>>>(p.nslices, p.nrows, p.slice_ptr, p.cols, val, dinv, mask, b, \
+                                                                  xin, xout, ld, ak, ck, k, rtol, atol, w.flags,            \
+                                                                  m->red.partials, m->red.counter, w.scal)
+    if (mode == CHEB_PLAIN) CHEB_GO(CHEB_PLAIN, true);
+    else if (mode == CHEB_CHECK) { if (local) CHEB_GO(CHEB_CHECK, true); else CHEB_GO(CHEB_CHECK, false); }
+    else { if (local) CHEB_GO(CHEB_FIRST, true); else CHEB_GO(CHEB_FIRST, false); }
+#undef CHEB_GO
+    MV_KERNEL_CHECK();
+    return MV_OK;
+  }
+};
+
+template <int C, int CG, int SPB, int MINB>
+static int cheb_soa(mv_mesh* m, const double* val, const double* dinv, const double* rhs, double* x, const uint16_t* mask,
+                    double rtol, double atol, int maxit, int* iters, double* relres) {
+  MV_CHECK(ensure_pcg_workspace(m));
+  PcgWork& w = m->pcg;
+  const int64_t n = m->Vown, ld = m->V;
+  const bool dist = comm_active();
+  double lmin, lmax;
+  mass_spectrum(m->dim, &lmin, &lmax);
+  const double theta = 0.5 * (lmax + lmin), delta = 0.5 * (lmax - lmin), sigma1 = theta / delta;
+
+  double* X[2] = {w.xs, w.p};   // both span the ghosts
+  double* bs = w.r;
+  MV_CHECK(aos_to_soa(C, n, x, X[0], ld));
+  if (rhs) MV_CHECK(aos_to_soa(C, n, rhs, bs, ld));
+  else MV_CUDA(cudaMemsetAsync(bs, 0, (size_t)ld * C * sizeof(double), g_stream));
+  MV_CUDA(cudaMemsetAsync(w.flags, 0, 4 * sizeof(int), g_stream));
+
+  const int kmin = 6;           // first sampled convergence check (after the k = 0 launch, which sets the thresholds)
+  const int kdense = 18;        // from here on every launch checks (the bound 2 rho^k reaches 1e-12 at k = 26..30)
+  int k = 0;
+  double rho = 1.0 / sigma1;    // rho_{k-1}
+  w.h_flags[0] = 0;
+  int batch = 20;
+  while (true) {
+    const int kend = k + batch < maxit ? k + batch : maxit;
+    for (; k < kend; ++k) {
+      double ak = 0.0, ck = 1.0 / theta;
+      if (k > 0) {
+        const double rk = 1.0 / (2.0 * sigma1 - rho);
+        ak = rk * rho;
+        ck = 2.0 * rk / delta;
+        rho = rk;
+      }
+      const int mode = k == 0 ? CHEB_FIRST : ((k >= kdense || (k >= kmin && ((k - kmin) & 1) == 0)) ? CHEB_CHECK : CHEB_PLAIN);
+      if (dist) MV_CHECK(halo_exchange_soa(m->halo, n, C, X[k & 1], ld));
+      const int pslot = prof_begin(C);
+      MV_CHECK((ChebLaunch<C, CG, SPB, MINB>::run(m, val, dinv, mask, bs, X[k & 1], X[(k + 1) & 1], ld, ak, ck, k, mode, !dist, rtol, atol)));
+      prof_end(pslot);
+      if (dist && mode != CHEB_PLAIN) {
+        MV_CHECK(allreduce_sum_dev(w.scal + SC(S_RZ, 0), C));
+        if (mode == CHEB_FIRST) MV_CHECK(allreduce_sum_dev(w.scal + SC(S_BB, 0), C));
+        MV_L k_cheb_post<C><<<1, 1, 0, g_stream>>>(k, mode == CHEB_FIRST, rtol, atol, w.scal, w.flags);
+        MV_KERNEL_CHECK();
+      }
+    }
+    MV_CUDA(cudaMemcpyAsync(w.h_flags, w.flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, g_stream));
+    MV_CUDA(cudaStreamSynchronize(g_stream));
+    if (g_prof.used) prof_drain();
+    if (w.h_flags[0] || k >= maxit) break;
+    batch = 8;
+  }
+  const int done = w.h_flags[0], kv = done ? w.h_flags[1] : k, breakdown = w.h_flags[2];
+  g_prof.pcg_iters[C & 15] += kv;
+  // the verified iterate x_kv was the input of launch kv
+  MV_CHECK(soa_to_aos(C, n, X[kv & 1], ld, x));
+  if (iters) *iters = kv;
+  if (relres) {
+    MV_CUDA(cudaMemcpyAsync(w.h_scal, w.scal, S_NSLOTS * 16 * sizeof(double), cudaMemcpyDeviceToHost, g_stream));
+    MV_CUDA(cudaStreamSynchronize(g_stream));
+    for (int c = 0; c < C; ++c) {
+      const double ref = w.h_scal[SC(S_REF, c)];
+      relres[c] = ref > 0.0 ? sqrt(w.h_scal[SC(S_RZ, c)] / ref) : 0.0;
+    }
+  }
+  if (breakdown) {
+    set_error("chebyshev: breakdown (NaN) after %d iterations", kv);
+    return MV_ERR_NOT_CONVERGED;
+  }
+  if (!done) {
+    set_error("chebyshev: not converged in %d iterations", maxit);
+    return MV_ERR_NOT_CONVERGED;
+  }
+  return MV_OK;
+}
+
+int cheb_mass_solve(mv_mesh* m, int ncomp, const double* val, const double* dinv, const double* rhs, double* x,
+                    const uint16_t* mask, double rtol, double atol, int maxit, int* iters, double* relres) {
+  static int var = -1;   // experiment knob: occupancy target (min CTAs/SM -> register cap)
+  if (var < 0) { const char* e = getenv("MV_CHEB_VAR"); var = e ? atoi(e) : 0; }
+#define CHEB_ARGS m, val, dinv, rhs, x, mask, rtol, atol, maxit, iters, relres
+  // defaults = the fastest of the variants measured at 256^3 (B200, round 1): C = 1: 64 registers, 32 warps/SM,
+  // 0.64 ms; C = 3: 40 registers, 48 warps/SM, 0.97 ms; C = 9: three 3-component warps per slice, 40 registers, 2.9 ms
+  switch (ncomp) {
+    case 1:
+      if (var == 1) return cheb_soa<1, 1, 8, 6>(CHEB_ARGS);
+      return cheb_soa<1, 1, 8, 4>(CHEB_ARGS);
+    case 2: return cheb_soa<2, 2, 8, 4>(CHEB_ARGS);
+    case 3:
+      if (var == 1) return cheb_soa<3, 3, 8, 4>(CHEB_ARGS);
+      return cheb_soa<3, 3, 8, 6>(CHEB_ARGS);
+    case 4: return cheb_soa<4, 4, 8, 4>(CHEB_ARGS);
+    case 9:
+      if (var == 1) return cheb_soa<9, 3, 2, 5>(CHEB_ARGS);
+      if (var == 4) return cheb_soa<9, 9, 8, 4>(CHEB_ARGS);
+      return cheb_soa<9, 3, 2, 8>(CHEB_ARGS);
+  }
+#undef CHEB_ARGS
+  set_error("chebyshev: unsupported ncomp %d (1,2,3,4,9)", ncomp);
+  return MV_ERR_UNSUPPORTED;
+}
+
+}  // namespace mv
+
+extern "C" int mv_set_mass_solver(int kind) {
+  if (kind != MV_MASS_PCG && kind != MV_MASS_CHEBYSHEV) return MV_ERR_BADARG;
+  mv::g_mass_solver = kind;
+  return MV_OK;
+}

@@ -269,6 +269,12 @@ int pcg_solve(mv_mesh* m, int op, int ncomp, const double* rhs, double* x, const
 int spmv(mv_mesh* m, int op, int ncomp, const double* x, double* y);
 int pcg_solve_soa(mv_mesh* m, int ncomp, const double* val, const double* dinv, const double* rhs, double* x, const uint16_t* mask,
                   double rtol, double atol, int maxit, int project_mean, int* iters, double* relres, Amg* pc);
+int aos_to_soa(int C, int64_t n, const double* src, double* dst, int64_t ld);
+int soa_to_aos(int C, int64_t n, const double* src, int64_t ld, double* dst);
+// fused Chebyshev iteration for the consistent mass matrix (mv_cheb.cu)
+extern int g_mass_solver;
+int cheb_mass_solve(mv_mesh* m, int ncomp, const double* val, const double* dinv, const double* rhs, double* x,
+                    const uint16_t* mask, double rtol, double atol, int maxit, int* iters, double* relres);
 int halo_exchange_soa(const Halo& h, int64_t nown, int C, double* vec, int64_t ld);
 int op_arrays(mv_mesh* m, int op, const double** val, const double** dinv);
 int halo_exchange(mv_mesh* m, int ncomp, double* vec);

@@ -427,6 +427,8 @@ int pcg_solve(mv_mesh* m, int op, int ncomp, const double* rhs, double* x, const
     set_error("pcg: ncomp %d exceeds dim^2", ncomp);
     return MV_ERR_BADARG;
   }
+  if (op == MV_OP_MASS && g_mass_solver == MV_MASS_CHEBYSHEV && !project_mean)
+    return cheb_mass_solve(m, ncomp, lop.val, lop.dinv, rhs, x, mask, rtol, atol, maxit, iters, relres);
   Amg* pc = nullptr;
   if (ncomp <= 3) MV_CHECK(amg_get(m, op, mask, ncomp, project_mean, &pc));
   return pcg_solve_soa(m, ncomp, lop.val, lop.dinv, rhs, x, mask, rtol, atol, maxit, project_mean, iters, relres, pc);

@@ -328,6 +328,34 @@ k_sub_mean_aos(int64_t n, double* __restrict__ x, const double* __restrict__ sca
 
 namespace mv {
 
+// layout conversion for other translation units (mv_cheb.cu)
+int aos_to_soa(int C, int64_t n, const double* src, double* dst, int64_t ld) {
+  const int g = grid_for(n);
+  switch (C) {
+    case 1: MV_CUDA(cudaMemcpyAsync(dst, src, n * sizeof(double), cudaMemcpyDeviceToDevice, g_stream)); break;
+    case 2: MV_L k_aos_to_soa<2><<<g, MV_BLOCK, 0, g_stream>>>(n, src, dst, ld); break;
+    case 3: MV_L k_aos_to_soa<3><<<g, MV_BLOCK, 0, g_stream>>>(n, src, dst, ld); break;
+    case 4: MV_L k_aos_to_soa<4><<<g, MV_BLOCK, 0, g_stream>>>(n, src, dst, ld); break;
+    case 9: MV_L k_aos_to_soa<9><<<g, MV_BLOCK, 0, g_stream>>>(n, src, dst, ld); break;
+    default: set_error("aos_to_soa: unsupported ncomp %d", C); return MV_ERR_UNSUPPORTED;
+  }
+  MV_KERNEL_CHECK();
+  return MV_OK;
+}
+int soa_to_aos(int C, int64_t n, const double* src, int64_t ld, double* dst) {
+  const int g = grid_for(n);
+  switch (C) {
+    case 1: MV_CUDA(cudaMemcpyAsync(dst, src, n * sizeof(double), cudaMemcpyDeviceToDevice, g_stream)); break;
+    case 2: MV_L k_soa_to_aos<2><<<g, MV_BLOCK, 0, g_stream>>>(n, src, ld, dst); break;
+    case 3: MV_L k_soa_to_aos<3><<<g, MV_BLOCK, 0, g_stream>>>(n, src, ld, dst); break;
+    case 4: MV_L k_soa_to_aos<4><<<g, MV_BLOCK, 0, g_stream>>>(n, src, ld, dst); break;
+    case 9: MV_L k_soa_to_aos<9><<<g, MV_BLOCK, 0, g_stream>>>(n, src, ld, dst); break;
+    default: set_error("soa_to_aos: unsupported ncomp %d", C); return MV_ERR_UNSUPPORTED;
+  }
+  MV_KERNEL_CHECK();
+  return MV_OK;
+}
+
 template <int C>
 static int spmv_soa_launch(mv_mesh* m, const double* val, const double* x, double* y, int64_t ld, bool dot) {
   const Sell& p = m->pat;
