@@ -116,7 +116,8 @@ int mv_mesh_create(int dim, int64_t V, int64_t C, const double* coords, const in
                    int64_t F, const int32_t* bfacet_verts, const int32_t* bfacet_tags,
                    int64_t n_owned_vertices, int64_t n_owned_cells, mv_mesh** out);
 void mv_mesh_destroy(mv_mesh* m);
-/* info[0..9] = V, C, F, nnz, sell_len, nslices, max_row, dim, n_owned_vertices, n_owned_cells */
+/* info[0..11] = V, C, F, nnz, sell_len, nslices, max_row, dim, n_owned_vertices, n_owned_cells,
+ * slice schedule of the gather kernels (0 not built yet, 1 identity, 2 lattice tiles), its length */
 int mv_mesh_info(const mv_mesh* m, int64_t* info);
 /* scalars[0..2] = total_volume (owned cells), sum m_l^2 (owned), sum m_l (owned) */
 int mv_mesh_scalars(const mv_mesh* m, double* scalars);

@@ -50,7 +50,7 @@ class DeviceMesh:
         L.check(lib.mv_mesh_create(self.dim, self.V, self.C, L.ptr(coords), L.ptr(cells), self.F, L.ptr(bfacets),
                                    L.ptr(btags), self.Vown, self.Cown, C.byref(h)))
         self.handle = h
-        info = (C.c_int64 * 10)()
+        info = (C.c_int64 * 16)()
         L.check(lib.mv_mesh_info(h, info))
         self.nnz, self.sell_len, self.nslices = int(info[3]), int(info[4]), int(info[5])
         sc = (C.c_double * 3)()
@@ -134,6 +134,13 @@ class DeviceMesh:
         L.check(L.load().mv_pcg_solve(self.handle, op, ncomp, L.ptr(rhs), L.ptr(x), L.ptr(mask), rtol, atol, maxit,
                                       1 if project_mean else 0, C.byref(it), rel))
         return it.value, np.array(rel[:])
+
+    def slice_schedule(self):
+        """State of the slice schedule of the gather kernels (csrc/mv_sched.cu): "none" before the first
+        mass solve, "identity", or "tiled" (lattice tiles of 16 neighbouring slices)."""
+        info = (C.c_int64 * 16)()
+        L.check(L.load().mv_mesh_info(self.handle, info))
+        return ("none", "identity", "tiled")[int(info[10])]
 
     def set_preconditioner(self, kind):
         """"amg" (default) or "jacobi" for the stiffness-type solves (mass solves are always Jacobi)."""

@@ -59,6 +59,57 @@ __global__ void k_cheb_post(int k, int first, double rtol, double atol, double* 
   cheb_decide<C>(k, scal, flags);
 }
 
+// Deterministic grid reduction of the per-thread sums of a checked launch (same scheme as grid_reduce_sum, with
+// the component of a slot depending on the warp): totals [kind][component] -> scal, then the decision.
+template <int C, int CG, int SPB, int MODE, bool LOCAL, int NS>
+__device__ __forceinline__ void cheb_grid_reduce(double (&sum)[NS], int k, double rtol, double atol, int* __restrict__ flags,
+                                                 double* __restrict__ partials, unsigned* __restrict__ counter,
+                                                 double* __restrict__ scal) {
+  constexpr int NG = C / CG, NW = NG * SPB;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  constexpr int NT = MODE == CHEB_FIRST ? 2 * C : C;   // totals: [kind][component]
+  __shared__ double s_w[NW][NS];
+  __shared__ double s_tot[MV_RED_SLOTS];
+  __shared__ bool s_last;
+#pragma unroll
+  for (int n = 0; n < NS; ++n) {
+    const double t = warp_sum(sum[n]);
+    if (lane == 0) s_w[wid][n] = t;
+  }
+  __syncthreads();
+  if (threadIdx.x < NT) {
+    const int kind = threadIdx.x / C, c = threadIdx.x % C, gg = c / CG, j = c % CG;
+    double t = 0.0;
+    for (int q = 0; q < SPB; ++q) t += s_w[q * NG + gg][kind * CG + j];
+    partials[(size_t)blockIdx.x * MV_RED_SLOTS + threadIdx.x] = t;
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(counter, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  // last block: warp n sums slot n over the blocks in a fixed order
+  for (int n = wid; n < NT; n += NW) {
+    double t = 0.0;
+    for (unsigned q = lane; q < gridDim.x; q += 32) t += __ldcg(&partials[(size_t)q * MV_RED_SLOTS + n]);
+    t = warp_sum(t);
+    if (lane == 0) s_tot[n] = t;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    *counter = 0u;
+    for (int c = 0; c < C; ++c) {
+      scal[SC(S_RZ, c)] = s_tot[c];
+      if (MODE == CHEB_FIRST) scal[SC(S_BB, c)] = s_tot[C + c];
+    }
+    if (LOCAL) {
+      if (MODE == CHEB_FIRST) cheb_setup<C>(rtol, atol, scal);
+      cheb_decide<C>(k, scal, flags);
+    }
+  }
+}
+
 // One Chebyshev iteration.  xin = x_k ([C][ld], ghosts valid), xout holds x_{k-1} on entry and x_{k+1} on exit
 // (owned rows), b is component-major [C][ld].  MODE: CHEB_CHECK also sums r_k.D^-1 r_k, CHEB_FIRST (k = 0,
 // a = 0, xout not read) sums b.D^-1 b as well and fixes the thresholds.  LOCAL: single GPU, decide in-kernel.
@@ -69,7 +120,7 @@ __global__ void k_cheb_post(int k, int first, double rtol, double atol, double* 
 // slice read the same column/value stream; the first one brings it from HBM, the others hit L1.
 template <int C, int CG, int SPB, int MINB, int MODE, bool LOCAL>
 __global__ void __launch_bounds__(32 * (C / CG) * SPB, MINB)
-k_cheb_soa(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
+k_cheb_soa(const int* __restrict__ sched, int64_t ngroups, int64_t nrows, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
            const double* __restrict__ val, const double* __restrict__ dinv, const uint16_t* __restrict__ mask,
            const double* __restrict__ b, const double* __restrict__ xin, double* __restrict__ xout, int64_t ld,
            double ak, double ck, int k, double rtol, double atol, int* __restrict__ flags,
@@ -85,10 +136,9 @@ k_cheb_soa(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_ptr
   double sum[NS];
 #pragma unroll
   for (int c = 0; c < NS; ++c) sum[c] = 0.0;
-  const int64_t ngroups = (nslices + SPB - 1) / SPB;
   for (int64_t sg = blockIdx.x; sg < ngroups; sg += gridDim.x) {
-    const int64_t s = sg * SPB + sl;
-    if (s >= nslices) continue;
+    const int64_t s = __ldg(&sched[sg * SPB + sl]);   // the SPB slices of a group are neighbours in the mesh (mv_sched.cu)
+    if (s < 0) continue;
     const int64_t base = __ldg(&slice_ptr[s]);
     const int w = (int)((__ldg(&slice_ptr[s + 1]) - base) >> 5);
     const int64_t row = s * MV_SLICE + lane;
@@ -142,50 +192,163 @@ k_cheb_soa(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_ptr
     }
   }
   if (MODE == CHEB_PLAIN) return;
-  // deterministic grid reduction (same scheme as grid_reduce_sum, with the component of a slot depending on the warp)
-  constexpr int NT = MODE == CHEB_FIRST ? 2 * C : C;   // totals: [kind][component]
-  __shared__ double s_w[NW][NS];
-  __shared__ double s_tot[MV_RED_SLOTS];
-  __shared__ bool s_last;
-#pragma unroll
-  for (int n = 0; n < NS; ++n) {
-    const double t = warp_sum(sum[n]);
-    if (lane == 0) s_w[wid][n] = t;
-  }
-  __syncthreads();
-  if (threadIdx.x < NT) {
-    const int kind = threadIdx.x / C, c = threadIdx.x % C, gg = c / CG, j = c % CG;
-    double t = 0.0;
-    for (int q = 0; q < SPB; ++q) t += s_w[q * NG + gg][kind * CG + j];
-    partials[(size_t)blockIdx.x * MV_RED_SLOTS + threadIdx.x] = t;
-  }
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) s_last = (atomicAdd(counter, 1u) == gridDim.x - 1);
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
-  // last block: warp n sums slot n over the blocks in a fixed order
-  for (int n = wid; n < NT; n += NW) {
-    double t = 0.0;
-    for (unsigned q = lane; q < gridDim.x; q += 32) t += __ldcg(&partials[(size_t)q * MV_RED_SLOTS + n]);
-    t = warp_sum(t);
-    if (lane == 0) s_tot[n] = t;
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    *counter = 0u;
-    for (int c = 0; c < C; ++c) {
-      scal[SC(S_RZ, c)] = s_tot[c];
-      if (MODE == CHEB_FIRST) scal[SC(S_BB, c)] = s_tot[C + c];
-    }
-    if (LOCAL) {
-      if (MODE == CHEB_FIRST) cheb_setup<C>(rtol, atol, scal);
-      cheb_decide<C>(k, scal, flags);
-    }
-  }
+  cheb_grid_reduce<C, CG, SPB, MODE, LOCAL, NS>(sum, k, rtol, atol, flags, partials, counter, scal);
 }
 
+// ------------------------------------------------------------------------------------------------------
+// TMA-staged variant: the matrix stream of a slice (column indices + values, two contiguous runs of
+// w*128 B and w*256 B) is brought into shared memory by bulk asynchronous copies (cp.async.bulk, completion
+// on an mbarrier) ONE ITERATION AHEAD of its use.  ncu of k_cheb_soa<9> showed no unit above 50 % and every
+// warp stalled on the scoreboard: each chunk of a row waits for its indices from HBM and only then can
+// issue the gathers that depend on them (two memory latencies in series, three chunks per row, few
+// registers to keep loads in flight).  With the indices already in shared memory the gathers of a whole row
+// are issued back to back, and the HBM stream needs no registers at all.
+// ------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+template <int C, int CG, int SPB, int MINB, int NSTAGE, bool VS, int MODE, bool LOCAL>
+__global__ void __launch_bounds__(32 * (C / CG) * SPB, MINB)
+k_cheb_tma(const int* __restrict__ sched, int64_t ngroups, int64_t nrows, const int64_t* __restrict__ slice_ptr,
+           const int* __restrict__ cols, const double* __restrict__ val, const double* __restrict__ dinv,
+           const uint16_t* __restrict__ mask, const double* __restrict__ b, const double* __restrict__ xin,
+           double* __restrict__ xout, int64_t ld, double ak, double ck, int k, double rtol, double atol,
+           int* __restrict__ flags, double* __restrict__ partials, unsigned* __restrict__ counter,
+           double* __restrict__ scal, int maxw) {
+  constexpr int NG = C / CG, NW = NG * SPB;
+  if (MODE != CHEB_FIRST && *flags) return;
+  constexpr int NS = MODE == CHEB_FIRST ? 2 * CG : (MODE == CHEB_CHECK ? CG : 1);
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const int slice_elems = maxw * MV_SLICE;
+  // VS: the values are staged too; otherwise only the indices (the gathers depend on them, the values do not) and
+  // the shared-memory carve-out stays small, which leaves the L1 to the gathered vector
+  double* s_val = reinterpret_cast<double*>(smem_raw);                                        // [NSTAGE][SPB][maxw*32] if VS
+  int* s_col = reinterpret_cast<int*>(smem_raw + (VS ? (size_t)NSTAGE * SPB * slice_elems * sizeof(double) : 0));   // [NSTAGE][SPB][maxw*32]
+  __shared__ int64_t s_base[NSTAGE][SPB];
+  __shared__ __align__(8) uint64_t s_bar[NSTAGE];
+  __shared__ int s_width[NSTAGE][SPB];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int g = wid % NG, sl = wid / NG;
+  const int64_t cb = (int64_t)g * CG * ld;
+  b += cb; xin += cb; xout += cb;
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int q = 0; q < NSTAGE; ++q) mbar_init(&s_bar[q], SPB);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  // producer: lane q < SPB of warp 0 fetches the stream of slot q of group `sg` into stage `st`
+  auto produce = [&](int64_t sg, int st) {
+    if (wid == 0 && lane < SPB) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic reads of this stage precede the async writes
+      const int64_t s = sg < ngroups ? (int64_t)__ldg(&sched[sg * SPB + lane]) : -1;
+      if (s >= 0) {
+        const int64_t base = __ldg(&slice_ptr[s]);
+        const int w = (int)((__ldg(&slice_ptr[s + 1]) - base) >> 5);
+        s_width[st][lane] = w;
+        s_base[st][lane] = base;
+        const uint32_t nb_col = (uint32_t)w * MV_SLICE * sizeof(int), nb_val = VS ? (uint32_t)w * MV_SLICE * sizeof(double) : 0u;
+        mbar_arrive_expect_tx(&s_bar[st], nb_col + nb_val);
+        if (w > 0) {
+          if (VS) bulk_g2s(s_val + ((size_t)st * SPB + lane) * slice_elems, val + base, nb_val, &s_bar[st]);
+          bulk_g2s(s_col + ((size_t)st * SPB + lane) * slice_elems, cols + base, nb_col, &s_bar[st]);
+        }
+      } else {
+        s_width[st][lane] = 0;
+        mbar_arrive_expect_tx(&s_bar[st], 0u);
+      }
+    }
+  };
+  double sum[NS];
+#pragma unroll
+  for (int c = 0; c < NS; ++c) sum[c] = 0.0;
+#pragma unroll
+  for (int q = 0; q < NSTAGE - 1; ++q) produce(blockIdx.x + (int64_t)q * gridDim.x, q);
+  int64_t s_cur = blockIdx.x < ngroups ? (int64_t)__ldg(&sched[(int64_t)blockIdx.x * SPB + sl]) : -1;
+  int it = 0;
+  for (int64_t sg = blockIdx.x; sg < ngroups; sg += gridDim.x, ++it) {
+    const int st = it % NSTAGE;
+    // every warp is done with the stage read in the previous iteration: refill it for iteration it + NSTAGE - 1
+    __syncthreads();
+    produce(sg + (int64_t)(NSTAGE - 1) * gridDim.x, (it + NSTAGE - 1) % NSTAGE);
+    const int64_t s = s_cur;
+    const int64_t sgn = sg + gridDim.x;
+    s_cur = sgn < ngroups ? (int64_t)__ldg(&sched[sgn * SPB + sl]) : -1;
+    const int64_t row = (s < 0 ? 0 : s) * MV_SLICE + lane;
+    const bool live = s >= 0 && row < nrows;
+    const int64_t rr = live ? row : 0;
+    // streamed operands first: they are in flight while the warp waits for the matrix tile
+    double bv[CG], xo[CG];
+#pragma unroll
+    for (int c = 0; c < CG; ++c) {
+      bv[c] = __ldcs(&b[c * ld + rr]);
+      xo[c] = MODE == CHEB_FIRST ? 0.0 : __ldcs(&xout[c * ld + rr]);
+    }
+    const double di = __ldg(&dinv[rr]);
+    const unsigned mk = mask ? (unsigned)__ldg(&mask[rr]) >> (g * CG) : 0u;
+    mbar_wait(&s_bar[st], (uint32_t)((it / NSTAGE) & 1));
+    const int w = s >= 0 ? s_width[st][sl] : 0;
+    const int* cp = s_col + ((size_t)st * SPB + sl) * slice_elems + lane;
+    const double* vp = VS ? s_val + ((size_t)st * SPB + sl) * slice_elems + lane : val + (s >= 0 ? s_base[st][sl] : 0) + lane;
+    double acc[CG];
+#pragma unroll
+    for (int c = 0; c < CG; ++c) acc[c] = 0.0;
+    constexpr int KB = CG >= 9 ? 2 : (CG >= 3 ? 5 : 8);
+    for (int k0 = 0; k0 < w; k0 += KB) {
+      int col[KB];
+#pragma unroll
+      for (int j = 0; j < KB; ++j) col[j] = k0 + j < w ? cp[(k0 + j) * MV_SLICE] : (int)rr;
+      double xv[KB][CG];
+#pragma unroll
+      for (int j = 0; j < KB; ++j) {
+        const double* xp = xin + col[j];
+#pragma unroll
+        for (int c = 0; c < CG; ++c) xv[j][c] = __ldg(xp + c * ld);
+      }
+#pragma unroll
+      for (int j = 0; j < KB; ++j) {
+        const double a = k0 + j < w ? (VS ? vp[(k0 + j) * MV_SLICE] : (NG > 1 ? __ldg(vp + (k0 + j) * MV_SLICE) : __ldcs(vp + (k0 + j) * MV_SLICE))) : 0.0;
+#pragma unroll
+        for (int c = 0; c < CG; ++c) acc[c] = fma(a, xv[j][c], acc[c]);
+      }
+    }
+    if (live) {
+#pragma unroll
+      for (int c = 0; c < CG; ++c) {
+        const bool fix = (mk >> c) & 1u;
+        const double xk = __ldg(&xin[c * ld + row]);
+        const double r = fix ? 0.0 : bv[c] - acc[c];
+        const double z = di * r;
+        const double xn = fix ? xk : xk + (MODE == CHEB_FIRST ? 0.0 : ak * (xk - xo[c])) + ck * z;
+        xout[c * ld + row] = xn;
+        if (MODE != CHEB_PLAIN) sum[c] = fma(r, z, sum[c]);
+        if (MODE == CHEB_FIRST) sum[CG + c] = fix ? sum[CG + c] : fma(bv[c] * di, bv[c], sum[CG + c]);
+      }
+    }
+  }
+  if (MODE == CHEB_PLAIN) return;
+  cheb_grid_reduce<C, CG, SPB, MODE, LOCAL, NS>(sum, k, rtol, atol, flags, partials, counter, scal);
+}
 
 // Wathen's interval for diag(M)^-1 M, P1 simplices in d dimensions.
 static inline void mass_spectrum(int dim, double* lmin, double* lmax) {
@@ -193,9 +356,9 @@ static inline void mass_spectrum(int dim, double* lmin, double* lmax) {
   *lmax = 1.0 + 0.5 * dim;
 }
 
-template <int C, int CG, int SPB, int MINB>
+template <int C, int CG, int SPB, int MINB, int NSTAGE, bool VS>
 struct ChebLaunch {
-  static int grid(int64_t nslices) {
+  static int grid(int64_t ngroups) {
     static int per_sm = 0;
     if (per_sm == 0) {
       int nb = 0;
@@ -204,7 +367,7 @@ struct ChebLaunch {
         nb = 1;
       per_sm = nb;
     }
-    const int64_t need = (nslices + SPB - 1) / SPB;
+    const int64_t need = ngroups;
     int64_t g = (int64_t)g_nsm * per_sm;
     if (g > MV_MAX_BLOCKS) g = MV_MAX_BLOCKS;
     if (g > need) g = need;
@@ -213,11 +376,46 @@ struct ChebLaunch {
   static int run(mv_mesh* m, const double* val, const double* dinv, const uint16_t* mask, const double* b, const double* xin,
                  double* xout, int64_t ld, double ak, double ck, int k, int mode, bool local, double rtol, double atol) {
     const Sell& p = m->pat;
-    const int gr = grid(p.nslices);
+    static_assert(MV_SCHED_TILE % SPB == 0, "a CTA works on an aligned part of a schedule tile");
+    const int64_t ngroups = p.sched_len / SPB;
     constexpr int NT = 32 * (C / CG) * SPB;
     PcgWork& w = m->pcg;
+    static int use_tma = -1;
+    if (use_tma < 0) { const char* e = getenv("MV_CHEB_TMA"); use_tma = e ? atoi(e) : 1; }
+    constexpr int NST = NSTAGE > 0 ? NSTAGE : 2;
+    const size_t smem = (size_t)NST * SPB * p.maxw * MV_SLICE * ((VS ? sizeof(double) : 0) + sizeof(int));
+    if (NSTAGE > 0 && use_tma && smem <= 200 * 1024) {
+      static size_t smem_set = 0;
+      static int per_sm = 0;
+      if (smem != smem_set) {
+        if (smem > 48 * 1024) {
+#define CHEB_ATTR(MODE, LOC) MV_CUDA(cudaFuncSetAttribute(k_cheb_tma<C, CG, SPB, MINB, NST, VS, MODE, LOC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem))
+          CHEB_ATTR(CHEB_PLAIN, true); CHEB_ATTR(CHEB_CHECK, true); CHEB_ATTR(CHEB_CHECK, false); CHEB_ATTR(CHEB_FIRST, true); CHEB_ATTR(CHEB_FIRST, false);
+#undef CHEB_ATTR
+        }
+        int nb = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_cheb_tma<C, CG, SPB, MINB, NST, VS, CHEB_CHECK, true>, NT, smem) != cudaSuccess || nb < 1) nb = 1;
+        per_sm = nb;
+        smem_set = smem;
+      }
+      int64_t g = (int64_t)g_nsm * per_sm;
+      if (g > MV_MAX_BLOCKS) g = MV_MAX_BLOCKS;
+      if (g > ngroups) g = ngroups;
+      const int gr = (int)(g < 1 ? 1 : g);
 #define CHEB_GO(MODE, LOC)                                                                                                  \
-  MV_L k_cheb_soa<C, CG, SPB, MINB, MODE, LOC><<<gr, NT, 0, g_stream>>>(p.nslices, p.nrows, p.slice_ptr, p.cols, val, dinv, mask, b, \
+  MV_L k_cheb_tma<C, CG, SPB, MINB, NST, VS, MODE, LOC><<<gr, NT, smem, g_stream>>>(p.sched, ngroups, p.nrows, p.slice_ptr, p.cols, val, dinv, mask, \
+                                                                     b, xin, xout, ld, ak, ck, k, rtol, atol, w.flags,       \
+                                                                     m->red.partials, m->red.counter, w.scal, p.maxw)
+      if (mode == CHEB_PLAIN) CHEB_GO(CHEB_PLAIN, true);
+      else if (mode == CHEB_CHECK) { if (local) CHEB_GO(CHEB_CHECK, true); else CHEB_GO(CHEB_CHECK, false); }
+      else { if (local) CHEB_GO(CHEB_FIRST, true); else CHEB_GO(CHEB_FIRST, false); }
+#undef CHEB_GO
+      MV_KERNEL_CHECK();
+      return MV_OK;
+    }
+    const int gr = grid(ngroups);
+#define CHEB_GO(MODE, LOC)                                                                                                  \
+  MV_L k_cheb_soa<C, CG, SPB, MINB, MODE, LOC><<<gr, NT, 0, g_stream>>>(p.sched, ngroups, p.nrows, p.slice_ptr, p.cols, val, dinv, mask, b, \
                                                                   xin, xout, ld, ak, ck, k, rtol, atol, w.flags,            \
                                                                   m->red.partials, m->red.counter, w.scal)
     if (mode == CHEB_PLAIN) CHEB_GO(CHEB_PLAIN, true);
@@ -229,10 +427,11 @@ struct ChebLaunch {
   }
 };
 
-template <int C, int CG, int SPB, int MINB>
+template <int C, int CG, int SPB, int MINB, int NSTAGE, bool VS = false>
 static int cheb_soa(mv_mesh* m, const double* val, const double* dinv, const double* rhs, double* x, const uint16_t* mask,
                     double rtol, double atol, int maxit, int* iters, double* relres) {
   MV_CHECK(ensure_pcg_workspace(m));
+  MV_CHECK(ensure_slice_schedule(m));
   PcgWork& w = m->pcg;
   const int64_t n = m->Vown, ld = m->V;
   const bool dist = comm_active();
@@ -266,7 +465,7 @@ static int cheb_soa(mv_mesh* m, const double* val, const double* dinv, const dou
       const int mode = k == 0 ? CHEB_FIRST : ((k >= kdense || (k >= kmin && ((k - kmin) & 1) == 0)) ? CHEB_CHECK : CHEB_PLAIN);
       if (dist) MV_CHECK(halo_exchange_soa(m->halo, n, C, X[k & 1], ld));
       const int pslot = prof_begin(C);
-      MV_CHECK((ChebLaunch<C, CG, SPB, MINB>::run(m, val, dinv, mask, bs, X[k & 1], X[(k + 1) & 1], ld, ak, ck, k, mode, !dist, rtol, atol)));
+      MV_CHECK((ChebLaunch<C, CG, SPB, MINB, NSTAGE, VS>::run(m, val, dinv, mask, bs, X[k & 1], X[(k + 1) & 1], ld, ak, ck, k, mode, !dist, rtol, atol)));
       prof_end(pslot);
       if (dist && mode != CHEB_PLAIN) {
         MV_CHECK(allreduce_sum_dev(w.scal + SC(S_RZ, 0), C));
@@ -312,19 +511,20 @@ int cheb_mass_solve(mv_mesh* m, int ncomp, const double* val, const double* dinv
 #define CHEB_ARGS m, val, dinv, rhs, x, mask, rtol, atol, maxit, iters, relres
   // defaults = the fastest of the variants measured at 256^3 (B200, round 1): C = 1: 64 registers, 32 warps/SM,
   // 0.64 ms; C = 3: 40 registers, 48 warps/SM, 0.97 ms; C = 9: three 3-component warps per slice, 40 registers, 2.9 ms
+  // last template argument: stages of the TMA pipeline of the matrix stream (0 = plain loads; measured faster for C <= 3)
   switch (ncomp) {
-    case 1:
-      if (var == 1) return cheb_soa<1, 1, 8, 6>(CHEB_ARGS);
-      return cheb_soa<1, 1, 8, 4>(CHEB_ARGS);
-    case 2: return cheb_soa<2, 2, 8, 4>(CHEB_ARGS);
-    case 3:
-      if (var == 1) return cheb_soa<3, 3, 8, 4>(CHEB_ARGS);
-      return cheb_soa<3, 3, 8, 6>(CHEB_ARGS);
-    case 4: return cheb_soa<4, 4, 8, 4>(CHEB_ARGS);
+    case 1: return cheb_soa<1, 1, 8, 4, 0>(CHEB_ARGS);
+    case 2: return cheb_soa<2, 2, 8, 4, 0>(CHEB_ARGS);
+    case 3: return cheb_soa<3, 3, 8, 6, 0>(CHEB_ARGS);
+    case 4: return cheb_soa<4, 4, 8, 4, 0>(CHEB_ARGS);
     case 9:
-      if (var == 1) return cheb_soa<9, 3, 2, 5>(CHEB_ARGS);
-      if (var == 4) return cheb_soa<9, 9, 8, 4>(CHEB_ARGS);
-      return cheb_soa<9, 3, 2, 8>(CHEB_ARGS);
+      // measured at 256^3, ms per iteration: plain loads <9,3,2,8> 2.8-3.0; TMA-staged indices + values, 2 stages,
+      // 4 slices x 3 component groups per CTA, 56 registers: 2.0; indices only: 2.9; 3 stages: 2.9 (the larger
+      // carve-out takes the L1 away from the gathered vector)
+      if (var == 1) return cheb_soa<9, 3, 4, 3, 2, false>(CHEB_ARGS);
+      if (var == 2) return cheb_soa<9, 3, 2, 6, 2, true>(CHEB_ARGS);
+      if (var == 6) return cheb_soa<9, 3, 2, 8, 0>(CHEB_ARGS);
+      return cheb_soa<9, 3, 4, 3, 2, true>(CHEB_ARGS);
   }
 #undef CHEB_ARGS
   set_error("chebyshev: unsupported ncomp %d (1,2,3,4,9)", ncomp);

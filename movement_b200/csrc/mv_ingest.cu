@@ -480,7 +480,7 @@ extern "C" void mv_mesh_destroy(mv_mesh* m) {
   dev_free(m->xi); dev_free(m->cells); dev_free(m->v2c_ptr); dev_free(m->v2c);
   dev_free(m->bf_verts); dev_free(m->bf_tags); dev_free(m->bf_cell); dev_free(m->bf_normal); dev_free(m->bf_area);
   dev_free(m->v2f_ptr); dev_free(m->v2f);
-  dev_free(m->pat.slice_ptr); dev_free(m->pat.cols); dev_free(m->pat.row_nnz);
+  dev_free(m->pat.slice_ptr); dev_free(m->pat.cols); dev_free(m->pat.row_nnz); dev_free(m->pat.sched);
   dev_free(m->Mval); dev_free(m->Kval); dev_free(m->MKval); dev_free(m->ml); dev_free(m->vol);
   dev_free(m->dinvM); dev_free(m->dinvK); dev_free(m->dinvMK); dev_free(m->edge_opp);
   dev_free(m->red.partials); dev_free(m->red.counter);
@@ -498,6 +498,7 @@ extern "C" int mv_mesh_info(const mv_mesh* m, int64_t* info) {
   if (!m || !info) return MV_ERR_BADARG;
   info[0] = m->V; info[1] = m->C; info[2] = m->F; info[3] = m->pat.nnz; info[4] = m->pat.len;
   info[5] = m->pat.nslices; info[6] = m->pat.maxw; info[7] = m->dim; info[8] = m->Vown; info[9] = m->Cown;
+  info[10] = m->pat.sched ? (m->pat.sched_tiled ? 2 : 1) : 0; info[11] = m->pat.sched_len;
   return MV_OK;
 }
 

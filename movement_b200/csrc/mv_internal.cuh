@@ -15,6 +15,7 @@
 #define MV_MAX_COMP 9
 #define MV_RED_SLOTS 24      // doubles per block in the partials buffer
 #define MV_MAX_BLOCKS 2368   // 148 SMs x 16: upper bound on persistent grids
+#define MV_SCHED_TILE 16     // slices per tile of the slice schedule (mv_sched.cu)
 
 namespace mv {
 
@@ -103,6 +104,10 @@ struct Sell {
   int64_t* slice_ptr = nullptr;  // [nslices+1]
   int* cols = nullptr;           // [len]
   int* row_nnz = nullptr;        // [nrows]
+  // slice schedule (mv_sched.cu, mesh pattern only): tiles of MV_SCHED_TILE slice indices, -1 = empty slot
+  int* sched = nullptr;          // [sched_len]
+  int64_t sched_len = 0;
+  int sched_tiled = 0;           // 1: lattice tiling, 0: identity
 };
 
 struct Halo {
@@ -271,6 +276,7 @@ int pcg_solve_soa(mv_mesh* m, int ncomp, const double* val, const double* dinv, 
                   double rtol, double atol, int maxit, int project_mean, int* iters, double* relres, Amg* pc);
 int aos_to_soa(int C, int64_t n, const double* src, double* dst, int64_t ld);
 int soa_to_aos(int C, int64_t n, const double* src, int64_t ld, double* dst);
+int ensure_slice_schedule(mv_mesh* m);
 // fused Chebyshev iteration for the consistent mass matrix (mv_cheb.cu)
 extern int g_mass_solver;
 int cheb_mass_solve(mv_mesh* m, int ncomp, const double* val, const double* dinv, const double* rhs, double* x,

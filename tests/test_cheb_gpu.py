@@ -118,3 +118,32 @@ def test_chebyshev_maxit_reports_not_converged():
     with pytest.raises(L.MovementB200Error, match="not converged in 4 iterations") as e:
         dm.pcg(L.MV_OP_MASS, b, dm.zeros(V), rtol=1e-12, maxit=4)
     assert e.value.status == L.MV_ERR_NOT_CONVERGED
+
+
+@pytest.mark.parametrize("dim,n,ncomp", [(2, 96, 2), (2, 200, 4), (3, 64, 3), (3, 70, 9)])
+def test_chebyshev_tiled_slice_schedule(dim, n, ncomp, solver, monkeypatch):
+    """Meshes large enough for the lattice-tiled slice schedule (csrc/mv_sched.cu): the order in which the
+    slices are visited must not change a single bit of the solution, only the reduction order of the
+    measured residual; checked against the Jacobi-PCG, which does not use the schedule."""
+    from movement_b200 import _lib as L
+    from movement_b200.core import DeviceMesh
+    from movement_b200.mesh import cube_arrays, square_arrays
+
+    monkeypatch.setenv("MV_SCHED", "1")          # the identity schedule is the default (csrc/mv_sched.cu)
+    arrays = square_arrays(n, n) if dim == 2 else cube_arrays(n, n, n)
+    dm = DeviceMesh(*arrays)
+    V = dm.Vown
+    g = torch.Generator(device="cuda").manual_seed(3)
+    b = torch.randn(V, ncomp, dtype=torch.float64, device="cuda", generator=g) / V
+    assert dm.slice_schedule() == "none"
+    x = torch.zeros_like(b)
+    it, rel = dm.pcg(L.MV_OP_MASS, b, x, rtol=1e-12)
+    assert dm.slice_schedule() == "tiled"
+    assert rel.max() <= 1e-12
+    solver(L.MV_MASS_PCG)
+    y = torch.zeros_like(b)
+    dm.pcg(L.MV_OP_MASS, b, y, rtol=1e-12)
+    assert float((x - y).abs().max()) < 1e-10 * float(y.abs().max())
+    # every row was visited: M x = b row by row
+    r = dm.spmv(L.MV_OP_MASS, x) - b
+    assert float(r.abs().max()) < 1e-10 * float(b.abs().max())
