@@ -125,7 +125,7 @@ k_cheb_soa(const int* __restrict__ sched, int64_t ngroups, int64_t nrows, const 
            const double* __restrict__ b, const double* __restrict__ xin, double* __restrict__ xout, int64_t ld,
            double ak, double ck, int k, double rtol, double atol, int* __restrict__ flags,
            double* __restrict__ partials, unsigned* __restrict__ counter, double* __restrict__ scal) {
-  constexpr int NG = C / CG, NW = NG * SPB;
+  constexpr int NG = C / CG;
   static_assert(C % CG == 0, "component groups must tile C");
   if (MODE != CHEB_FIRST && *flags) return;
   constexpr int NS = MODE == CHEB_FIRST ? 2 * CG : (MODE == CHEB_CHECK ? CG : 1);
@@ -235,7 +235,7 @@ k_cheb_tma(const int* __restrict__ sched, int64_t ngroups, int64_t nrows, const 
            double* __restrict__ xout, int64_t ld, double ak, double ck, int k, double rtol, double atol,
            int* __restrict__ flags, double* __restrict__ partials, unsigned* __restrict__ counter,
            double* __restrict__ scal, int maxw) {
-  constexpr int NG = C / CG, NW = NG * SPB;
+  constexpr int NG = C / CG;
   if (MODE != CHEB_FIRST && *flags) return;
   constexpr int NS = MODE == CHEB_FIRST ? 2 * CG : (MODE == CHEB_CHECK ? CG : 1);
   extern __shared__ __align__(128) unsigned char smem_raw[];

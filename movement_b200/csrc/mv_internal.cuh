@@ -233,6 +233,10 @@ struct mv_ma {
   double* rhs = nullptr;        // [V*MV_MAX_COMP] assembled right-hand sides
   double* a = nullptr;          // [V] assembled int psi m det(I+H)
   double* dphi = nullptr;       // [V]
+  // the two previous Poisson solves (update, right-hand side): Galerkin initial guess of the next one
+  double* hist_x[2] = {nullptr, nullptr};   // [V]
+  double* hist_b[2] = {nullptr, nullptr};   // [V]
+  int hist_n = 0;
   double* mon_raw = nullptr;    // [V]
   double* dscal = nullptr;      // device scalars
   double* h_scal = nullptr;     // pinned

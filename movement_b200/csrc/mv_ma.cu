@@ -580,6 +580,7 @@ extern "C" void mv_ma_destroy(mv_ma* ma) {
   dev_free(ma->qn_t2); dev_free(ma->qn_base); dev_free(ma->qn_dots);
   if (ma->qn_hdots) cudaFreeHost(ma->qn_hdots);
   dev_free(ma->rhs); dev_free(ma->a); dev_free(ma->dphi); dev_free(ma->dscal); dev_free(ma->bc_mask);
+  for (int i = 0; i < 2; ++i) { dev_free(ma->hist_x[i]); dev_free(ma->hist_b[i]); }
   if (ma->h_scal) cudaFreeHost(ma->h_scal);
   delete ma;
 }
@@ -838,6 +839,53 @@ extern "C" int mv_ma_diagnostics(mv_ma* ma, int use_H_old, double* out) {
   return MV_OK;
 }
 
+// Initial guess of the Poisson solve K x = b from the two previous solves (x1, b1), (x2, b2) of the same mover:
+// the Galerkin (energy-optimal) combination x0 = a1 x1 + a2 x2, i.e. [xi.K xj] a = [xi.b] with K xj = bj known.
+// The right-hand side dt * (a - theta m_l) changes smoothly from one relaxation iteration to the next, so x0 is
+// typically two to three digits accurate; the solve itself and its stopping rule (rtol relative to b) are unchanged.
+enum { H_G11 = 8, H_G12 = 9, H_G22 = 10, H_F1 = 11, H_F2 = 12, H_A1 = 13, H_A2 = 14 };
+__global__ void __launch_bounds__(MV_BLOCK)
+k_hist_dots(int64_t n, const double* __restrict__ x1, const double* __restrict__ b1, const double* __restrict__ x2,
+            const double* __restrict__ b2, const double* __restrict__ b, double* __restrict__ partials,
+            unsigned* __restrict__ counter, double* __restrict__ dscal) {
+  double acc[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+  for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < n; v += (int64_t)gridDim.x * blockDim.x) {
+    const double p1 = x1[v], q1 = b1[v], bb = b[v];
+    acc[0] = fma(p1, q1, acc[0]);
+    acc[3] = fma(p1, bb, acc[3]);
+    if (x2) {
+      const double p2 = x2[v], q2 = b2[v];
+      acc[1] = fma(p1, q2, acc[1]);
+      acc[2] = fma(p2, q2, acc[2]);
+      acc[4] = fma(p2, bb, acc[4]);
+    }
+  }
+  grid_reduce_sum<5>(acc, partials, counter, [&](double(&t)[5]) {
+    dscal[H_G11] = t[0]; dscal[H_G12] = t[1]; dscal[H_G22] = t[2]; dscal[H_F1] = t[3]; dscal[H_F2] = t[4];
+  });
+}
+__global__ void k_hist_alpha(int two, double* __restrict__ dscal) {
+  const double g11 = dscal[H_G11], g12 = dscal[H_G12], g22 = dscal[H_G22], f1 = dscal[H_F1], f2 = dscal[H_F2];
+  double a1 = 0.0, a2 = 0.0;
+  const double det = g11 * g22 - g12 * g12;
+  if (two && g11 > 0.0 && g22 > 0.0 && det > 1e-8 * g11 * g22) {   // x1, x2 not (numerically) parallel in the energy norm
+    a1 = (f1 * g22 - f2 * g12) / det;
+    a2 = (f2 * g11 - f1 * g12) / det;
+  } else if (g11 > 0.0) {
+    a1 = f1 / g11;
+  }
+  if (!(a1 == a1) || !(a2 == a2)) { a1 = 0.0; a2 = 0.0; }
+  dscal[H_A1] = a1;
+  dscal[H_A2] = a2;
+}
+__global__ void __launch_bounds__(MV_BLOCK)
+k_hist_guess(int64_t n, const double* __restrict__ x1, const double* __restrict__ x2, const double* __restrict__ dscal,
+             double* __restrict__ x0) {
+  const double a1 = dscal[H_A1], a2 = dscal[H_A2];
+  for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < n; v += (int64_t)gridDim.x * blockDim.x)
+    x0[v] = x2 ? fma(a2, x2[v], a1 * x1[v]) : a1 * x1[v];
+}
+
 extern "C" int mv_ma_pseudotimestep(mv_ma* ma, double dt, int* iters) {
   if (!ma) return MV_ERR_BADARG;
   MA_REQUIRE(ma, MV_F_PHI);
@@ -845,12 +893,39 @@ extern "C" int mv_ma_pseudotimestep(mv_ma* ma, double dt, int* iters) {
   MA_REQUIRE(ma, MV_F_RESIDUAL);
   mv_mesh* m = ma->mesh;
   const int64_t n = m->Vown;
-  MV_L k_scale<<<grid_for(n), MV_BLOCK, 0, g_stream>>>(n, dt, ma->f[MV_F_RESIDUAL], ma->rhs);
-  MV_CUDA(cudaMemsetAsync(ma->dphi, 0, m->V * sizeof(double), g_stream));
+  const int gv = grid_for(n);
+  MV_L k_scale<<<gv, MV_BLOCK, 0, g_stream>>>(n, dt, ma->f[MV_F_RESIDUAL], ma->rhs);
+  static int use_hist = -1;
+  if (use_hist < 0) { const char* e = getenv("MV_POISSON_HISTORY"); use_hist = e ? atoi(e) : 1; }
+  if (use_hist && ma->hist_n > 0) {
+    const bool two = ma->hist_n > 1;
+    MV_L k_hist_dots<<<gv, MV_BLOCK, 0, g_stream>>>(n, ma->hist_x[0], ma->hist_b[0], two ? ma->hist_x[1] : nullptr,
+                                               two ? ma->hist_b[1] : nullptr, ma->rhs, m->red.partials, m->red.counter, ma->dscal);
+    if (comm_active()) MV_CHECK(allreduce_sum_dev(ma->dscal + H_G11, 5));
+    MV_L k_hist_alpha<<<1, 1, 0, g_stream>>>(two ? 1 : 0, ma->dscal);
+    MV_L k_hist_guess<<<gv, MV_BLOCK, 0, g_stream>>>(n, ma->hist_x[0], two ? ma->hist_x[1] : nullptr, ma->dscal, ma->dphi);
+    MV_KERNEL_CHECK();
+  } else {
+    MV_CUDA(cudaMemsetAsync(ma->dphi, 0, m->V * sizeof(double), g_stream));
+  }
   MV_CHECK(pcg_solve(m, MV_OP_STIFFNESS, 1, ma->rhs, ma->dphi, nullptr, ma->rtol, ma->atol, ma->maxit_poisson, 1, iters,
                      nullptr));
-  MV_L k_add<<<grid_for(n), MV_BLOCK, 0, g_stream>>>(n, ma->f[MV_F_PHI_OLD], ma->dphi, ma->f[MV_F_PHI]);
+  MV_L k_add<<<gv, MV_BLOCK, 0, g_stream>>>(n, ma->f[MV_F_PHI_OLD], ma->dphi, ma->f[MV_F_PHI]);
   MV_KERNEL_CHECK();
+  if (use_hist) {
+    // newest pair into slot 0 (the oldest buffers are recycled)
+    if (!ma->hist_x[1]) {
+      for (int i = 0; i < 2; ++i) {
+        MV_CHECK(dev_alloc(&ma->hist_x[i], n));
+        MV_CHECK(dev_alloc(&ma->hist_b[i], n));
+      }
+    }
+    double* tx = ma->hist_x[1]; ma->hist_x[1] = ma->hist_x[0]; ma->hist_x[0] = tx;
+    double* tb = ma->hist_b[1]; ma->hist_b[1] = ma->hist_b[0]; ma->hist_b[0] = tb;
+    MV_CUDA(cudaMemcpyAsync(ma->hist_x[0], ma->dphi, n * sizeof(double), cudaMemcpyDeviceToDevice, g_stream));
+    MV_CUDA(cudaMemcpyAsync(ma->hist_b[0], ma->rhs, n * sizeof(double), cudaMemcpyDeviceToDevice, g_stream));
+    if (ma->hist_n < 2) ++ma->hist_n;
+  }
   return MV_OK;
 }
 

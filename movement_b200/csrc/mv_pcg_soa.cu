@@ -160,6 +160,21 @@ k_init_soa(int64_t n, int64_t ld, const double* __restrict__ b, const double* __
   });
 }
 
+// Multigrid-preconditioned solves: the stopping rule is relative to max(b, r0) in the preconditioned norm, but only
+// r0.M^-1 r0 is available without an extra V-cycle.  The ratio of the two in the Jacobi norm (both known from
+// k_init_soa) carries it over: ref = r0.z0 * max(1, b.D^-1 b / r0.D^-1 r0).  With a zero initial guess r0 = b and
+// nothing changes; with a good guess the target stays tied to b instead of tightening with the guess.
+__global__ void k_ref_ratio(int C, int phase, double* __restrict__ scal) {
+  for (int c = 0; c < C; ++c) {
+    if (phase == 0) {
+      const double rz = scal[SC(S_RZ, c)], bb = scal[SC(S_BB, c)];
+      scal[SC(S_SUM, c)] = (rz > 0.0 && bb > rz) ? bb / rz : 1.0;
+    } else {
+      scal[SC(S_BB, c)] *= scal[SC(S_SUM, c)];
+    }
+  }
+}
+
 __global__ void k_setup_soa(int C, double rtol, double atol, double* __restrict__ scal, int* __restrict__ flags) {
   bool all = true;
   for (int c = 0; c < C; ++c) {
@@ -411,12 +426,14 @@ int pcg_soa(mv_mesh* m, const double* val, const double* dinv, const double* rhs
   if (pc) {
     // z0 = M^-1 r0 by one V-cycle; reference norm r0.z0
     MV_CHECK(amg_ensure_work(pc, C));
+    MV_L k_ref_ratio<<<1, 1, 0, g_stream>>>(C, 0, w.scal);
     MV_CHECK(amg_apply(m, pc, C, w.r, pc->z, nullptr));
     MV_L k_dot_rz_soa<C, 0><<<gv, MV_BLOCK, 0, g_stream>>>(n, ld, w.r, pc->z, w.flags, m->red.partials, m->red.counter, w.scal, S_RZ, S_BB);
     if (dist) {
       MV_CHECK(allreduce_sum_dev(w.scal + SC(S_RZ, 0), C));
       MV_CHECK(allreduce_sum_dev(w.scal + SC(S_BB, 0), C));
     }
+    MV_L k_ref_ratio<<<1, 1, 0, g_stream>>>(C, 1, w.scal);
     MV_L k_dir_z_soa<C><<<gv, MV_BLOCK, 0, g_stream>>>(n, ld, pc->z, w.p, w.flags, w.scal, 1);
     MV_KERNEL_CHECK();
   }
