@@ -28,6 +28,10 @@
 
 namespace mv {
 
+__global__ void k_to_float(int64_t n, const double* __restrict__ a, float* __restrict__ b) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) b[i] = (float)a[i];
+}
+
 void Csr::release() {
   dev_free(ptr);
   dev_free(col);
@@ -50,6 +54,7 @@ Amg::~Amg() {
       dev_free(v);
     }
     dev_free(L.dinv);
+    dev_free(L.valf);
     sell_free(L.P);
     sell_free(L.R);
     dev_free(L.Pval);
@@ -978,6 +983,16 @@ static int amg_build(mv_mesh* m, int op, const uint16_t* mask_bit0, int singular
   }
   a->lv.push_back(L0);
   int st = build_levels(m, a, bp);
+  // The V-cycle streams the level-0 operator four times per PCG iteration; it reads a single-precision copy of the
+  // values (8 instead of 12 B per non-zero).  The cycle is still one fixed symmetric operator (fl(K_ij) = fl(K_ji)),
+  // vectors, diagonal and the outer PCG stay in double precision, so the solve reaches the same 1e-12.
+  if (st == MV_OK && env_int("MV_AMG_FP32", 1) && a->lv.size() > 1) {
+    AmgLevel& F = a->lv[0];
+    st = dev_alloc(&F.valf, F.pat.len);
+    if (st == MV_OK) {
+      MV_L k_to_float<<<grid_for(F.pat.len), MV_BLOCK, 0, g_stream>>>(F.pat.len, F.val, F.valf);
+    }
+  }
   cudaEventRecord(e1, g_stream);
   cudaEventSynchronize(e1);
   float ms = 0.f;

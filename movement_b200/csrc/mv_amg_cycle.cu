@@ -20,14 +20,14 @@
 
 namespace mv {
 
-template <int C>
+template <int C, typename TV = double>
 __device__ __forceinline__ void sell_dot(const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
-                                         const double* __restrict__ val, const double* __restrict__ x, int64_t ldx, int64_t s,
+                                         const TV* __restrict__ val, const double* __restrict__ x, int64_t ldx, int64_t s,
                                          int lane, double (&acc)[C]) {
   const int64_t base = __ldg(&slice_ptr[s]);
   const int w = (int)((__ldg(&slice_ptr[s + 1]) - base) >> 5);
   const int* cp = cols + base + lane;
-  const double* vp = val + base + lane;
+  const TV* vp = val + base + lane;
 #pragma unroll
   for (int c = 0; c < C; ++c) acc[c] = 0.0;
   // column indices of a chunk first, then the gathers (breaks the index -> gather latency chain)
@@ -39,7 +39,7 @@ __device__ __forceinline__ void sell_dot(const int64_t* __restrict__ slice_ptr, 
     for (int j = 0; j < KB; ++j) {
       const bool in = k0 + j < w;
       col[j] = in ? __ldcs(cp + (k0 + j) * MV_SLICE) : 0;
-      a[j] = in ? __ldcs(vp + (k0 + j) * MV_SLICE) : 0.0;
+      a[j] = in ? (double)__ldcs(vp + (k0 + j) * MV_SLICE) : 0.0;
     }
 #pragma unroll
     for (int j = 0; j < KB; ++j) {
@@ -73,16 +73,16 @@ k_smooth_zero(int64_t n, int64_t ld, const double* __restrict__ b, const double*
   }
 }
 
-template <int C>
+template <int C, typename TV>
 __global__ void __launch_bounds__(MV_BLOCK)
 k_smooth_first(int64_t nslices, int64_t nrows, int64_t ld, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
-               const double* __restrict__ val, const double* __restrict__ b, const double* __restrict__ xin,
+               const TV* __restrict__ val, const double* __restrict__ b, const double* __restrict__ xin,
                const double* __restrict__ dinv, double sc, double* __restrict__ xout, double* __restrict__ d,
                double* __restrict__ r, const int* __restrict__ done) {
   if (done && *done) return;
   SLICE_LOOP {
     double acc[C];
-    sell_dot<C>(slice_ptr, cols, val, xin, ld, s, lane, acc);
+    sell_dot<C, TV>(slice_ptr, cols, val, xin, ld, s, lane, acc);
     const int64_t row = s * MV_SLICE + lane;
     if (row < nrows) {
       const double di = __ldg(&dinv[row]);
@@ -99,16 +99,16 @@ k_smooth_first(int64_t nslices, int64_t nrows, int64_t ld, const int64_t* __rest
   }
 }
 
-template <int C>
+template <int C, typename TV>
 __global__ void __launch_bounds__(MV_BLOCK)
 k_smooth_next(int64_t nslices, int64_t nrows, int64_t ld, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
-              const double* __restrict__ val, const double* __restrict__ din, double* __restrict__ dout,
+              const TV* __restrict__ val, const double* __restrict__ din, double* __restrict__ dout,
               const double* __restrict__ rin, double* __restrict__ rout, const double* __restrict__ dinv, double c1, double c2,
               double* __restrict__ x, const int* __restrict__ done) {
   if (done && *done) return;
   SLICE_LOOP {
     double acc[C];
-    sell_dot<C>(slice_ptr, cols, val, din, ld, s, lane, acc);
+    sell_dot<C, TV>(slice_ptr, cols, val, din, ld, s, lane, acc);
     const int64_t row = s * MV_SLICE + lane;
     if (row < nrows) {
       const double di = __ldg(&dinv[row]);
@@ -125,15 +125,15 @@ k_smooth_next(int64_t nslices, int64_t nrows, int64_t ld, const int64_t* __restr
   }
 }
 
-template <int C>
+template <int C, typename TV>
 __global__ void __launch_bounds__(MV_BLOCK)
 k_residual(int64_t nslices, int64_t nrows, int64_t ld, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
-           const double* __restrict__ val, const double* __restrict__ b, const double* __restrict__ x,
+           const TV* __restrict__ val, const double* __restrict__ b, const double* __restrict__ x,
            const double* __restrict__ dinv, double* __restrict__ r, const int* __restrict__ done) {
   if (done && *done) return;
   SLICE_LOOP {
     double acc[C];
-    sell_dot<C>(slice_ptr, cols, val, x, ld, s, lane, acc);
+    sell_dot<C, TV>(slice_ptr, cols, val, x, ld, s, lane, acc);
     const int64_t row = s * MV_SLICE + lane;
     if (row < nrows) {
       const bool free_row = __ldg(&dinv[row]) != 0.0;
@@ -278,8 +278,12 @@ static int smooth(AmgLevel& L, const double* b, const double* xin, double* xout,
   if (!xin) {
     MV_L k_smooth_zero<C><<<grid_for(L.n), MV_BLOCK, 0, g_stream>>>(L.n, L.ntot, b, L.dinv, 1.0 / theta, xout, dcur, done);
   } else {
-    MV_L k_smooth_first<C><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, L.n, L.ntot, p.slice_ptr, p.cols, L.val, b, xin, L.dinv, 1.0 / theta, xout,
-                                                       dcur, deg > 1 ? L.r : nullptr, done);
+    if (L.valf)
+      MV_L k_smooth_first<C, float><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, L.n, L.ntot, p.slice_ptr, p.cols, L.valf, b, xin, L.dinv, 1.0 / theta,
+                                                                xout, dcur, deg > 1 ? L.r : nullptr, done);
+    else
+      MV_L k_smooth_first<C, double><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, L.n, L.ntot, p.slice_ptr, p.cols, L.val, b, xin, L.dinv, 1.0 / theta,
+                                                                 xout, dcur, deg > 1 ? L.r : nullptr, done);
     rin = L.r;
   }
   double rho_k = 1.0 / sigma;
@@ -287,8 +291,12 @@ static int smooth(AmgLevel& L, const double* b, const double* xin, double* xout,
     const double rho_n = 1.0 / (2.0 * sigma - rho_k);
     const bool last = k == deg - 1;
     if (L.dist) MV_CHECK(halo_exchange_soa(L.halo, L.n, C, dcur, L.ntot));
-    MV_L k_smooth_next<C><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, L.n, L.ntot, p.slice_ptr, p.cols, L.val, dcur, dnext, rin, last ? nullptr : L.r,
-                                                      L.dinv, rho_n * rho_k, 2.0 * rho_n / delta, xout, done);
+    if (L.valf)
+      MV_L k_smooth_next<C, float><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, L.n, L.ntot, p.slice_ptr, p.cols, L.valf, dcur, dnext, rin,
+                                                               last ? nullptr : L.r, L.dinv, rho_n * rho_k, 2.0 * rho_n / delta, xout, done);
+    else
+      MV_L k_smooth_next<C, double><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, L.n, L.ntot, p.slice_ptr, p.cols, L.val, dcur, dnext, rin,
+                                                                last ? nullptr : L.r, L.dinv, rho_n * rho_k, 2.0 * rho_n / delta, xout, done);
     rin = L.r;
     rho_k = rho_n;
     double* t = dcur; dcur = dnext; dnext = t;
@@ -306,8 +314,12 @@ static int vcycle(mv_mesh* m, Amg* a, const double* rfine, double* z, const int*
     AmgLevel& N = a->lv[l + 1];
     MV_CHECK(smooth<C>(L, b, nullptr, L.x0, done));
     if (L.dist) MV_CHECK(halo_exchange_soa(L.halo, L.n, C, L.x0, L.ntot));
-    MV_L k_residual<C><<<slice_grid(L.pat), MV_BLOCK, 0, g_stream>>>(L.pat.nslices, L.n, L.ntot, L.pat.slice_ptr, L.pat.cols, L.val, b, L.x0, L.dinv,
-                                                                L.r, done);
+    if (L.valf)
+      MV_L k_residual<C, float><<<slice_grid(L.pat), MV_BLOCK, 0, g_stream>>>(L.pat.nslices, L.n, L.ntot, L.pat.slice_ptr, L.pat.cols, L.valf, b, L.x0,
+                                                                         L.dinv, L.r, done);
+    else
+      MV_L k_residual<C, double><<<slice_grid(L.pat), MV_BLOCK, 0, g_stream>>>(L.pat.nslices, L.n, L.ntot, L.pat.slice_ptr, L.pat.cols, L.val, b, L.x0,
+                                                                          L.dinv, L.r, done);
     if (L.Rc.ptr)
       MV_L k_csr_apply_warp<C><<<grid_for(L.Rc.nrows * 32), MV_BLOCK, 0, g_stream>>>(L.Rc.nrows, L.Rc.ptr, L.Rc.col, L.Rc.val, L.r, L.ntot, N.b,
                                                                               N.ntot, done);

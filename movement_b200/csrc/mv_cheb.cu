@@ -447,7 +447,9 @@ static int cheb_soa(mv_mesh* m, const double* val, const double* dinv, const dou
   MV_CUDA(cudaMemsetAsync(w.flags, 0, 4 * sizeof(int), g_stream));
 
   const int kmin = 6;           // first sampled convergence check (after the k = 0 launch, which sets the thresholds)
-  const int kdense = 18;        // from here on every launch checks (the bound 2 rho^k reaches 1e-12 at k = 26..30)
+  static int kdense_env = -1;
+  if (kdense_env < 0) { const char* e = getenv("MV_CHEB_KDENSE"); kdense_env = e ? atoi(e) : 18; }
+  const int kdense = kdense_env;        // from here on every launch checks (the bound 2 rho^k reaches 1e-12 at k = 26..30)
   int k = 0;
   double rho = 1.0 / sigma1;    // rho_{k-1}
   w.h_flags[0] = 0;
