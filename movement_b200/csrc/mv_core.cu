@@ -87,6 +87,10 @@ template <int D>
 __device__ __forceinline__ double signed_detJ(const double (&xc)[D + 1][D]);
 
 template <>
+__device__ __forceinline__ double signed_detJ<1>(const double (&xc)[2][1]) {
+  return __dsub_rn(xc[1][0], xc[0][0]);   // interval: x1 - x0 (movement/tangling.py:26-29 in 1D)
+}
+template <>
 __device__ __forceinline__ double signed_detJ<2>(const double (&xc)[3][2]) {
   const double e00 = __dsub_rn(xc[1][0], xc[0][0]), e01 = __dsub_rn(xc[1][1], xc[0][1]);
   const double e10 = __dsub_rn(xc[2][0], xc[0][0]), e11 = __dsub_rn(xc[2][1], xc[0][1]);
@@ -268,7 +272,9 @@ extern "C" int mv_tangle_init(mv_mesh* m, const double* coords, double* detJ0) {
   MV_CHECK(sx.in(coords, m->V * m->dim * sizeof(double)));
   MV_CHECK(sd.out_begin(detJ0, m->C * sizeof(double)));
   const int grid = grid_for(m->C);
-  if (m->dim == 2)
+  if (m->dim == 1)
+    MV_L k_tangle<1, true><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, m->C, m->C, sd.as<double>(), nullptr, nullptr);
+  else if (m->dim == 2)
     MV_L k_tangle<2, true><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, m->C, m->C, sd.as<double>(), nullptr, nullptr);
   else
     MV_L k_tangle<3, true><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, m->C, m->C, sd.as<double>(), nullptr, nullptr);
@@ -287,7 +293,9 @@ extern "C" int mv_tangle_check(mv_mesh* m, const double* coords, const double* d
   // the ratio field is written for all local cells, only owned cells are counted
   const int64_t C = ratio ? m->C : m->Cown;
   const int grid = grid_for(C);
-  if (m->dim == 2)
+  if (m->dim == 1)
+    MV_L k_tangle<1, false><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, C, m->Cown, sd.as<double>(), sr.as<double>(), d_count);
+  else if (m->dim == 2)
     MV_L k_tangle<2, false><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, C, m->Cown, sd.as<double>(), sr.as<double>(), d_count);
   else
     MV_L k_tangle<3, false><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, C, m->Cown, sd.as<double>(), sr.as<double>(), d_count);
@@ -301,6 +309,10 @@ extern "C" int mv_tangle_check(mv_mesh* m, const double* coords, const double* d
 
 extern "C" int mv_cell_volumes(mv_mesh* m, const double* coords, double* volume, double* stats) {
   if (!m || !coords || !volume) return MV_ERR_BADARG;
+  if (m->dim < 2) {
+    set_error("mv_cell_volumes: not available on 1D meshes (geometry for the tangling check only)");
+    return MV_ERR_UNSUPPORTED;
+  }
   Staged sx, sv;
   MV_CHECK(sx.in(coords, m->V * m->dim * sizeof(double)));
   MV_CHECK(sv.out_begin(volume, m->C * sizeof(double)));

@@ -423,8 +423,8 @@ extern "C" int mv_mesh_create(int dim, int64_t V, int64_t C, const double* coord
                               int64_t n_owned_cells, mv_mesh** out) {
   if (!out) return MV_ERR_BADARG;
   *out = nullptr;
-  if (dim != 2 && dim != 3) {
-    set_error("mv_mesh_create: dim must be 2 or 3 (got %d)", dim);
+  if (dim < 1 || dim > 3) {
+    set_error("mv_mesh_create: dim must be 1, 2 or 3 (got %d)", dim);
     return MV_ERR_UNSUPPORTED;
   }
   if (V <= 0 || C < 0 || F < 0 || !coords || (C > 0 && !cells) || n_owned_vertices < 0 || n_owned_vertices > V ||
@@ -467,6 +467,15 @@ extern "C" int mv_mesh_create(int dim, int64_t V, int64_t C, const double* coord
     e = cudaMemcpyAsync(m->h_bf_tags.data(), m->bf_tags, F * sizeof(int), cudaMemcpyDeviceToHost, g_stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(g_stream);
     if (e != cudaSuccess) { set_error("mv_mesh_create: %s", cudaGetErrorString(e)); return fail(MV_ERR_CUDA); }
+  }
+  if (dim == 1) {
+    // interval meshes: geometry only, for the tangling check (movement/tangling.py on UnitIntervalMesh,
+    // test/test_tangling.py:14-37); the movers reject 1D meshes above the ABI, no operators are built
+    if ((st = dev_alloc(&m->red.partials, (size_t)MV_MAX_BLOCKS * MV_RED_SLOTS)) != MV_OK) return fail(st);
+    if ((st = dev_alloc(&m->red.counter, 4)) != MV_OK) return fail(st);
+    if (cudaMemsetAsync(m->red.counter, 0, 4 * sizeof(unsigned), g_stream) != cudaSuccess) return fail(MV_ERR_CUDA);
+    *out = m;
+    return MV_OK;
   }
   st = dim == 2 ? ingest_impl<2>(m) : ingest_impl<3>(m);
   if (st != MV_OK) return fail(st);

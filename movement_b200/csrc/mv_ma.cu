@@ -555,6 +555,10 @@ using namespace mv;
 
 extern "C" int mv_ma_create(mv_mesh* m, mv_ma** out) {
   if (!m || !out) return MV_ERR_BADARG;
+  if (m->dim < 2) {
+    set_error("mv_ma_create: 1D meshes are outside the accelerated path (SURVEY 8f-2)");
+    return MV_ERR_UNSUPPORTED;
+  }
   mv_ma* ma = new mv_ma();
   ma->mesh = m;
   const size_t maxc = (size_t)m->dim * m->dim;

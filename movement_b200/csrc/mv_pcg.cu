@@ -261,6 +261,10 @@ __global__ void k_dinv_sum(int64_t n, const double* __restrict__ a, const double
 }
 
 int op_arrays(mv_mesh* m, int op, const double** val, const double** dinv) {
+  if (!m->Mval) {
+    set_error("no operators on a %dD mesh (interval meshes carry geometry for the tangling check only)", m->dim);
+    return MV_ERR_UNSUPPORTED;
+  }
   switch (op) {
     case MV_OP_MASS: *val = m->Mval; *dinv = m->dinvM; return MV_OK;
     case MV_OP_STIFFNESS: *val = m->Kval; *dinv = m->dinvK; return MV_OK;

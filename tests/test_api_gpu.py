@@ -227,6 +227,31 @@ def test_tangling_checker_api():
         assert checker.check() == 6
 
 
+def test_tangling_checker_1d():
+    """test/test_tangling.py:14-37 (interval meshes carry geometry only; the movers reject them)."""
+    mv = _mv()
+    checker = mv.MeshTanglingChecker(mv.UnitIntervalMesh(3), raise_error=True)
+    checker.mesh.coordinates.dat.data[1] += 0.4
+    with pytest.raises(ValueError, match=r"^Mesh has 1 tangled element\.$"):
+        checker.check()
+    checker = mv.MeshTanglingChecker(mv.UnitIntervalMesh(3), raise_error=False)
+    assert checker.check() == 0
+    checker.mesh.coordinates.dat.data[1] += 0.4
+    with pytest.warns(UserWarning, match="Mesh has 1 tangled element."):
+        assert checker.check() == 1
+    checker = mv.MeshTanglingChecker(mv.UnitIntervalMesh(3), raise_error=False)
+    checker.mesh.coordinates.dat.data[1] += 0.4
+    checker.mesh.coordinates.dat.data[3] -= 0.4
+    with pytest.warns(UserWarning, match="Mesh has 2 tangled elements."):
+        assert checker.check() == 2
+    checker = mv.MeshTanglingChecker(mv.UnitIntervalMesh(3), raise_error=False)
+    checker.mesh.coordinates.interpolate(lambda x: 1.0 - x)          # flip: every element inverts
+    with pytest.warns(UserWarning):
+        assert checker.check() == checker.mesh.num_cells()
+    ratio = checker.jacobian_determinant_ratio.dat.data
+    assert np.allclose(ratio, -1.0, rtol=1e-14, atol=0.0)
+
+
 # ------------------------------------------------------------------ forced movement (test_forced_movement.py)
 def _move(mv, cls, mesh, fixed=None, moving=None, vector=None, **kwargs):
     mover = cls(mesh, 1.0)

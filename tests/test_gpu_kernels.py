@@ -250,6 +250,24 @@ def test_tangling_3d_kat():
         assert dm.tangle_check(torch.as_tensor(c).cuda(), detJ0) == expected
 
 
+def test_tangling_1d_bit_exact():
+    """A9 on interval meshes (movement/tangling.py:26-29 with d = 1): detJ = x1 - x0, ratio and count bit-exact."""
+    from movement_b200.core import DeviceMesh
+
+    rng = np.random.default_rng(12)
+    n = 5000
+    coords = np.sort(rng.random(n + 1))[:, None].copy()
+    cells = np.stack([np.arange(n), np.arange(n) + 1], axis=1).astype(np.int32)
+    dm = DeviceMesh(coords, cells, np.array([[0], [n]], dtype=np.int32), np.array([1, 2], dtype=np.int32))
+    detJ0 = dm.tangle_init(torch.as_tensor(coords).cuda())
+    moved = coords + 2e-4 * (rng.random((n + 1, 1)) - 0.5)
+    ratio = dm.empty(n)
+    cnt = dm.tangle_check(torch.as_tensor(moved).cuda(), detJ0, ratio)
+    ref = mo.OracleTanglingChecker(coords, cells, raise_error=False).ratio(moved)
+    assert np.array_equal(ratio.cpu().numpy(), ref)
+    assert cnt == int((ref <= 0).sum()) and cnt > 0
+
+
 @pytest.mark.parametrize("dim,n", [(2, 40), (3, 12)])
 def test_tangling_bit_exact_random(dim, n):
     mesh = _mesh(dim, n)
