@@ -450,12 +450,12 @@ static int csr_transpose(const Csr& a, Csr& t) {
   void* tmp = nullptr;
   size_t bytes = 0;
   MV_CUDA(cub::DeviceRadixSort::SortPairs(tmp, bytes, k0, k1, a.val, t.val, (int)a.nnz, 0, 32 + bits_col, g_stream));
-  MV_CUDA(cudaMalloc(&tmp, bytes));
+  MV_CUDA(cudaMallocAsync(&tmp, bytes, g_stream));
   MV_CUDA(cub::DeviceRadixSort::SortPairs(tmp, bytes, k0, k1, a.val, t.val, (int)a.nnz, 0, 32 + bits_col, g_stream));
   MV_L k_tr_unpack<<<grid_for(a.nnz), MV_BLOCK, 0, g_stream>>>(a.nnz, k1, t.col);
   MV_KERNEL_CHECK();
   MV_CUDA(cudaStreamSynchronize(g_stream));
-  cudaFree(tmp);
+  cudaFreeAsync(tmp, g_stream);
   dev_free(k0); dev_free(k1);
   (void)bits_row;
   return MV_OK;

@@ -7,6 +7,20 @@ namespace mv {
 
 static thread_local char g_err[1024] = "";
 cudaStream_t g_stream = 0;
+
+int pool_init() {
+  static int done_for = -1;
+  int dev = 0;
+  MV_CUDA(cudaGetDevice(&dev));
+  if (done_for == dev) return MV_OK;
+  cudaMemPool_t pool;
+  MV_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
+  const char* e = getenv("MV_POOL_KEEP_GB");
+  unsigned long long keep = (unsigned long long)(e ? atof(e) : 32.0) * (1ull << 30);
+  MV_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+  done_for = dev;
+  return MV_OK;
+}
 int g_nsm = 0;
 long long g_launches = 0;
 Prof g_prof;

@@ -63,16 +63,23 @@ void prof_drain();           // stream must be synchronised
 // ---------------------------------------------------------------------------------
 // device memory helpers
 // ---------------------------------------------------------------------------------
+// Device memory comes from the CUDA stream-ordered pool (cudaMallocAsync / cudaFreeAsync on g_stream): the set-up
+// phases (ingest, multigrid hierarchy) allocate and drop gigabytes of temporaries, and with cudaMalloc/cudaFree
+// every free synchronised the device and every second mover paid the driver for the same pages again (multigrid
+// set-up 260 ms for the first mover of a process, 680 ms for the next one, round 1).  The pool keeps up to
+// MV_POOL_KEEP_GB (default 32) of freed memory for reuse.
+int pool_init();
 template <typename T>
 int dev_alloc(T** p, size_t n) {
   *p = nullptr;
   if (n == 0) n = 1;
-  MV_CUDA(cudaMalloc((void**)p, n * sizeof(T)));
+  MV_CHECK(pool_init());
+  MV_CUDA(cudaMallocAsync((void**)p, n * sizeof(T), g_stream));
   return MV_OK;
 }
 template <typename T>
 void dev_free(T*& p) {
-  if (p) cudaFree(p);
+  if (p) cudaFreeAsync(p, g_stream);
   p = nullptr;
 }
 bool is_device_ptr(const void* p);

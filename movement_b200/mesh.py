@@ -117,7 +117,10 @@ class Function:
             t.copy_(other.to(t.device, torch.float64).expand_as(t))
         else:
             a = np.asarray(other, dtype=np.float64)
-            t.copy_(torch.from_numpy(np.broadcast_to(a, tuple(t.shape)).copy()).to(t.device))
+            if a.shape == tuple(t.shape) and a.flags.c_contiguous and a.flags.writeable:
+                t.copy_(torch.from_numpy(a))      # straight from the caller's buffer (DMA if it is pinned)
+            else:
+                t.copy_(torch.from_numpy(np.broadcast_to(a, tuple(t.shape)).copy()).to(t.device))
         return self.written()
 
     def interpolate(self, expr):
