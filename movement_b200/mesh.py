@@ -75,7 +75,7 @@ class Function:
     @property
     def tensor(self):
         if self._host_dirty:
-            self._t.copy_(torch.from_numpy(self._host), non_blocking=False)
+            self._t.copy_(self._host_t, non_blocking=False)
             self._host_dirty = False
         return self._t
 
@@ -93,10 +93,12 @@ class Function:
                 a.flags.writeable = False
             return a
         if self._host is None:
-            self._host = np.empty(tuple(self._t.shape), dtype=np.float64)
+            # page-locked mirror: refreshed and uploaded by DMA (25 GB/s) instead of through a pageable staging copy
+            self._host_t = torch.empty(tuple(self._t.shape), dtype=torch.float64, pin_memory=True)
+            self._host = self._host_t.numpy()
             self._dev_newer = True
         if self._dev_newer and not self._host_dirty:
-            self._host[...] = self._t.cpu().numpy()
+            self._host_t.copy_(self._t)
             self._dev_newer = False
         if writable:
             self._host_dirty = True
