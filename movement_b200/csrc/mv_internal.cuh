@@ -155,7 +155,7 @@ struct AmgLevel {
   int64_t ntot = 0;         // owned + ghost columns of A
   Sell pat;                 // operator of this level (level 0 borrows the mesh pattern)
   const double* val = nullptr;
-  float* valf = nullptr;    // single-precision copy of val for the V-cycle's matrix streams (level 0 only; mv_amg_cycle.cu)
+  float* valf = nullptr;    // single-precision copy of val for the V-cycle's matrix streams (smoothed levels; mv_amg_cycle.cu)
   bool owns_A = false;
   double* dinv = nullptr;   // [n]; 0 at constrained vertices
   const uint16_t* mask = nullptr;  // level 0 only: bit 0 set = constrained vertex
