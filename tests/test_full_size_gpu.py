@@ -79,13 +79,16 @@ def test_forced_movers_full_size(which, n):
     assert torch.equal(_dev(mesh), xi)                       # the caller's mesh is never touched (mover.py:49)
     del mover
     # demo forcing: one step at amplitude 1 and one at amplitude 2 -> linear in the data
-    m1 = _forced(mv, cls, mesh, 1.0, steps=2)
-    m2 = _forced(mv, cls, mesh, 2.0, steps=2)
-    d1, d2 = _dev(m1.mesh) - xi, _dev(m2.mesh) - xi
+    # (the spring solve is a Jacobi-PCG with O(n) iterations at this size: one step, no second run)
+    m1 = _forced(mv, cls, mesh, 1.0, steps=2 if which == "laplacian" else 1)
+    d1 = _dev(m1.mesh) - xi
     scale = float(d1.abs().max())
     assert scale > 1e-3
     if which == "laplacian":                                 # K is assembled once on xi: exactly linear
+        m2 = _forced(mv, cls, mesh, 2.0, steps=2)
+        d2 = _dev(m2.mesh) - xi
         assert float((d2 - 2 * d1).abs().max()) < 1e-9 * max(scale, 1.0)
+        del m2
     # fixed boundaries stay exactly where they were; the moving one only moves vertically
     c0 = xi
     left, right, bottom, top = c0[:, 0] == 0.0, c0[:, 0] == 1.0, c0[:, 1] == 0.0, c0[:, 1] == 1.0
