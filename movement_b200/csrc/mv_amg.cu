@@ -18,6 +18,7 @@
 //   6. rho(D^-1 A)      power iteration, 12 steps, x1.1
 // The coarsest operator (<= MV_AMG_DENSE rows) is inverted densely by Gauss-Jordan in one CTA.
 // oracle/amg_prototype.py is the numpy statement of the same algorithm.
+#include <algorithm>
 #include <cub/device/device_radix_sort.cuh>
 
 #include "mv_internal.cuh"
@@ -993,6 +994,22 @@ static int amg_build(mv_mesh* m, int op, const uint16_t* mask_bit0, int singular
       if (!F.val || F.pat.len == 0) continue;
       st = dev_alloc(&F.valf, F.pat.len);
       if (st == MV_OK) MV_L k_to_float<<<grid_for(F.pat.len), MV_BLOCK, 0, g_stream>>>(F.pat.len, F.val, F.valf);
+    }
+  }
+  // Work split of large replicated levels: the tail of a multi-GPU hierarchy is replicated, so its cost does not
+  // shrink with the number of ranks (256^3: level 1 has 1.5 M rows, ~25 ms per relaxation step on every rank,
+  // half of the step at 8 GPUs).  Each rank then smooths only its chunk of slices and the vectors are allgathered.
+  if (st == MV_OK && comm_active() && env_int("MV_AMG_SPLIT", 1)) {
+    const int64_t split_min = (int64_t)env_int("MV_AMG_SPLIT_MIN", 200000);
+    const size_t nsm = a->lv.size() - (a->coarse_inv ? 1 : 0);
+    for (size_t l = 1; l < nsm; ++l) {
+      AmgLevel& S = a->lv[l];
+      if (S.dist || S.n < split_min || S.ntot != S.n) continue;
+      const int64_t per = (S.pat.nslices + comm_size() - 1) / comm_size();
+      S.split_chunk = per * MV_SLICE;
+      S.split_lo = std::min<int64_t>(S.n, (int64_t)comm_rank() * S.split_chunk);
+      S.split_hi = std::min<int64_t>(S.n, (int64_t)(comm_rank() + 1) * S.split_chunk);
+      S.ntot = S.split_chunk * comm_size();   // leading dimension of the level's vectors (>= n)
     }
   }
   cudaEventRecord(e1, g_stream);

@@ -54,7 +54,7 @@ __device__ __forceinline__ void sell_dot(const int64_t* __restrict__ slice_ptr, 
   const int lane = threadIdx.x & 31;                                                       \
   const int64_t warp0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;             \
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;                           \
-  for (int64_t s = warp0; s < nslices; s += nwarps)
+  for (int64_t s = s0 + warp0; s < nslices; s += nwarps)
 
 // x = d = D^-1 b / theta (zero initial guess)
 template <int C>
@@ -75,7 +75,7 @@ k_smooth_zero(int64_t n, int64_t ld, const double* __restrict__ b, const double*
 
 template <int C, typename TV>
 __global__ void __launch_bounds__(MV_BLOCK)
-k_smooth_first(int64_t nslices, int64_t nrows, int64_t ld, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
+k_smooth_first(int64_t s0, int64_t nslices, int64_t nrows, int64_t ld, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
                const TV* __restrict__ val, const double* __restrict__ b, const double* __restrict__ xin,
                const double* __restrict__ dinv, double sc, double* __restrict__ xout, double* __restrict__ d,
                double* __restrict__ r, const int* __restrict__ done) {
@@ -101,7 +101,7 @@ k_smooth_first(int64_t nslices, int64_t nrows, int64_t ld, const int64_t* __rest
 
 template <int C, typename TV>
 __global__ void __launch_bounds__(MV_BLOCK)
-k_smooth_next(int64_t nslices, int64_t nrows, int64_t ld, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
+k_smooth_next(int64_t s0, int64_t nslices, int64_t nrows, int64_t ld, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
               const TV* __restrict__ val, const double* __restrict__ din, double* __restrict__ dout,
               const double* __restrict__ rin, double* __restrict__ rout, const double* __restrict__ dinv, double c1, double c2,
               double* __restrict__ x, const int* __restrict__ done) {
@@ -127,7 +127,7 @@ k_smooth_next(int64_t nslices, int64_t nrows, int64_t ld, const int64_t* __restr
 
 template <int C, typename TV>
 __global__ void __launch_bounds__(MV_BLOCK)
-k_residual(int64_t nslices, int64_t nrows, int64_t ld, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
+k_residual(int64_t s0, int64_t nslices, int64_t nrows, int64_t ld, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
            const TV* __restrict__ val, const double* __restrict__ b, const double* __restrict__ x,
            const double* __restrict__ dinv, double* __restrict__ r, const int* __restrict__ done) {
   if (done && *done) return;
@@ -150,6 +150,7 @@ k_sell_apply(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_p
              const double* __restrict__ val, const double* __restrict__ x, int64_t ldx, double* __restrict__ y, int64_t ldy,
              const int* __restrict__ done) {
   if (done && *done) return;
+  const int64_t s0 = 0;
   SLICE_LOOP {
     double acc[C];
     sell_dot<C>(slice_ptr, cols, val, x, ldx, s, lane, acc);
@@ -234,10 +235,12 @@ int amg_ensure_work(Amg* a, int C) {
     MV_CUDA(cudaMemsetAsync(L.x0, 0, nt * sizeof(double), g_stream));
     if (l > 0) {
       MV_CHECK(dev_alloc(&L.b, nt));
+      MV_CUDA(cudaMemsetAsync(L.b, 0, nt * sizeof(double), g_stream));
       MV_CHECK(dev_alloc(&L.x1, nt));
       MV_CUDA(cudaMemsetAsync(L.x1, 0, nt * sizeof(double), g_stream));
     }
     MV_CHECK(dev_alloc(&L.r, nt));
+    MV_CUDA(cudaMemsetAsync(L.r, 0, nt * sizeof(double), g_stream));
     if (L.degree > 1) {
       MV_CHECK(dev_alloc(&L.d0, nt));
       MV_CHECK(dev_alloc(&L.d1, nt));
@@ -270,7 +273,12 @@ static int smooth(AmgLevel& L, const double* b, const double* xin, double* xout,
   const double lmax = L.rho, lmin = L.rho / ratio;
   const double theta = 0.5 * (lmax + lmin), delta = 0.5 * (lmax - lmin), sigma = theta / delta;
   const Sell& p = L.pat;
-  const int grid = slice_grid(p);
+  // work-split replicated level: this rank's slices only, vectors allgathered after each matrix pass
+  const bool split = L.split_chunk > 0;
+  const int64_t s0 = split ? L.split_lo / MV_SLICE : 0;
+  const int64_t s1 = split ? (L.split_hi > L.split_lo ? (L.split_hi + MV_SLICE - 1) / MV_SLICE : s0) : p.nslices;
+  const int grid = split ? grid_for((s1 - s0 > 0 ? s1 - s0 : 1) * MV_SLICE, 8) : slice_grid(p);
+  bool x_partial = false;      // xout is current on this rank's rows only
   double* dcur = deg > 1 ? L.d0 : nullptr;
   double* dnext = L.d1;
   const double* rin = b;
@@ -278,11 +286,12 @@ static int smooth(AmgLevel& L, const double* b, const double* xin, double* xout,
   if (!xin) {
     MV_L k_smooth_zero<C><<<grid_for(L.n), MV_BLOCK, 0, g_stream>>>(L.n, L.ntot, b, L.dinv, 1.0 / theta, xout, dcur, done);
   } else {
+    x_partial = split;
     if (L.valf)
-      MV_L k_smooth_first<C, float><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, L.n, L.ntot, p.slice_ptr, p.cols, L.valf, b, xin, L.dinv, 1.0 / theta,
+      MV_L k_smooth_first<C, float><<<grid, MV_BLOCK, 0, g_stream>>>(s0, s1, L.n, L.ntot, p.slice_ptr, p.cols, L.valf, b, xin, L.dinv, 1.0 / theta,
                                                                 xout, dcur, deg > 1 ? L.r : nullptr, done);
     else
-      MV_L k_smooth_first<C, double><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, L.n, L.ntot, p.slice_ptr, p.cols, L.val, b, xin, L.dinv, 1.0 / theta,
+      MV_L k_smooth_first<C, double><<<grid, MV_BLOCK, 0, g_stream>>>(s0, s1, L.n, L.ntot, p.slice_ptr, p.cols, L.val, b, xin, L.dinv, 1.0 / theta,
                                                                  xout, dcur, deg > 1 ? L.r : nullptr, done);
     rin = L.r;
   }
@@ -291,17 +300,20 @@ static int smooth(AmgLevel& L, const double* b, const double* xin, double* xout,
     const double rho_n = 1.0 / (2.0 * sigma - rho_k);
     const bool last = k == deg - 1;
     if (L.dist) MV_CHECK(halo_exchange_soa(L.halo, L.n, C, dcur, L.ntot));
+    if (split && x_partial) MV_CHECK(allgather_rows_dev(dcur, L.ntot, C, L.split_chunk));   // (after k_smooth_zero d is complete everywhere)
+    x_partial = split;
     if (L.valf)
-      MV_L k_smooth_next<C, float><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, L.n, L.ntot, p.slice_ptr, p.cols, L.valf, dcur, dnext, rin,
+      MV_L k_smooth_next<C, float><<<grid, MV_BLOCK, 0, g_stream>>>(s0, s1, L.n, L.ntot, p.slice_ptr, p.cols, L.valf, dcur, dnext, rin,
                                                                last ? nullptr : L.r, L.dinv, rho_n * rho_k, 2.0 * rho_n / delta, xout, done);
     else
-      MV_L k_smooth_next<C, double><<<grid, MV_BLOCK, 0, g_stream>>>(p.nslices, L.n, L.ntot, p.slice_ptr, p.cols, L.val, dcur, dnext, rin,
+      MV_L k_smooth_next<C, double><<<grid, MV_BLOCK, 0, g_stream>>>(s0, s1, L.n, L.ntot, p.slice_ptr, p.cols, L.val, dcur, dnext, rin,
                                                                 last ? nullptr : L.r, L.dinv, rho_n * rho_k, 2.0 * rho_n / delta, xout, done);
     rin = L.r;
     rho_k = rho_n;
     double* t = dcur; dcur = dnext; dnext = t;
   }
   MV_KERNEL_CHECK();
+  if (x_partial) MV_CHECK(allgather_rows_dev(xout, L.ntot, C, L.split_chunk));
   return MV_OK;
 }
 
@@ -314,12 +326,17 @@ static int vcycle(mv_mesh* m, Amg* a, const double* rfine, double* z, const int*
     AmgLevel& N = a->lv[l + 1];
     MV_CHECK(smooth<C>(L, b, nullptr, L.x0, done));
     if (L.dist) MV_CHECK(halo_exchange_soa(L.halo, L.n, C, L.x0, L.ntot));
-    if (L.valf)
-      MV_L k_residual<C, float><<<slice_grid(L.pat), MV_BLOCK, 0, g_stream>>>(L.pat.nslices, L.n, L.ntot, L.pat.slice_ptr, L.pat.cols, L.valf, b, L.x0,
-                                                                         L.dinv, L.r, done);
-    else
-      MV_L k_residual<C, double><<<slice_grid(L.pat), MV_BLOCK, 0, g_stream>>>(L.pat.nslices, L.n, L.ntot, L.pat.slice_ptr, L.pat.cols, L.val, b, L.x0,
-                                                                          L.dinv, L.r, done);
+    {
+      const bool split = L.split_chunk > 0;
+      const int64_t s0 = split ? L.split_lo / MV_SLICE : 0;
+      const int64_t s1 = split ? (L.split_hi > L.split_lo ? (L.split_hi + MV_SLICE - 1) / MV_SLICE : s0) : L.pat.nslices;
+      const int rg = split ? grid_for((s1 - s0 > 0 ? s1 - s0 : 1) * MV_SLICE, 8) : slice_grid(L.pat);
+      if (L.valf)
+        MV_L k_residual<C, float><<<rg, MV_BLOCK, 0, g_stream>>>(s0, s1, L.n, L.ntot, L.pat.slice_ptr, L.pat.cols, L.valf, b, L.x0, L.dinv, L.r, done);
+      else
+        MV_L k_residual<C, double><<<rg, MV_BLOCK, 0, g_stream>>>(s0, s1, L.n, L.ntot, L.pat.slice_ptr, L.pat.cols, L.val, b, L.x0, L.dinv, L.r, done);
+      if (split) MV_CHECK(allgather_rows_dev(L.r, L.ntot, C, L.split_chunk));   // the restriction below gathers all of r
+    }
     if (L.Rc.ptr)
       MV_L k_csr_apply_warp<C><<<grid_for(L.Rc.nrows * 32), MV_BLOCK, 0, g_stream>>>(L.Rc.nrows, L.Rc.ptr, L.Rc.col, L.Rc.val, L.r, L.ntot, N.b,
                                                                               N.ntot, done);

@@ -23,6 +23,7 @@ struct NcclApi {
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
   ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*GroupStart)() = nullptr;
@@ -61,6 +62,7 @@ static int load_nccl(const char* path) {
   SYM(CommDestroy, "ncclCommDestroy");
   SYM(AllReduce, "ncclAllReduce");
   SYM(Broadcast, "ncclBroadcast");
+  SYM(AllGather, "ncclAllGather");
   SYM(Send, "ncclSend");
   SYM(Recv, "ncclRecv");
   SYM(GroupStart, "ncclGroupStart");
@@ -81,6 +83,16 @@ int allreduce_dev(double* d, int n, int op) {
   return MV_OK;
 }
 int allreduce_sum_dev(double* d, int n) { return allreduce_dev(d, n, 0); }
+// In-place allgather of C component rows: rank r holds vec[c*ld + r*chunk .. + chunk) and receives the others'
+// chunks; ld >= chunk * ranks (work-split replicated multigrid levels, mv_amg_cycle.cu).
+int allgather_rows_dev(double* vec, int64_t ld, int C, int64_t chunk) {
+  if (!comm_active()) return MV_OK;
+  if (C > 1) MV_NCCL(g_nccl.GroupStart());
+  for (int c = 0; c < C; ++c)
+    MV_NCCL(g_nccl.AllGather(vec + c * ld + (int64_t)g_rank * chunk, vec + c * ld, (size_t)chunk, ncclDouble, g_comm, g_stream));
+  if (C > 1) MV_NCCL(g_nccl.GroupEnd());
+  return MV_OK;
+}
 int allreduce_volstats_dev(double* dout) {
   MV_CHECK(allreduce_dev(dout + 0, 1, 0));
   MV_CHECK(allreduce_dev(dout + 1, 1, 1));

@@ -170,6 +170,9 @@ struct AmgLevel {
   Halo halo;
   bool owns_halo = false;
   bool dist = false;        // operator rows are spread over the ranks (halo exchange before every gather of a vector)
+  // replicated level whose matrix passes are split over the ranks (rows [split_lo, split_hi) here, vectors
+  // allgathered in place after each pass; ntot is padded to split_chunk * ranks); 0 = every rank does every row
+  int64_t split_chunk = 0, split_lo = 0, split_hi = 0;
   bool reduce_next = false; // next level is replicated on every rank: its right-hand side is the allreduce of the partial restrictions
   int64_t nglobal = 0;      // rows over all ranks
   int64_t goff = 0;         // global index of owned row 0
@@ -297,6 +300,7 @@ int halo_exchange_soa(const Halo& h, int64_t nown, int C, double* vec, int64_t l
 int op_arrays(mv_mesh* m, int op, const double** val, const double** dinv);
 int halo_exchange(mv_mesh* m, int ncomp, double* vec);
 int allreduce_sum_dev(double* dscal, int n);
+int allgather_rows_dev(double* vec, int64_t ld, int C, int64_t chunk);
 int allreduce_dev(double* dscal, int n, int op);  // op: 0 sum, 1 max, 2 min
 int allreduce_volstats_dev(double* dout);  // [0] sum, [1] max, [2] min
 int volume_stats_device(mv_mesh* m, const double* x, const double* mon, const double* vol0, double* volume,

@@ -21,12 +21,15 @@ def test_two_rank_relaxation_matches_oracle(dim, n):
     assert out.returncode == 0 and "DIST-OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
 
 
+@pytest.mark.parametrize("split_min", ["200000", "1"])
 @pytest.mark.parametrize("dim,n", [(3, 20), (2, 96)])
-def test_two_rank_multigrid_poisson(dim, n):
+def test_two_rank_multigrid_poisson(dim, n, split_min):
+    """split_min = 1: the replicated level 1 of these small hierarchies is work-split over the ranks
+    (row chunks + in-place allgather, csrc/mv_amg_cycle.cu), as happens by default from 200 000 rows on."""
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
                           "--master-addr", "127.0.0.1", "--master-port", "29519",
                           os.path.join(ROOT, "tests", "dist", "run_amg_2rank.py"), str(dim), str(n)],
-                         capture_output=True, text=True, timeout=600)
+                         capture_output=True, text=True, timeout=600, env=dict(os.environ, MV_AMG_SPLIT_MIN=split_min))
     assert out.returncode == 0 and "DIST-AMG-OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
