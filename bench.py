@@ -306,6 +306,31 @@ def run_ours(args):
     step_bytes = float(np.mean(cg[:, 0] * bmass(d) + cg[:, 1] * bcg(1) + cg[:, 2] * bmass(d * d))) * Vglobal
     step_gbs = step_bytes / (ms / args.steps * 1e-3) / 1e9
 
+    # ---- where a step goes: two more (untimed above) iterations with CUDA events between the phases, max over ranks
+    def phase_step(mv_):
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+        ev[0].record()
+        n1 = mv_._l2_project()
+        ev[1].record()
+        mv_._update_physical_coordinates()
+        mv_._n1 = n1
+        mv_._diagnostics(use_H_old=True)
+        ev[2].record()
+        n2 = mv_._pseudotimestep()
+        ev[3].record()
+        n3 = mv_._equidistribute()
+        mv_._advance()
+        mv_.cg_iterations.append((n1, n2, n3))
+        ev[4].record()
+        torch.cuda.synchronize()
+        return [ev[i].elapsed_time(ev[i + 1]) for i in range(4)]
+
+    ph = torch.tensor([phase_step(mover) for _ in range(2)], dtype=torch.float64, device="cuda").mean(dim=0)
+    if world > 1:
+        dist.all_reduce(ph, op=dist.ReduceOp.MAX)
+    phases = dict(zip(["l2_projection(A1)", "update_x+monitor+tangling+diagnostics(A2-A6)", "poisson_pseudotimestep(A7)",
+                       "hessian_recovery(A8)"], [float(v) for v in ph.tolist()]))
+
     # ---- end to end through the public API from host buffers ---------------------------------------
     e2e = None
     if not args.no_e2e:
@@ -348,6 +373,7 @@ def run_ours(args):
                            "residual_after_timed_steps": residuals[-1]},
                 "roofline": roofline,
                 "step_model": {"bytes_per_step": step_bytes, "GBs": step_gbs, "frac_of_peak": step_gbs / (peak * world)},
+                "phases_ms": phases,
                 "gpu_launches": int(launches.value), "clocks": clocks, "e2e": e2e}
         if world == 1 and not args.no_cpu_baseline:
             r = cpu_relax(args.cpu_n, args.cpu_steps, 1, args.inner_rtol)

@@ -432,6 +432,48 @@ class MAOperators:
         lu, free = self._Mbc_lu[comp]
         return lu.solve(np.where(free, rhs, 0.0))
 
+    def solve_mass_chebyshev(self, rhs, x0=None, fixed=None, rtol=1e-12, atol=1e-50, maxit=500, kmin=6, kdense=18):
+        """CPU restatement of the GPU path's iterative mass solver (movement_b200/csrc/mv_cheb.cu), used to pin its
+        iteration counts: Chebyshev iteration on diag(M)^-1 M over Wathen's interval [1/2, 1 + d/2] for P1
+        simplices, x_{k+1} = x_k + a_k (x_k - x_{k-1}) + c_k D^-1 (b - M x_k), stopped when every component has
+        sqrt(r.D^-1 r) <= max(rtol * ref, atol), ref = max(b.D^-1 b, r_0.D^-1 r_0), checked at k = 0 (a converged
+        guess is returned untouched), k = kmin, kmin + 2, ... and every k >= kdense.  Replaces the KSP `cg` of
+        movement/solver_parameters.py:62-66 at movement/monge_ampere.py:340,483 -- same linear systems, so
+        results agree with `solve_mass` to the tolerance.  `fixed`: boolean [V, c] mask of Dirichlet dofs whose
+        value in x0 is kept.  Returns (x, iterations)."""
+        b = np.asarray(rhs, dtype=float)
+        one = b.ndim == 1
+        b = b.reshape(self.V, -1)
+        x = np.zeros_like(b) if x0 is None else np.array(x0, dtype=float).reshape(self.V, -1)
+        fix = np.zeros(b.shape, bool) if fixed is None else np.asarray(fixed, bool).reshape(self.V, -1)
+        dinv = 1.0 / self.M.diagonal()
+        lmin, lmax = 0.5, 1.0 + 0.5 * self.dim
+        theta, delta = 0.5 * (lmax + lmin), 0.5 * (lmax - lmin)
+        sigma1 = theta / delta
+        rho = 1.0 / sigma1
+        xprev = x.copy()
+        thr = None
+        for k in range(maxit):
+            r = np.where(fix, 0.0, b - self.M @ x)
+            z = dinv[:, None] * r
+            check = k == 0 or k >= kdense or (k >= kmin and (k - kmin) % 2 == 0)
+            if check:
+                rz = (r * z).sum(axis=0)
+                if k == 0:
+                    bb = np.where(fix, 0.0, b * dinv[:, None] * b).sum(axis=0)
+                    thr = np.maximum(rtol ** 2 * np.maximum(rz, bb), atol ** 2)
+                if np.all(rz <= thr):
+                    return (x[:, 0] if one else x), k
+            if k == 0:
+                ak, ck = 0.0, 1.0 / theta
+            else:
+                rk = 1.0 / (2.0 * sigma1 - rho)
+                ak, ck = rk * rho, 2.0 * rk / delta
+                rho = rk
+            xnew = np.where(fix, x, x + ak * (x - xprev) + ck * z)
+            xprev, x = x, xnew
+        raise RuntimeError(f"chebyshev: not converged in {maxit} iterations")
+
     def solve_poisson_nullspace(self, rhs):
         """K u = rhs with constant nullspace: rhs and u projected to zero mean."""
         V = self.V

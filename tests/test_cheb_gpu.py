@@ -62,6 +62,10 @@ def test_chebyshev_matches_exact_solve_and_pcg(dim, n, ncomp, solver):
     rho = (np.sqrt(kappa) - 1) / (np.sqrt(kappa) + 1)
     assert it_c <= int(np.ceil(np.log(2e12 * np.sqrt(kappa)) / -np.log(rho))) + 2
     assert it_c < 2 * it_p
+    # the oracle's restatement of the same iteration (same interval, same check schedule): same count
+    x_o, it_o = ops.solve_mass_chebyshev(b, rtol=1e-12)
+    assert abs(it_c - it_o) <= 1
+    assert np.abs(out[L.MV_MASS_CHEBYSHEV][1] - x_o.reshape(V, ncomp)).max() < 1e-10 * np.abs(ref).max()
     assert np.abs(out[L.MV_MASS_CHEBYSHEV][1] - out[L.MV_MASS_PCG][1]).max() < 1e-10 * np.abs(ref).max()
 
 
