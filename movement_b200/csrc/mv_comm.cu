@@ -192,8 +192,63 @@ __global__ void k_halo_pack_soa(int64_t nsend, int C, const int* __restrict__ id
   }
 }
 
+// Packed variant for C > 1: ONE message per neighbour ([C][ns_k] contiguous in the send buffer, received into a
+// staging buffer and scattered by a kernel) instead of C messages per neighbour.  At 8 GPUs the C = 9 exchange of
+// the Hessian-recovery iteration cost ~0.27 ms as 36 point-to-point operations against 0.22 ms for the kernel it feeds.
+__global__ void k_halo_pack_nb(int64_t ns, int C, const int* __restrict__ idx, const double* __restrict__ vec, int64_t ld,
+                               double* __restrict__ buf) {
+  const int64_t n = ns * C;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t c = i / ns, t = i - c * ns;
+    buf[i] = vec[c * ld + idx[t]];
+  }
+}
+__global__ void k_halo_unpack_nb(int64_t nr, int C, const double* __restrict__ buf, double* __restrict__ ghost, int64_t ld) {
+  const int64_t n = nr * C;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t c = i / nr, t = i - c * nr;
+    ghost[c * ld + t] = buf[i];
+  }
+}
+static double* g_halo_rbuf = nullptr;
+static size_t g_halo_rbuf_cap = 0;
+
+static int halo_exchange_soa_packed(const Halo& h, int64_t nown, int C, double* vec, int64_t ld) {
+  const size_t need = (size_t)h.recv_ptr[h.nn] * C;
+  if (need > g_halo_rbuf_cap) {
+    dev_free(g_halo_rbuf);
+    MV_CHECK(dev_alloc(&g_halo_rbuf, need));
+    g_halo_rbuf_cap = need;
+  }
+  for (int k = 0; k < h.nn; ++k) {
+    const int64_t ns = h.send_ptr[k + 1] - h.send_ptr[k];
+    if (ns > 0)
+      MV_L k_halo_pack_nb<<<grid_for(ns * C), MV_BLOCK, 0, g_stream>>>(ns, C, h.send_idx + h.send_ptr[k], vec, ld,
+                                                                  h.send_buf + (size_t)C * h.send_ptr[k]);
+  }
+  MV_KERNEL_CHECK();
+  MV_NCCL(g_nccl.GroupStart());
+  for (int k = 0; k < h.nn; ++k) {
+    const int64_t ns = h.send_ptr[k + 1] - h.send_ptr[k], nr = h.recv_ptr[k + 1] - h.recv_ptr[k];
+    if (ns > 0) MV_NCCL(g_nccl.Send(h.send_buf + (size_t)C * h.send_ptr[k], (size_t)(ns * C), ncclDouble, h.ranks[k], g_comm, g_stream));
+    if (nr > 0) MV_NCCL(g_nccl.Recv(g_halo_rbuf + (size_t)C * h.recv_ptr[k], (size_t)(nr * C), ncclDouble, h.ranks[k], g_comm, g_stream));
+  }
+  MV_NCCL(g_nccl.GroupEnd());
+  for (int k = 0; k < h.nn; ++k) {
+    const int64_t nr = h.recv_ptr[k + 1] - h.recv_ptr[k];
+    if (nr > 0)
+      MV_L k_halo_unpack_nb<<<grid_for(nr * C), MV_BLOCK, 0, g_stream>>>(nr, C, g_halo_rbuf + (size_t)C * h.recv_ptr[k],
+                                                                    vec + nown + h.recv_ptr[k], ld);
+  }
+  MV_KERNEL_CHECK();
+  return MV_OK;
+}
+
 int halo_exchange_soa(const Halo& h, int64_t nown, int C, double* vec, int64_t ld) {
   if (!comm_active() || h.nn == 0) return MV_OK;
+  static int packed = -1;
+  if (packed < 0) { const char* e = getenv("MV_HALO_PACKED"); packed = e ? atoi(e) : 0; }
+  if (packed && C > 1) return halo_exchange_soa_packed(h, nown, C, vec, ld);
   const int64_t nsend = h.send_ptr[h.nn];
   if (nsend > 0) MV_L k_halo_pack_soa<<<grid_for(nsend * C), MV_BLOCK, 0, g_stream>>>(nsend, C, h.send_idx, vec, ld, h.send_buf);
   MV_KERNEL_CHECK();
