@@ -106,6 +106,15 @@ int mv_prof_enable(int on);
 int mv_prof_reset(void);
 int mv_prof_get(double* spmv_ms16, int64_t* spmv_count16, int64_t* pcg_iters16, int64_t* launches);
 
+/* True-residual audit of the preconditioned CG solves (the KSPs of movement/monge_ampere.py:441-448 and
+ * laplacian_smoothing.py:75 report the recurrence residual; PETSc's -ksp_true_residual_norm is the analogue).
+ * When enabled, every mv_pcg_solve / Poisson / Laplacian solve recomputes, at exit and with one extra SpMV, the
+ * Euclidean ||P(b - A x)|| / ||P b|| of the iterate it RETURNS (P: Dirichlet rows removed, mean removed for the
+ * singular operator), maximum over its right-hand sides.  Arrays of 16, indexed by the number of right-hand
+ * sides of the solve: running maximum, value of the last solve, number of audited solves.  Enabling resets.  */
+int mv_true_residual_enable(int on);
+int mv_true_residual_get(double* max_rel16, double* last_rel16, int64_t* count16);
+
 /* ---- ingest (replaces: movement/mover.py:49-102 -- mesh copy, function spaces, cell
  * volumes; monge_ampere.py:176-184 -- total volume; and the operator assembly Firedrake
  * does inside every LinearVariationalSolver: monge_ampere.py:327,437,476,
@@ -193,6 +202,9 @@ int mv_ma_eval_monitor(mv_ma* ma, const double* coords, double* m_out);
 int mv_ma_diagnostics(mv_ma* ma, int use_H_old, double* out);
 /* replaces: monge_ampere.py:419-449 + :535 -- K dphi = dt * residual, phi = phi_old+dphi */
 int mv_ma_pseudotimestep(mv_ma* ma, double pseudo_dt, int* iters);
+/* Initial guess of the Poisson solve: 1 (default) = Galerkin combination of the mover's two previous solves,
+ * 0 = zero, as a KSP without KSPSetInitialGuessNonzero starts (monge_ampere.py:441-448).  Process-wide.      */
+int mv_set_poisson_history(int on);
 /* replaces: monge_ampere.py:451-485 + :536 -- M H = -int div(tau).grad(phi) + bdry      */
 int mv_ma_equidistribute(mv_ma* ma, int* iters);
 /* replaces: monge_ampere.py:537-538 */
@@ -201,6 +213,15 @@ int mv_ma_advance(mv_ma* ma);
  * trace[K*6] receives mv_ma_diagnostics' output per iteration, cg_iters[K*3] the inner
  * iteration counts (l2 projection, poisson, hessian).                                */
 int mv_ma_relax_iterate(mv_ma* ma, double pseudo_dt, int niter, double* trace, int* cg_iters);
+/* replaces: the loop of monge_ampere.py:488-540 with its three exits (:518 converged, :525 diverged, :530 maxiter),
+ * for a built-in monitor: iterations i0, i0+1, ... (at most nmax in this call), each = l2 projection, x update +
+ * monitor, diagnostics, [exit tests], pseudo-timestep, Hessian recovery, advance (by pointer exchange).  res0: in/out
+ * initial residual (written at i == 0).  trace[nmax*6], cg_iters[nmax*3] as in mv_ma_relax_iterate.  info[0] = index
+ * i of the last iteration, info[1] = 0 converged / 1 diverged / 2 maxiter reached / 3 nmax done (call again with
+ * i0 = info[0] + 1), info[2] = number of trace lines written.  The tangling test of :244 looks at the xi-mesh, which
+ * is constant during the loop: the caller performs it once.                                                     */
+int mv_ma_relax_move(mv_ma* ma, double pseudo_dt, int i0, int nmax, int maxiter, double rtol, double dtol, double* res0,
+                     double* trace, int* cg_iters, int* info);
 
 /* ---- quasi-Newton (replaces: PETSc SNES newtonls + KSP gmres + PC fieldsplit behind
  * movement/monge_ampere.py:640-645,670-675,686-700 and movement/solver_parameters.py:1-47).
@@ -209,8 +230,10 @@ int mv_ma_relax_iterate(mv_ma* ma, double pseudo_dt, int niter, double* trace, i
  *   out[0..2] = ||F||^2, theta, relative l2 residual.  The caller performs update_monitor
  *   (monge_ampere.py:648-662) first with mv_ma_l2_project / mv_ma_update_coordinates.
  * mv_qn_solve: J Y = F by flexible GMRES(restart) right-preconditioned with the multiplicative
- *   fieldsplit [(M+K)^-1 ; M^-1] (inexact inner PCG: pc_rtol, pc_maxit); info[0..1] = iterations,
- *   relative residual.  mv_qn_save / mv_qn_set_iterate: (phi,H) = saved - lambda*Y (line search). */
+ *   fieldsplit [(M+K)^-1 ; M^-1] (inexact inner PCG: pc_rtol, pc_maxit); info[0..2] = iterations,
+ *   relative residual, restart length used (the requested one -- the reference's 200, solver_parameters.py:13 -- capped
+ *   by ksp_maxit and by the device memory the 2*restart+1 basis vectors need).  Returns MV_ERR_NOT_CONVERGED when the
+ *   residual test is not met after ksp_maxit iterations (PETSc: KSP_DIVERGED_ITS -> SNES_DIVERGED_LINEAR_SOLVE).  mv_qn_save / mv_qn_set_iterate: (phi,H) = saved - lambda*Y (line search). */
 int mv_qn_residual(mv_ma* ma, double* F, double* out);
 int mv_qn_jacobian_apply(mv_ma* ma, const double* z, double* y);
 int mv_qn_solve(mv_ma* ma, const double* F, double* Y, double ksp_rtol, int ksp_maxit, int restart,
@@ -256,11 +279,18 @@ int mv_spring_apply(mv_mesh* m, const double* coords, const uint16_t* mask, cons
 int mv_comm_unique_id(const char* nccl_lib_path, void* unique_id_128);
 int mv_comm_init(const char* nccl_lib_path, const void* unique_id_128, int rank, int nranks);
 int mv_comm_finalize(void);
+/* info[0] = 1 when the peer-memory collectives are active (halo exchange and scalar allreduce of the inner solvers as one
+ * kernel each over CUDA-IPC windows, NVLink peer stores; csrc/mv_p2p.cu; MV_P2P=0 keeps everything on NCCL),
+ * info[1], info[2] = halo exchanges / allreduces carried that way so far, info[3] = ranks.                          */
+int mv_comm_info(int64_t* info);
 /* halo plan: for each neighbour rank, the local owned vertices to send (send_idx grouped by
  * neighbour via send_ptr) and the contiguous ghost range received from it.             */
 int mv_mesh_set_halo(mv_mesh* m, int n_neighbours, const int32_t* neighbour_ranks,
                      const int64_t* send_ptr, const int32_t* send_idx, const int64_t* recv_ptr);
 int mv_halo_exchange(mv_mesh* m, int ncomp, double* vec);
+/* global numbers of the local cells [C] (host or device): the '+' cell of an interior edge (spring.py:113-127) is its
+ * lowest-numbered incident cell in the GLOBAL numbering, which the local order (owned cells first) does not preserve */
+int mv_mesh_set_cell_order(mv_mesh* m, const int64_t* global_cell);
 int mv_allreduce_sum(double* device_scalars, int n);
 
 #ifdef __cplusplus

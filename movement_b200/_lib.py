@@ -35,6 +35,8 @@ SIGNATURES = {
     "mv_prof_enable": (_i, [_i]),
     "mv_prof_reset": (_i, []),
     "mv_prof_get": (_i, [_pd, _pi64, _pi64, _pi64]),
+    "mv_true_residual_enable": (_i, [_i]),
+    "mv_true_residual_get": (_i, [_pd, _pd, _pi64]),
     "mv_mesh_create": (_i, [_i, _i64, _i64, _vp, _vp, _i64, _vp, _vp, _i64, _i64, C.POINTER(_vp)]),
     "mv_mesh_destroy": (None, [_vp]),
     "mv_mesh_info": (_i, [_vp, _pi64]),
@@ -60,9 +62,11 @@ SIGNATURES = {
     "mv_ma_eval_monitor": (_i, [_vp, _vp, _vp]),
     "mv_ma_diagnostics": (_i, [_vp, _i, _pd]),
     "mv_ma_pseudotimestep": (_i, [_vp, _d, _pi]),
+    "mv_set_poisson_history": (_i, [_i]),
     "mv_ma_equidistribute": (_i, [_vp, _pi]),
     "mv_ma_advance": (_i, [_vp]),
     "mv_ma_relax_iterate": (_i, [_vp, _d, _i, _pd, _pi]),
+    "mv_ma_relax_move": (_i, [_vp, _d, _i, _i, _i, _d, _d, _pd, _pd, _pi, _pi]),
     "mv_qn_residual": (_i, [_vp, _vp, _pd]),
     "mv_qn_jacobian_apply": (_i, [_vp, _vp, _vp]),
     "mv_qn_solve": (_i, [_vp, _vp, _vp, _d, _i, _i, _d, _i, _pd]),
@@ -80,7 +84,9 @@ SIGNATURES = {
     "mv_comm_unique_id": (_i, [C.c_char_p, _vp]),
     "mv_comm_init": (_i, [C.c_char_p, _vp, _i, _i]),
     "mv_comm_finalize": (_i, []),
+    "mv_comm_info": (_i, [_pi64]),
     "mv_mesh_set_halo": (_i, [_vp, _i, _vp, _vp, _vp, _vp]),
+    "mv_mesh_set_cell_order": (_i, [_vp, _vp]),
     "mv_halo_exchange": (_i, [_vp, _i, _vp]),
     "mv_allreduce_sum": (_i, [_vp, _i]),
 }

@@ -312,6 +312,7 @@ def device_mesh_from(mesh):
                                      L.ptr(np.ascontiguousarray(part.send_ptr, dtype=np.int64)),
                                      L.ptr(np.ascontiguousarray(part.send_idx, dtype=np.int32)),
                                      L.ptr(np.ascontiguousarray(part.recv_ptr, dtype=np.int64))))
+        L.check(lib.mv_mesh_set_cell_order(dm.handle, L.ptr(np.ascontiguousarray(part.global_cell, dtype=np.int64))))
         dm.global_cells = part.global_num_cells
         dm.global_vertices = part.global_num_vertices
     else:

@@ -187,7 +187,7 @@ int amg_exchange_prolongator(const Halo& H, int64_t n, int64_t ntot, const Csr& 
   dev_free(scol); dev_free(sval); dev_free(gcol); dev_free(gval);
   *ntot_c = nc_own + nghost_c;
   *gid_c = gid;
-  return MV_OK;
+  return halo_finalize(Hc);
 }
 
 // ------------------------------------------------------------------ coarsest level, gathered on every rank

@@ -78,6 +78,7 @@ int comm_size() { return g_nranks; }
 
 int allreduce_dev(double* d, int n, int op) {
   if (!comm_active()) return MV_OK;
+  if (p2p_allreduce_fits(n)) return p2p_allreduce(d, n, op, nullptr);   // one kernel over the peer windows (mv_p2p.cu)
   const ncclRedOp_t rop = op == 0 ? ncclSum : (op == 1 ? ncclMax : ncclMin);
   MV_NCCL(g_nccl.AllReduce(d, d, (size_t)n, ncclDouble, rop, g_comm, g_stream));
   return MV_OK;
@@ -114,6 +115,7 @@ k_halo_pack(int64_t n, const int* __restrict__ idx, const double* __restrict__ v
 int halo_exchange(mv_mesh* m, int C, double* vec) {
   if (!comm_active() || m->halo.nn == 0) return MV_OK;
   Halo& h = m->halo;
+  if (C <= h.p2p_maxC) return p2p_halo_exchange(h, m->Vown, C, vec, m->V, false, nullptr);
   const int64_t nsend = h.send_ptr[h.nn];
   const int grid = grid_for(nsend * C);
   switch (C) {
@@ -244,8 +246,28 @@ static int halo_exchange_soa_packed(const Halo& h, int64_t nown, int C, double* 
   return MV_OK;
 }
 
+// Collective (every rank, once per halo plan): the peer-memory path carries an exchange of C components only if the
+// largest message of ANY rank fits a window slot -- a per-rank decision could pair a peer-memory sender with an NCCL receiver.
+int halo_finalize(Halo& h) {
+  h.p2p_maxC = 0;
+  if (!comm_active() || !p2p_active()) return MV_OK;
+  double m = 0.0;
+  for (int k = 0; k < h.nn; ++k) {
+    const double ns = (double)(h.send_ptr[k + 1] - h.send_ptr[k]), nr = (double)(h.recv_ptr[k + 1] - h.recv_ptr[k]);
+    m = fmax(m, fmax(ns, nr));
+  }
+  double nn = (double)h.nn;
+  MV_CHECK(allreduce_host(&m, 1, 1));
+  MV_CHECK(allreduce_host(&nn, 1, 1));
+  if (nn > 16.0) return MV_OK;
+  const double fit = m > 0.0 ? floor((double)p2p_slot_bytes() / (sizeof(double) * m)) : 64.0;
+  h.p2p_maxC = fit > 64.0 ? 64 : (int)fit;
+  return MV_OK;
+}
+
 int halo_exchange_soa(const Halo& h, int64_t nown, int C, double* vec, int64_t ld) {
   if (!comm_active() || h.nn == 0) return MV_OK;
+  if (C <= h.p2p_maxC) return p2p_halo_exchange(h, nown, C, vec, ld, true, nullptr);
   static int packed = -1;
   if (packed < 0) { const char* e = getenv("MV_HALO_PACKED"); packed = e ? atoi(e) : 0; }
   if (packed && C > 1) return halo_exchange_soa_packed(h, nown, C, vec, ld);
@@ -278,6 +300,20 @@ extern "C" int mv_comm_unique_id(const char* nccl_lib_path, void* unique_id_128)
   return MV_OK;
 }
 
+// host bytes of every rank, concatenated in rank order (set-up only): staged through the device for ncclAllGather
+static int allgather_host_bytes(const void* sendbuf, void* recvbuf, size_t bytes) {
+  unsigned char *ds = nullptr, *dr = nullptr;
+  MV_CUDA(cudaMalloc((void**)&ds, bytes));
+  MV_CUDA(cudaMalloc((void**)&dr, bytes * g_nranks));
+  MV_CUDA(cudaMemcpyAsync(ds, sendbuf, bytes, cudaMemcpyHostToDevice, g_stream));
+  MV_NCCL(g_nccl.AllGather(ds, dr, bytes, ncclChar, g_comm, g_stream));
+  MV_CUDA(cudaMemcpyAsync(recvbuf, dr, bytes * g_nranks, cudaMemcpyDeviceToHost, g_stream));
+  MV_CUDA(cudaStreamSynchronize(g_stream));
+  cudaFree(ds);
+  cudaFree(dr);
+  return MV_OK;
+}
+
 extern "C" int mv_comm_init(const char* nccl_lib_path, const void* unique_id_128, int rank, int nranks) {
   if (!unique_id_128 || rank < 0 || rank >= nranks) return MV_ERR_BADARG;
   MV_CHECK(load_nccl(nccl_lib_path));
@@ -286,10 +322,25 @@ extern "C" int mv_comm_init(const char* nccl_lib_path, const void* unique_id_128
   MV_NCCL(g_nccl.CommInitRank(&g_comm, nranks, id, rank));
   g_rank = rank;
   g_nranks = nranks;
+  // peer-memory windows for the latency-critical collectives (mv_p2p.cu); NCCL stays for set-up and large messages
+  MV_CHECK(p2p_init(rank, nranks, allgather_host_bytes));
+  return MV_OK;
+}
+
+// info[0] = 1 if the peer-memory path is active, info[1] / info[2] = halo exchanges / allreduces it has carried
+extern "C" int mv_comm_info(int64_t* info) {
+  if (!info) return MV_ERR_BADARG;
+  long long h = 0, r = 0;
+  p2p_counts(&h, &r);
+  info[0] = p2p_active() ? 1 : 0;
+  info[1] = h;
+  info[2] = r;
+  info[3] = g_nranks;
   return MV_OK;
 }
 
 extern "C" int mv_comm_finalize(void) {
+  p2p_finalize();
   if (g_comm) {
     cudaStreamSynchronize(g_stream);
     g_nccl.CommDestroy(g_comm);
@@ -320,7 +371,7 @@ extern "C" int mv_mesh_set_halo(mv_mesh* m, int nn, const int32_t* ranks, const 
   MV_CHECK(dev_alloc(&h.send_buf, nsend * (size_t)(m->dim * m->dim)));
   if (nsend) MV_CUDA(cudaMemcpyAsync(h.send_idx, send_idx, nsend * sizeof(int), cudaMemcpyDefault, g_stream));
   MV_CUDA(cudaStreamSynchronize(g_stream));
-  return MV_OK;
+  return halo_finalize(h);
 }
 
 extern "C" int mv_halo_exchange(mv_mesh* m, int ncomp, double* vec) {

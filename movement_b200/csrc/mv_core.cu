@@ -24,6 +24,7 @@ int pool_init() {
 int g_nsm = 0;
 long long g_launches = 0;
 Prof g_prof;
+TrueRes g_trueres;
 
 int prof_begin(int ncomp) {
   Prof& p = g_prof;
@@ -273,6 +274,19 @@ extern "C" int mv_prof_get(double* spmv_ms16, int64_t* spmv_count16, int64_t* pc
     if (pcg_iters16) pcg_iters16[i] = g_prof.pcg_iters[i];
   }
   if (launches) *launches = g_launches;
+  return MV_OK;
+}
+extern "C" int mv_true_residual_enable(int on) {
+  g_trueres.on = on != 0;
+  for (int i = 0; i < 16; ++i) { g_trueres.max_rel[i] = 0; g_trueres.last_rel[i] = 0; g_trueres.count[i] = 0; }
+  return MV_OK;
+}
+extern "C" int mv_true_residual_get(double* max_rel16, double* last_rel16, int64_t* count16) {
+  for (int i = 0; i < 16; ++i) {
+    if (max_rel16) max_rel16[i] = g_trueres.max_rel[i];
+    if (last_rel16) last_rel16[i] = g_trueres.last_rel[i];
+    if (count16) count16[i] = g_trueres.count[i];
+  }
   return MV_OK;
 }
 extern "C" int mv_sync(void) {

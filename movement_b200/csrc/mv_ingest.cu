@@ -491,7 +491,7 @@ extern "C" void mv_mesh_destroy(mv_mesh* m) {
   dev_free(m->v2f_ptr); dev_free(m->v2f);
   dev_free(m->pat.slice_ptr); dev_free(m->pat.cols); dev_free(m->pat.row_nnz); dev_free(m->pat.sched);
   dev_free(m->Mval); dev_free(m->Kval); dev_free(m->MKval); dev_free(m->ml); dev_free(m->vol);
-  dev_free(m->dinvM); dev_free(m->dinvK); dev_free(m->dinvMK); dev_free(m->edge_opp);
+  dev_free(m->dinvM); dev_free(m->dinvK); dev_free(m->dinvMK); dev_free(m->edge_opp); dev_free(m->cell_gid);
   dev_free(m->red.partials); dev_free(m->red.counter);
   dev_free(m->pcg.r); dev_free(m->pcg.p); dev_free(m->pcg.q); dev_free(m->pcg.xs); dev_free(m->pcg.scal); dev_free(m->pcg.flags);
   if (m->pcg.h_flags) cudaFreeHost(m->pcg.h_flags);

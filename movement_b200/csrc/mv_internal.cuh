@@ -39,6 +39,16 @@ struct Prof {
   long long pcg_iters[16] = {0};
 };
 extern Prof g_prof;
+// True-residual audit of the preconditioned CG (mv_true_residual_*): at the exit of a solve the Euclidean
+// ||P(b - A x)|| / ||P b|| of the RETURNED iterate is recomputed with one extra SpMV (the recurrence r -= alpha q
+// that the stopping rule watches can drift from it), indexed by the number of right-hand sides like Prof.
+struct TrueRes {
+  bool on = false;
+  double max_rel[16] = {0};
+  double last_rel[16] = {0};
+  long long count[16] = {0};
+};
+extern TrueRes g_trueres;
 int prof_begin(int ncomp);   // returns slot or -1
 void prof_end(int slot);
 void prof_drain();           // stream must be synchronised
@@ -123,6 +133,7 @@ struct Halo {
   std::vector<int64_t> send_ptr, recv_ptr;  // host copies
   int* send_idx = nullptr;                  // device [send_ptr[nn]]
   double* send_buf = nullptr;               // device [send_ptr[nn]*MV_MAX_COMP]
+  int p2p_maxC = 0;                         // components per exchange that fit the peer-memory slots on EVERY rank (0: NCCL path)
 };
 
 struct Reduce {
@@ -225,6 +236,7 @@ struct mv_mesh {
   double total_volume = 0, ml_sumsq = 0, ml_sum = 0;
   // spring data (lazy)
   int* edge_opp = nullptr;   // [sell_len] opposite vertex of the '+' cell for (row,col)
+  int64_t* cell_gid = nullptr;   // [C] global cell numbers (partitioned meshes only; mv_mesh_set_cell_order)
   // work
   mv::Reduce red;
   mv::PcgWork pcg;
@@ -266,6 +278,9 @@ struct mv_ma {
 
 namespace mv {
 
+// device scalar slots of mv_ma::dscal (mv_ma.cu, mv_qn.cu)
+enum { D_MONMAX = 0, D_SUMA = 1, D_THETA = 2, D_RES2 = 3, D_VSUM = 4, D_VMAX = 5, D_VMIN = 6, D_VSSD = 7, D_N = 16 };
+
 // PCG device scalar slots: scal[slot*16 + comp]
 enum { S_RZ = 0, S_PQ = 1, S_RZNEW = 2, S_BETA = 3, S_THR = 4, S_REF = 5, S_BB = 6, S_SUM = 7, S_NSLOTS = 8 };
 #define SC(slot, c) ((slot) * 16 + (c))
@@ -278,7 +293,7 @@ struct LinOp {
   const double* spring_coords = nullptr;
 };
 int spring_apply_dev(mv_mesh* m, const double* coords, const uint16_t* mask, const double* x, double* y, bool dot);
-int pcg_solve_spring(mv_mesh* m, const double* coords, const double* dinv_dof, double* x, const uint16_t* mask,
+int pcg_solve_spring(mv_mesh* m, const double* coords, const double* dinv_dof, const double* rhs, double* x, const uint16_t* mask,
                      double rtol, double atol, int maxit, int* iters);
 int ensure_pcg_workspace(mv_mesh* m);
 int exclusive_scan_i32(const int* in, int* out, int64_t n);
@@ -297,6 +312,17 @@ extern int g_mass_solver;
 int cheb_mass_solve(mv_mesh* m, int ncomp, const double* val, const double* dinv, const double* rhs, double* x,
                     const uint16_t* mask, double rtol, double atol, int maxit, int* iters, double* relres);
 int halo_exchange_soa(const Halo& h, int64_t nown, int C, double* vec, int64_t ld);
+int halo_finalize(Halo& h);   // collective: decides whether the peer-memory path can carry this halo
+// peer-memory collectives (mv_p2p.cu)
+bool p2p_active();
+int p2p_init(int rank, int nranks, int (*allgather_bytes)(const void* sendbuf, void* recvbuf, size_t bytes));
+void p2p_finalize();
+size_t p2p_slot_bytes();
+int p2p_halo_exchange(const Halo& h, int64_t nown, int C, double* vec, int64_t ld, bool soa, const int* done);
+bool p2p_allreduce_fits(int n);
+int p2p_allreduce(double* d, int n, int op, const int* done);
+int p2p_check_status();
+void p2p_counts(long long* halo, long long* red);
 int op_arrays(mv_mesh* m, int op, const double** val, const double** dinv);
 int halo_exchange(mv_mesh* m, int ncomp, double* vec);
 int allreduce_sum_dev(double* dscal, int n);

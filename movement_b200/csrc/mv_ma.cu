@@ -10,8 +10,6 @@
 
 namespace mv {
 
-// device scalar slots of mv_ma::dscal
-enum { D_MONMAX = 0, D_SUMA = 1, D_THETA = 2, D_RES2 = 3, D_VSUM = 4, D_VMAX = 5, D_VMIN = 6, D_VSSD = 7, D_N = 16 };
 
 // ------------------------------------------------------------------ quadrature tables
 // 2D: Dunavant 6-point rule, exact to degree 4 = d+2.  3D: 14-point rule exact to degree
@@ -890,6 +888,12 @@ k_hist_guess(int64_t n, const double* __restrict__ x1, const double* __restrict_
     x0[v] = x2 ? fma(a2, x2[v], a1 * x1[v]) : a1 * x1[v];
 }
 
+static int g_poisson_history = -1;   // -1: read MV_POISSON_HISTORY (default on)
+extern "C" int mv_set_poisson_history(int on) {
+  g_poisson_history = on ? 1 : 0;
+  return MV_OK;
+}
+
 extern "C" int mv_ma_pseudotimestep(mv_ma* ma, double dt, int* iters) {
   if (!ma) return MV_ERR_BADARG;
   MA_REQUIRE(ma, MV_F_PHI);
@@ -899,8 +903,8 @@ extern "C" int mv_ma_pseudotimestep(mv_ma* ma, double dt, int* iters) {
   const int64_t n = m->Vown;
   const int gv = grid_for(n);
   MV_L k_scale<<<gv, MV_BLOCK, 0, g_stream>>>(n, dt, ma->f[MV_F_RESIDUAL], ma->rhs);
-  static int use_hist = -1;
-  if (use_hist < 0) { const char* e = getenv("MV_POISSON_HISTORY"); use_hist = e ? atoi(e) : 1; }
+  if (g_poisson_history < 0) { const char* e = getenv("MV_POISSON_HISTORY"); g_poisson_history = e ? atoi(e) : 1; }
+  const int use_hist = g_poisson_history;
   if (use_hist && ma->hist_n > 0) {
     const bool two = ma->hist_n > 1;
     MV_L k_hist_dots<<<gv, MV_BLOCK, 0, g_stream>>>(n, ma->hist_x[0], ma->hist_b[0], two ? ma->hist_x[1] : nullptr,
@@ -977,4 +981,69 @@ extern "C" int mv_ma_relax_iterate(mv_ma* ma, double dt, int niter, double* trac
     if (cg_iters) for (int k = 0; k < 3; ++k) cg_iters[i * 3 + k] = it[k];
   }
   return MV_OK;
+}
+
+// The whole relaxation loop of movement/monge_ampere.py:488-540 behind one call: iterations i0, i0+1, ... until the
+// residual test passes, the divergence test fires, `maxiter` is reached or `nmax` iterations were done in this call
+// (the caller prints the trace lines of a chunk and calls again).  phi/phi_old and H/H_old are advanced by swapping
+// the bound pointers instead of copying 8(1+d^2) B per vertex; on return all four user buffers hold what the
+// reference's fields hold at that point (phi == phi_old, H == H_old after an advance).
+//   res0: in/out initial residual (set at i == 0);  info[0] = last iteration index i, info[1] = status
+//   (0 converged, 1 diverged, 2 maxiter reached, 3 chunk exhausted -- call again with i0 = info[0] + 1).
+extern "C" int mv_ma_relax_move(mv_ma* ma, double dt, int i0, int nmax, int maxiter, double rtol, double dtol, double* res0,
+                                double* trace, int* cg_iters, int* info) {
+  if (!ma || !res0 || !info || nmax < 1) return MV_ERR_BADARG;
+  if (ma->mon_kind == MV_MON_USER) {
+    set_error("mv_ma_relax_move needs a built-in monitor");
+    return MV_ERR_BADARG;
+  }
+  MA_REQUIRE(ma, MV_F_PHI); MA_REQUIRE(ma, MV_F_PHI_OLD); MA_REQUIRE(ma, MV_F_H); MA_REQUIRE(ma, MV_F_H_OLD);
+  mv_mesh* m = ma->mesh;
+  const int dd = m->dim * m->dim;
+  double* const user_phi = ma->f[MV_F_PHI];
+  double* const user_phi_old = ma->f[MV_F_PHI_OLD];
+  double* const user_H = ma->f[MV_F_H];
+  double* const user_H_old = ma->f[MV_F_H_OLD];
+  int status = 3, i = i0, st = MV_OK, done = 0;
+  bool advanced = false;
+  for (int k = 0; k < nmax && i < maxiter; ++k, ++i) {
+    int it[3] = {0, 0, 0};
+    double out[6];
+    if ((st = mv_ma_l2_project(ma, &it[0])) != MV_OK) break;
+    if ((st = mv_ma_update_coordinates(ma)) != MV_OK) break;
+    if ((st = mv_ma_diagnostics(ma, 1, out)) != MV_OK) break;
+    if (trace) for (int q = 0; q < 6; ++q) trace[k * 6 + q] = out[q];
+    ++done;
+    const double residual = out[1];
+    if (i == 0) *res0 = residual;
+    if (residual < rtol) { status = 0; }
+    else if (residual > dtol * *res0) { status = 1; }
+    else if (i == maxiter - 1) { status = 2; }
+    if (status != 3) {
+      if (cg_iters) { cg_iters[k * 3] = it[0]; cg_iters[k * 3 + 1] = 0; cg_iters[k * 3 + 2] = 0; }
+      break;
+    }
+    if ((st = mv_ma_pseudotimestep(ma, dt, &it[1])) != MV_OK) break;
+    if ((st = mv_ma_equidistribute(ma, &it[2])) != MV_OK) break;
+    // advance (monge_ampere.py:537-538) by exchanging the roles of the buffers
+    double* t = ma->f[MV_F_PHI]; ma->f[MV_F_PHI] = ma->f[MV_F_PHI_OLD]; ma->f[MV_F_PHI_OLD] = t;
+    t = ma->f[MV_F_H]; ma->f[MV_F_H] = ma->f[MV_F_H_OLD]; ma->f[MV_F_H_OLD] = t;
+    advanced = true;
+    if (cg_iters) for (int q = 0; q < 3; ++q) cg_iters[k * 3 + q] = it[q];
+  }
+  if (status == 3 && st == MV_OK) --i;   // chunk exhausted: i is the last completed iteration
+  // hand the fields back: the newest iterate sits in f[*_OLD] after an advance; both user buffers get it
+  const double* newest_phi = ma->f[MV_F_PHI_OLD];
+  const double* newest_H = ma->f[MV_F_H_OLD];
+  ma->f[MV_F_PHI] = user_phi; ma->f[MV_F_PHI_OLD] = user_phi_old; ma->f[MV_F_H] = user_H; ma->f[MV_F_H_OLD] = user_H_old;
+  if (advanced) {
+    if (newest_phi != user_phi_old) MV_CUDA(cudaMemcpyAsync(user_phi_old, newest_phi, m->V * sizeof(double), cudaMemcpyDeviceToDevice, g_stream));
+    else MV_CUDA(cudaMemcpyAsync(user_phi, newest_phi, m->V * sizeof(double), cudaMemcpyDeviceToDevice, g_stream));
+    if (newest_H != user_H_old) MV_CUDA(cudaMemcpyAsync(user_H_old, newest_H, m->V * dd * sizeof(double), cudaMemcpyDeviceToDevice, g_stream));
+    else MV_CUDA(cudaMemcpyAsync(user_H, newest_H, m->V * dd * sizeof(double), cudaMemcpyDeviceToDevice, g_stream));
+  }
+  info[0] = i;
+  info[1] = status;
+  info[2] = done;
+  return st;
 }

@@ -70,7 +70,7 @@ __device__ __forceinline__ EdgeBlock edge_block(const double* __restrict__ X, in
 __global__ void __launch_bounds__(MV_BLOCK)
 k_edge_opp(const int* __restrict__ cells, const int* __restrict__ v2c_ptr, const int* __restrict__ v2c, int64_t nrows,
            const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols, const int* __restrict__ row_nnz,
-           int* __restrict__ opp) {
+           const int64_t* __restrict__ cell_gid, int* __restrict__ opp) {
   for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < nrows; v += (int64_t)gridDim.x * blockDim.x) {
     const int64_t s = v / MV_SLICE;
     const int64_t base = slice_ptr[s] + (v % MV_SLICE);
@@ -81,11 +81,20 @@ k_edge_opp(const int* __restrict__ cells, const int* __restrict__ v2c_ptr, const
       const int u = cols[pos];
       int o = -1;
       if (k < nn && u != v) {
-        // the global lowest cell containing both v and u: cells are listed ascending per vertex
-        for (int t = v2c_ptr[v]; t < v2c_ptr[v + 1] && o < 0; ++t) {
+        // the lowest-numbered cell containing both v and u.  One GPU: cells are listed ascending per vertex, the first hit
+        // wins.  Partitioned: the local cell order (owned cells first) is not the global one, so the hit with the smallest
+        // GLOBAL cell number wins (cell_gid, mv_mesh_set_cell_order) -- every rank then picks the same '+' cell.
+        int64_t best = -1;
+        for (int t = v2c_ptr[v]; t < v2c_ptr[v + 1] && (o < 0 || cell_gid); ++t) {
           const int64_t c = v2c[t] / 3;
           const int c0 = cells[c * 3], c1 = cells[c * 3 + 1], c2 = cells[c * 3 + 2];
-          if (c0 == u || c1 == u || c2 == u) o = (c0 != u && c0 != v) ? c0 : ((c1 != u && c1 != v) ? c1 : c2);
+          if (c0 == u || c1 == u || c2 == u) {
+            const int64_t g = cell_gid ? cell_gid[c] : c;
+            if (o < 0 || g < best) {
+              best = g;
+              o = (c0 != u && c0 != v) ? c0 : ((c1 != u && c1 != v) ? c1 : c2);
+            }
+          }
         }
       }
       opp[pos] = o;
@@ -209,7 +218,7 @@ static int ensure_edge_opp(mv_mesh* m) {
   if (m->edge_opp) return MV_OK;
   MV_CHECK(dev_alloc(&m->edge_opp, m->pat.len));
   MV_L k_edge_opp<<<grid_for(m->Vown), MV_BLOCK, 0, g_stream>>>(m->cells, m->v2c_ptr, m->v2c, m->Vown, m->pat.slice_ptr, m->pat.cols,
-                                                         m->pat.row_nnz, m->edge_opp);
+                                                         m->pat.row_nnz, m->cell_gid, m->edge_opp);
   MV_KERNEL_CHECK();
   return MV_OK;
 }
@@ -258,6 +267,17 @@ extern "C" int mv_laplace_move(mv_mesh* m, double* v, const uint16_t* mask, doub
   MV_CUDA(cudaMemcpyAsync(&h, dout, sizeof(double), cudaMemcpyDeviceToHost, g_stream));
   MV_CUDA(cudaStreamSynchronize(g_stream));
   if (displacement_norm) *displacement_norm = sqrt(h);
+  return MV_OK;
+}
+
+// global cell numbers of the local cells (partitioned meshes): the '+' cell of an edge is its lowest GLOBAL cell
+extern "C" int mv_mesh_set_cell_order(mv_mesh* m, const int64_t* global_cell) {
+  if (!m || !global_cell) return MV_ERR_BADARG;
+  dev_free(m->cell_gid);
+  dev_free(m->edge_opp);
+  MV_CHECK(dev_alloc(&m->cell_gid, (size_t)m->C));
+  MV_CUDA(cudaMemcpyAsync(m->cell_gid, global_cell, m->C * sizeof(int64_t), cudaMemcpyDefault, g_stream));
+  MV_CUDA(cudaStreamSynchronize(g_stream));
   return MV_OK;
 }
 
@@ -331,12 +351,18 @@ extern "C" int mv_spring_move(mv_mesh* m, double* coords, const double* forcing,
   MV_L k_zero_free<2><<<grid_for(n * 2), MV_BLOCK, 0, g_stream>>>(n, sm.as<uint16_t>(), u);
   MV_L k_spring_diag<<<grid_for(n), MV_BLOCK, 0, g_stream>>>(n, m->pat.slice_ptr, m->pat.cols, m->edge_opp, coords, dinv);
   MV_KERNEL_CHECK();
-  int st = pcg_solve_spring(m, coords, dinv, u, sm.as<uint16_t>(), rtol, atol, maxit, iters);
+  // right-hand side = the forcing vector: its rows at Dirichlet dofs are replaced (u = forcing there), its rows at free
+  // dofs are whatever earlier calls left in _forcing (spring.py:229-230 never clears it), normally zero
+  int st = pcg_solve_spring(m, coords, dinv, sf.as<double>(), u, sm.as<uint16_t>(), rtol, atol, maxit, iters);
   if (st != MV_OK) return st;
   double* dout = m->pcg.scal + SC(S_SUM, 8);
   MV_L k_axpy_norm<<<grid_for(n * 2), MV_BLOCK, 0, g_stream>>>(n * 2, dt, u, coords, displacement, m->red.partials, m->red.counter,
                                                          dout);
   MV_KERNEL_CHECK();
+  if (comm_active()) {
+    MV_CHECK(allreduce_sum_dev(dout, 1));
+    MV_CHECK(halo_exchange(m, 2, coords));   // the next call's stiffness reads the ghost coordinates
+  }
   double h = 0.0;
   MV_CUDA(cudaMemcpyAsync(&h, dout, sizeof(double), cudaMemcpyDeviceToHost, g_stream));
   MV_CUDA(cudaStreamSynchronize(g_stream));

@@ -438,7 +438,7 @@ int pcg_solve(mv_mesh* m, int op, int ncomp, const double* rhs, double* x, const
   return pcg_solve_soa(m, ncomp, lop.val, lop.dinv, rhs, x, mask, rtol, atol, maxit, project_mean, iters, relres, pc);
 }
 
-int pcg_solve_spring(mv_mesh* m, const double* coords, const double* dinv_dof, double* x, const uint16_t* mask,
+int pcg_solve_spring(mv_mesh* m, const double* coords, const double* dinv_dof, const double* rhs, double* x, const uint16_t* mask,
                      double rtol, double atol, int maxit, int* iters) {
   LinOp lop;
   lop.val = nullptr;
@@ -446,7 +446,7 @@ int pcg_solve_spring(mv_mesh* m, const double* coords, const double* dinv_dof, d
   lop.dpd = 1;
   lop.coupled = 1;
   lop.spring_coords = coords;
-  return pcg_impl<2>(m, lop, nullptr, x, mask, rtol, atol, maxit, 0, iters, nullptr);
+  return pcg_impl<2>(m, lop, rhs, x, mask, rtol, atol, maxit, 0, iters, nullptr);
 }
 
 int ensure_pcg_workspace(mv_mesh* m) { return ensure_pcg_work(m); }

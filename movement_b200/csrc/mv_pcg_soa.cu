@@ -316,6 +316,37 @@ k_dir_z_soa(int64_t n, int64_t ld, const double* __restrict__ z, double* __restr
   }
 }
 
+// audit: sums |P(b - mean - q)|^2 and |P(b - mean)|^2 per component, q = A x component-major, b interleaved
+template <int C>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_true_res_soa(int64_t n, int64_t ld, const double* __restrict__ b, const double* __restrict__ q, const uint16_t* __restrict__ mask,
+               double* __restrict__ partials, unsigned* __restrict__ counter, double* __restrict__ scal, double inv_nglobal,
+               int project_mean) {
+  double acc[2 * C];
+#pragma unroll
+  for (int c = 0; c < 2 * C; ++c) acc[c] = 0.0;
+  double mean[C];
+#pragma unroll
+  for (int c = 0; c < C; ++c) mean[c] = project_mean ? scal[SC(S_SUM, c)] * inv_nglobal : 0.0;
+  VERTEX_LOOP(v, n) {
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      if (fixed_dof<C>(mask, v, c)) continue;
+      const double bb = b ? (b[v * C + c] - mean[c]) : 0.0;
+      const double rr = bb - q[c * ld + v];
+      acc[c] = fma(rr, rr, acc[c]);
+      acc[C + c] = fma(bb, bb, acc[C + c]);
+    }
+  }
+  grid_reduce_sum<2 * C>(acc, partials, counter, [&](double(&t)[2 * C]) {
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      scal[SC(S_RZNEW, c)] = t[c];
+      scal[SC(S_PQ, c)] = t[C + c];
+    }
+  });
+}
+
 template <int C>
 __global__ void __launch_bounds__(MV_BLOCK)
 k_comp_sum_aos(int64_t n, const double* __restrict__ x, double* __restrict__ partials, unsigned* __restrict__ counter,
@@ -487,6 +518,34 @@ int pcg_soa(mv_mesh* m, const double* val, const double* dinv, const double* rhs
   }
   const int done = w.h_flags[0], niter = w.h_flags[1], breakdown = w.h_flags[2];
   g_prof.pcg_iters[C & 15] += niter;
+  if (g_trueres.on) {
+    // audit of the returned iterate: q = A x, then ||P(b - q)|| / ||P b|| (Euclidean) per right-hand side
+    if (project_mean && rhs) {
+      MV_L k_comp_sum_aos<C><<<gv, MV_BLOCK, 0, g_stream>>>(n, rhs, m->red.partials, m->red.counter, w.scal);
+      if (dist) MV_CHECK(allreduce_sum_dev(w.scal + SC(S_SUM, 0), C));
+    }
+    if (dist) MV_CHECK(halo_exchange_soa(m->halo, n, C, xs, ld));
+    MV_CHECK(spmv_soa_launch<C>(m, val, xs, w.q, ld, false));
+    MV_L k_true_res_soa<C><<<gv, MV_BLOCK, 0, g_stream>>>(n, ld, rhs, w.q, mask, m->red.partials, m->red.counter, w.scal, inv_ng,
+                                                     project_mean && rhs ? 1 : 0);
+    MV_KERNEL_CHECK();
+    if (dist) {
+      MV_CHECK(allreduce_sum_dev(w.scal + SC(S_RZNEW, 0), C));
+      MV_CHECK(allreduce_sum_dev(w.scal + SC(S_PQ, 0), C));
+    }
+    MV_CUDA(cudaMemcpyAsync(w.h_scal, w.scal, S_NSLOTS * 16 * sizeof(double), cudaMemcpyDeviceToHost, g_stream));
+    MV_CUDA(cudaStreamSynchronize(g_stream));
+    double worst = 0.0;
+    for (int c = 0; c < C; ++c) {
+      const double num = w.h_scal[SC(S_RZNEW, c)], den = w.h_scal[SC(S_PQ, c)];
+      const double rel = den > 0.0 ? sqrt(num / den) : 0.0;
+      if (rel > worst) worst = rel;
+    }
+    TrueRes& t = g_trueres;
+    t.last_rel[C & 15] = worst;
+    if (worst > t.max_rel[C & 15]) t.max_rel[C & 15] = worst;
+    t.count[C & 15] += 1;
+  }
   if (C > 1) MV_L k_soa_to_aos<C><<<grid_for(n), MV_BLOCK, 0, g_stream>>>(n, xs, ld, x);
   if (project_mean) {
     MV_L k_comp_sum_aos<C><<<gv, MV_BLOCK, 0, g_stream>>>(n, x, m->red.partials, m->red.counter, w.scal);

@@ -105,6 +105,12 @@ static int qn_setup(mv_ma* ma, Qn& q) {
   q.nv = q.m->Vown;
   q.N = q.nv * (1 + q.dd);
   mv_mesh* m = q.m;
+  for (int fld : {MV_F_PHI, MV_F_H, MV_F_MONITOR, MV_F_RESIDUAL}) {
+    if (!ma->f[fld]) {
+      set_error("mv_qn: field %d not bound", fld);
+      return MV_ERR_BADARG;
+    }
+  }
   if (!ma->qn_w) {
     MV_CHECK(dev_alloc(&ma->qn_w, (size_t)q.N));
     MV_CHECK(dev_alloc(&ma->qn_gphi, (size_t)m->V));
@@ -248,9 +254,9 @@ extern "C" int mv_qn_residual(mv_ma* ma, double* F, double* out) {
   }
   // F_psi = -(a - theta m_l)
   MV_CHECK(assemble_a_dev(m, ma->f[MV_F_MONITOR], ma->f[MV_F_H], ma->a, ma->dscal));
-  if (dist) MV_CHECK(allreduce_sum_dev(ma->dscal + 1, 1));
+  if (dist) MV_CHECK(allreduce_sum_dev(ma->dscal + D_SUMA, 1));
   double suma = 0.0;
-  MV_CUDA(cudaMemcpyAsync(&suma, ma->dscal + 1, sizeof(double), cudaMemcpyDeviceToHost, g_stream));
+  MV_CUDA(cudaMemcpyAsync(&suma, ma->dscal + D_SUMA, sizeof(double), cudaMemcpyDeviceToHost, g_stream));
   MV_CUDA(cudaStreamSynchronize(g_stream));
   const double theta = suma / gtot;
   // residual vector r = a - theta*ml into F_psi with a minus sign: reuse k_axpy_from (out = base - lambda*y)
@@ -322,8 +328,20 @@ extern "C" int mv_qn_solve(mv_ma* ma, const double* F, double* Y, double ksp_rto
   if (!ma || !F || !Y) return MV_ERR_BADARG;
   Qn q;
   MV_CHECK(qn_setup(ma, q));
-  if (restart < 1) restart = 30;
-  if (restart > 40) restart = 40;
+  // ksp_gmres_restart (movement/solver_parameters.py:13 sets 200 = ksp_max_it, i.e. no restart in the reference).  The
+  // Krylov basis of flexible GMRES costs 2 * restart + 1 vectors of V (1 + d^2) doubles, so the value is honoured up to what
+  // fits in 60 % of the free device memory (never below 5); info[2] reports the value used.  A solve that needs fewer
+  // iterations than that -- the normal case, 10-30 with this preconditioner -- is identical to the unrestarted one.
+  if (restart < 1) restart = 200;
+  if (restart > ksp_maxit && ksp_maxit >= 1) restart = ksp_maxit;
+  {
+    size_t free_b = 0, total_b = 0;
+    MV_CUDA(cudaMemGetInfo(&free_b, &total_b));
+    if (ma->qn_basis) free_b += (size_t)q.N * (2 * ma->qn_restart + 1) * sizeof(double);
+    const double cap = (0.6 * (double)free_b / ((double)q.N * sizeof(double)) - 1.0) / 2.0;
+    const int icap = cap < 5.0 ? 5 : (cap > 1e6 ? 1000000 : (int)cap);
+    if (restart > icap) restart = icap;
+  }
   if (ma->qn_restart != restart) {
     dev_free(ma->qn_basis);
     MV_CHECK(dev_alloc(&ma->qn_basis, (size_t)q.N * (2 * restart + 1)));
@@ -410,6 +428,11 @@ extern "C" int mv_qn_solve(mv_ma* ma, const double* F, double* Y, double ksp_rto
       break;
     }
   }
-  if (info) { info[0] = (double)total; info[1] = rel; }
+  if (info) { info[0] = (double)total; info[1] = rel; info[2] = (double)restart; }
+  if (rel > ksp_rtol) {
+    // PETSc: KSP_DIVERGED_ITS -> SNES_DIVERGED_LINEAR_SOLVE -> firedrake ConvergenceError (monge_ampere.py:744-745)
+    set_error("gmres: not converged in %d iterations (relative residual %.3e > %.3e)", total, rel, ksp_rtol);
+    return MV_ERR_NOT_CONVERGED;
+  }
   return MV_OK;
 }

@@ -261,6 +261,7 @@ class MongeAmpereMover_Relaxation(MongeAmpereMover_Base):
         if phi_init is not None or H_init is not None:
             self.apply_initial_guess(phi_init, H_init)
         self.cg_iterations = []  # (l2 projection, poisson, hessian) inner iteration counts per step
+        self.trace = []          # (i, volume ratio, sigma/mu, residual, theta) per iteration of the last move()
 
     def _pseudotimestep(self):
         it = C.c_int(0)
@@ -299,19 +300,74 @@ class MongeAmpereMover_Relaxation(MongeAmpereMover_Base):
         self._advance()
         self.cg_iterations.append((self._n1, n2, n3))
 
+    # relaxation iterations per call into the device-side loop (trace lines are printed chunk by chunk)
+    move_chunk = 10
+
+    def _line(self, i, vmax, vmin, cov, residual):
+        self.trace.append((i, vmax / vmin, cov, residual, self.theta))   # what the line prints, unrounded (+ theta)
+        _print(f"{i:4d}"
+               f"   Volume ratio {vmax / vmin:5.2f}"
+               f"   Variation (σ/μ) {cov:8.2e}"
+               f"   Residual {residual:8.2e}")
+
+    def _move_fused(self):
+        """The loop of movement/monge_ampere.py:488-540 inside the library (``mv_ma_relax_move``) for a built-in
+        monitor: the host sees one call per ``move_chunk`` iterations and prints their trace lines."""
+        lib = L.load()
+        if hasattr(self, "tangling_checker"):
+            self.tangling_checker.check()      # mesh.coordinates == xi for the whole loop (monge_ampere.py:244)
+        n = max(1, int(self.move_chunk))
+        trace = (C.c_double * (6 * n))()
+        its = (C.c_int * (3 * n))()
+        info = (C.c_int * 3)()
+        res0 = C.c_double(0.0)
+        i0 = 0
+        while True:
+            try:
+                L.check(lib.mv_ma_relax_move(self._ma, self.pseudo_dt, i0, n, int(self.maxiter), float(self.rtol),
+                                             float(self.dtol), C.byref(res0), trace, its, info))
+            except L.MovementB200Error as e:
+                for f in (self.phi, self.H, self.phi_old, self.H_old, self.x, self.monitor, self._grad_phi, self.volume):
+                    f.written()
+                if e.status == L.MV_ERR_NOT_CONVERGED:
+                    self._convergence_error(exception=e)
+                raise
+            i, status, done = int(info[0]), int(info[1]), int(info[2])
+            for k in range(done):
+                t = trace[6 * k:6 * k + 6]
+                self.theta = t[0]
+                self._volume_stats = (t[2], t[3], t[4], t[5])
+                self._line(i0 + k, t[2], t[3], t[5], t[1])
+                if not (k == done - 1 and status != 3):
+                    self.cg_iterations.append((its[3 * k], its[3 * k + 1], its[3 * k + 2]))
+            if status != 3:
+                break
+            i0 = i + 1
+        for f in (self.phi, self.H, self.phi_old, self.H_old, self.x, self.monitor, self._grad_phi, self.volume, self._residual):
+            f.written()
+        if status == 0:
+            self._convergence_message(i + 1)
+        elif status == 1:        # as in the reference, the mesh stays in computational coordinates on failure
+            self._divergence_error(i + 1)
+        elif status == 2:
+            self._convergence_error(i + 1)
+        return i
+
     def move(self):
         """Run the relaxation to convergence; returns the iteration count ``i`` at the break
         (movement/monge_ampere.py:488-540)."""
         self._begin()
+        self.trace = []
+        if self._fused and self.maxiter > 0:
+            i = self._move_fused()
+            self.to_physical_coordinates()
+            return i
         i = 0
         for i in range(self.maxiter):
             residual = self._evaluate()
             if i == 0:
                 initial_norm = residual
-            _print(f"{i:4d}"
-                   f"   Volume ratio {self.volume_ratio:5.2f}"
-                   f"   Variation (σ/μ) {self.coefficient_of_variation:8.2e}"
-                   f"   Residual {residual:8.2e}")
+            self._line(i, self._volume_stats[0], self._volume_stats[1], self.coefficient_of_variation, residual)
             if residual < self.rtol:
                 self._convergence_message(i + 1)
                 break
@@ -334,10 +390,13 @@ class MongeAmpereMover_QuasiNewton(MongeAmpereMover_Base):
     the multiplicative fieldsplit preconditioner of solver_parameters.py:1-21.
     """
 
-    # PETSc defaults of the reference's option set (solver_parameters.py:1-21)
+    # the reference's option set (solver_parameters.py:1-21: ksp_max_it 200, ksp_gmres_restart 200, snes_rtol 1e-8)
+    # and PETSc's defaults for what it leaves unset (ksp_rtol 1e-5).  The restart length is honoured up to the
+    # device memory the Krylov basis needs (mv_qn_solve); pc_rtol / pc_max_it steer the inexact block solves that
+    # stand in for one gamg V-cycle / one ILU application.
     ksp_rtol = 1.0e-05
     ksp_max_it = 200
-    ksp_gmres_restart = 30
+    ksp_gmres_restart = 200
     snes_rtol = 1.0e-08
     pc_rtol = 1.0e-03
     pc_max_it = 400
@@ -435,10 +494,19 @@ class MongeAmpereMover_QuasiNewton(MongeAmpereMover_Base):
                 self.snes_iterations = it
                 self.to_physical_coordinates()
                 self._convergence_error(it)
-            info = (C.c_double * 2)()
-            self._call(lib.mv_qn_solve, L.ptr(self._F), L.ptr(self._Y), self.ksp_rtol, self.ksp_max_it,
-                       self.ksp_gmres_restart, self.pc_rtol, self.pc_max_it, info)
+            info = (C.c_double * 3)()
+            try:
+                L.check(lib.mv_qn_solve(self._ma, L.ptr(self._F), L.ptr(self._Y), self.ksp_rtol, self.ksp_max_it,
+                                        self.ksp_gmres_restart, self.pc_rtol, self.pc_max_it, info))
+            except L.MovementB200Error as e:
+                self.ksp_iterations.append(int(info[0]))
+                if e.status != L.MV_ERR_NOT_CONVERGED:
+                    raise
+                # DIVERGED_LINEAR_SOLVE: the reference reports the SNES iteration count (monge_ampere.py:744-745)
+                self.snes_iterations = it
+                self._convergence_error(it, exception=e)
             self.ksp_iterations.append(int(info[0]))
+            self.gmres_restart_used = int(info[2])
             self._call(lib.mv_qn_save)
             lam = self._l2_linesearch(f2)
             self._set_iterate(lam)

@@ -119,6 +119,9 @@ class SpringMover_Base(PrimeMover):
             boundary_conditions = [boundary_conditions]
         assert isinstance(boundary_conditions, Iterable)
         markers = self._all_boundary_segments
+        # the reference rebuilds K on every call (spring.py:201), so only THIS call's conditions replace rows;
+        # the forcing persists (spring.py:229-230)
+        self._mask[:] = 0
         for bc in boundary_conditions:
             if bc.function_space() != self.coord_space:
                 raise ValueError(f"Boundary conditions must have {type(self).__name__}.coord_space"

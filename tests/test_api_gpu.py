@@ -498,3 +498,50 @@ def test_qn_maxiter_message():
     mover = mv.MongeAmpereMover(mv.UnitSquareMesh(4, 4), mv.ring_test_monitor(2), method="quasi_newton", maxiter=1)
     with pytest.raises(mv.ConvergenceError, match=r"^Solver failed to converge in 1 iteration\.$"):
         mover.move()
+
+
+def test_qn_linear_solve_failure_is_a_convergence_error():
+    """ksp_max_it = 1: GMRES cannot reach ksp_rtol -> KSP_DIVERGED_ITS -> SNES_DIVERGED_LINEAR_SOLVE, which the reference
+    turns into ConvergenceError with the SNES iteration count (movement/monge_ampere.py:744-745); here zero Newton
+    iterations were completed, so the message has no count."""
+    mv = _mv()
+    mover = mv.MongeAmpereMover(mv.UnitSquareMesh(8, 8), mv.ring_test_monitor(2), method="quasi_newton")
+    mover.ksp_max_it = 1
+    mover.ksp_rtol = 1e-12
+    with pytest.raises(mv.ConvergenceError, match=r"^Solver failed to converge\.$"):
+        mover.move()
+    assert mover.ksp_iterations == [1] and mover.snes_iterations == 0
+    # the reference's restart length (solver_parameters.py:13) is the default and fits at this size
+    mover2 = mv.MongeAmpereMover(mv.UnitSquareMesh(8, 8), mv.ring_test_monitor(2), method="quasi_newton", rtol=1e-3)
+    assert mover2.ksp_gmres_restart == 200
+    mover2.move()
+    assert mover2.gmres_restart_used == 200
+
+
+def test_spring_dirichlet_rows_follow_the_current_call():
+    """spring.py:183-235 rebuilds K on every call: only the boundary conditions of THIS call replace rows, while the
+    forcing written by earlier calls persists (spring.py:229-230).  Two consecutive moves with different tag sets
+    against the oracle's dense row-replaced system."""
+    mv = _mv()
+    n = 6
+    mesh = mv.UnitSquareMesh(n, n)
+    mover = mv.SpringMover(mesh, 1.0)
+    fA = mv.Function(mover.coord_space).interpolate([0.0, 0.01])
+    bcA = [mv.DirichletBC(mover.coord_space, fA, 4), mv.DirichletBC(mover.coord_space, 0, [1, 2, 3])]
+    bcB = [mv.DirichletBC(mover.coord_space, 0, [1, 2])]
+    omesh = mo.unit_square_mesh(n)
+    ref = mo.OracleSpringMover(omesh, 1.0)
+    nodesA4 = np.unique(omesh.bfacets[omesh.btags == 4])
+    nodesA0 = np.unique(omesh.bfacets[np.isin(omesh.btags, [1, 2, 3])])
+    # call 1: sets A (later BCs override earlier ones at shared vertices)
+    mover.move(0.0, boundary_conditions=bcA)
+    ref.move(np.concatenate([nodesA4, nodesA0]),
+             np.concatenate([np.tile([0.0, 0.01], (len(nodesA4), 1)), np.zeros((len(nodesA0), 2))]))
+    assert np.abs(mover.mesh.coordinates.dat.data_ro - ref.x).max() < 1e-10
+    # call 2: set B pins only x = 0 and x = 1; the top vertices keep their forcing but are free rows now
+    nodesB = np.unique(omesh.bfacets[np.isin(omesh.btags, [1, 2])])
+    mover.move(1.0, boundary_conditions=bcB)
+    ref.move(nodesB, np.zeros((len(nodesB), 2)))
+    assert np.abs(mover.mesh.coordinates.dat.data_ro - ref.x).max() < 1e-10
+    free_top = np.setdiff1d(nodesA4, nodesB)
+    assert len(free_top) and np.abs(mover.displacement.reshape(-1, 2)[free_top]).max() > 1e-6

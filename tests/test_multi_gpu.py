@@ -33,3 +33,15 @@ def test_two_rank_multigrid_poisson(dim, n, split_min):
                           os.path.join(ROOT, "tests", "dist", "run_amg_2rank.py"), str(dim), str(n)],
                          capture_output=True, text=True, timeout=600, env=dict(os.environ, MV_AMG_SPLIT_MIN=split_min))
     assert out.returncode == 0 and "DIST-AMG-OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
+
+
+def test_two_rank_laplacian_spring_quasi_newton_match_oracle():
+    """LaplacianSmoother, SpringMover ('+' cell by global cell number) and the quasi-Newton mover under a 2-way
+    partition against the global-mesh oracle: coordinates within 1e-10, Newton iteration count +-1."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29521",
+                          os.path.join(ROOT, "tests", "dist", "run_movers_2rank.py")],
+                         capture_output=True, text=True, timeout=900)
+    assert out.returncode == 0 and "DIST-MOVERS-OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
