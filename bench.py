@@ -59,6 +59,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--e2e-detail", action="store_true", help="one library call per iteration in the e2e leg, wall time of each reported")
     ap.add_argument("--write-parity", action="store_true", help="N = 1: store the parity record of this n")
     ap.add_argument("--mass-solver", default="chebyshev", choices=["chebyshev", "pcg"],
                     help="solver of the consistent-mass systems (A1, A8): fused Chebyshev (default) or Jacobi-PCG")
@@ -425,6 +426,8 @@ def run_relaxation(args, dim):
         t0 = time.perf_counter()
         m2 = make_mover()
         torch.cuda.synchronize(); t1 = time.perf_counter()
+        if args.e2e_detail:
+            m2.move_chunk = 1
         move_k(m2, args.steps)
         torch.cuda.synchronize(); t2 = time.perf_counter()
         out = out_host[: m2._dm.Vown]
@@ -439,6 +442,7 @@ def run_relaxation(args, dim):
                "breakdown_s": {"Mesh(host)+MongeAmpereMover(): h2d, ingest, assembly": t1 - t0,
                                "move() (incl. multigrid set-up)": t2 - t1, "d2h": t3 - t2},
                "outside_the_timer_s": prep,
+               "move_chunks(last_iteration,seconds_since_loop_start)": [(int(i), float(t)) for i, t in getattr(m2, "chunk_wall", [])],
                "what": "Mesh(pinned host arrays) -> MongeAmpereMover(mesh, monitor, method='relaxation', maxiter=K+1, "
                        "raise_convergence_errors=False) -> .move() -> D2H of mover.x; K full iterations + the evaluation half "
                        "of iteration K+1 are inside the timer and K is counted"}

@@ -124,6 +124,13 @@ int mv_true_residual_get(double* max_rel16, double* last_rel16, int64_t* count16
 int mv_mesh_create(int dim, int64_t V, int64_t C, const double* coords, const int32_t* cells,
                    int64_t F, const int32_t* bfacet_verts, const int32_t* bfacet_tags,
                    int64_t n_owned_vertices, int64_t n_owned_cells, mv_mesh** out);
+/* The same for a mesh whose coordinate field is DG1 (coord_dg = 1): Firedrake's layout of PERIODIC meshes
+ * (movement/mover.py:70-75, monge_ampere.py:236-239).  `cells` is the periodic P1 cell-node map over V vertices;
+ * `coords` has C*(dim+1) rows, row c*(dim+1)+j = corner j of cell c.  No boundary facets, not partitioned.
+ * Every coordinate-field argument of the other entry points then has C*(dim+1) rows.                            */
+int mv_mesh_create_ex(int dim, int64_t V, int64_t C, const double* coords, const int32_t* cells, int64_t F,
+                      const int32_t* bfacet_verts, const int32_t* bfacet_tags, int64_t n_owned_vertices,
+                      int64_t n_owned_cells, int coord_dg, mv_mesh** out);
 void mv_mesh_destroy(mv_mesh* m);
 /* info[0..11] = V, C, F, nnz, sell_len, nslices, max_row, dim, n_owned_vertices, n_owned_cells,
  * slice schedule of the gather kernels (0 not built yet, 1 identity, 2 lattice tiles), its length */

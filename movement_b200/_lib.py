@@ -38,6 +38,7 @@ SIGNATURES = {
     "mv_true_residual_enable": (_i, [_i]),
     "mv_true_residual_get": (_i, [_pd, _pd, _pi64]),
     "mv_mesh_create": (_i, [_i, _i64, _i64, _vp, _vp, _i64, _vp, _vp, _i64, _i64, C.POINTER(_vp)]),
+    "mv_mesh_create_ex": (_i, [_i, _i64, _i64, _vp, _vp, _i64, _vp, _vp, _i64, _i64, _i, C.POINTER(_vp)]),
     "mv_mesh_destroy": (None, [_vp]),
     "mv_mesh_info": (_i, [_vp, _pi64]),
     "mv_mesh_scalars": (_i, [_vp, _pd]),

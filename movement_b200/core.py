@@ -30,11 +30,14 @@ class DeviceMesh:
     be numpy arrays (host) or CUDA tensors.
     """
 
-    def __init__(self, coords, cells, bfacets=None, btags=None, n_owned_vertices=None, n_owned_cells=None):
+    def __init__(self, coords, cells, bfacets=None, btags=None, n_owned_vertices=None, n_owned_cells=None, periodic=False,
+                 num_vertices=None):
         _require_cuda()
         lib = L.load()
         self.dim = int(coords.shape[1])
-        self.V = int(coords.shape[0])
+        self.periodic = bool(periodic)
+        # periodic: coords is the DG1 coordinate field [C*(d+1), d], cells the periodic P1 map over num_vertices vertices
+        self.V = int(num_vertices) if periodic else int(coords.shape[0])
         self.C = int(cells.shape[0])
         self.F = 0 if bfacets is None else int(bfacets.shape[0])
         self.Vown = self.V if n_owned_vertices is None else int(n_owned_vertices)
@@ -47,8 +50,8 @@ class DeviceMesh:
         bfacets = self._prep(bfacets, np.int32, torch.int32)
         btags = self._prep(btags, np.int32, torch.int32)
         h = C.c_void_p()
-        L.check(lib.mv_mesh_create(self.dim, self.V, self.C, L.ptr(coords), L.ptr(cells), self.F, L.ptr(bfacets),
-                                   L.ptr(btags), self.Vown, self.Cown, C.byref(h)))
+        L.check(lib.mv_mesh_create_ex(self.dim, self.V, self.C, L.ptr(coords), L.ptr(cells), self.F, L.ptr(bfacets),
+                                      L.ptr(btags), self.Vown, self.Cown, 1 if self.periodic else 0, C.byref(h)))
         self.handle = h
         info = (C.c_int64 * 16)()
         L.check(lib.mv_mesh_info(h, info))
@@ -303,8 +306,10 @@ class MAState:
 def device_mesh_from(mesh):
     """Ingest a :class:`movement_b200.mesh.Mesh` (one-off)."""
     part = mesh.part
-    dm = DeviceMesh(mesh.coordinates.tensor, mesh.cells, mesh.bfacets, mesh.btags,
-                    n_owned_vertices=mesh.n_owned_vertices, n_owned_cells=mesh.n_owned_cells)
+    dm = DeviceMesh(mesh.coordinates.tensor, mesh.cells, mesh.bfacets if len(mesh.bfacets) else None,
+                    mesh.btags if len(mesh.btags) else None,
+                    n_owned_vertices=mesh.n_owned_vertices, n_owned_cells=mesh.n_owned_cells,
+                    periodic=getattr(mesh, "periodic", False), num_vertices=mesh.num_vertices())
     if part is not None:
         lib = L.load()
         nn = len(part.neighbours)

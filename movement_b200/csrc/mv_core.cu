@@ -128,14 +128,14 @@ __device__ __forceinline__ double signed_detJ<3>(const double (&xc)[4][3]) {
 
 template <int D, bool INIT>
 __global__ void __launch_bounds__(MV_BLOCK)
-k_tangle(const double* __restrict__ x, const int* __restrict__ cells, int64_t C, int64_t Ccount,
+k_tangle(const double* __restrict__ x, const int* __restrict__ cells, int dg, int64_t C, int64_t Ccount,
          double* __restrict__ detJ0, double* __restrict__ ratio, unsigned long long* __restrict__ count) {
   unsigned local = 0;
   for (int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; c < C; c += (int64_t)gridDim.x * blockDim.x) {
     int cv[D + 1];
     double xc[D + 1][D];
     load_cell<D>(cells, c, cv);
-    load_cell_coords<D>(x, cv, xc);
+    load_cell_coords<D>(x, cv, xc, dg, c);
     const double det = signed_detJ<D>(xc);
     if (INIT) {
       detJ0[c] = det;
@@ -161,7 +161,7 @@ k_tangle(const double* __restrict__ x, const int* __restrict__ cells, int64_t C,
 // ---------------------------------------------------------------------------------
 template <int D>
 __global__ void __launch_bounds__(MV_BLOCK)
-k_volumes(const double* __restrict__ x, const int* __restrict__ cells, int64_t C, const double* __restrict__ mon,
+k_volumes(const double* __restrict__ x, const int* __restrict__ cells, int dg, int64_t C, const double* __restrict__ mon,
           const double* __restrict__ vol0, double* __restrict__ volume, double* __restrict__ partials,
           unsigned* __restrict__ counter, double* __restrict__ out /* [0]=sum [1]=max [2]=min */) {
   double s[1] = {0.0};
@@ -171,7 +171,7 @@ k_volumes(const double* __restrict__ x, const int* __restrict__ cells, int64_t C
     double xc[D + 1][D];
     CellGeom<D> g;
     load_cell<D>(cells, c, cv);
-    load_cell_coords<D>(x, cv, xc);
+    load_cell_coords<D>(x, cv, xc, dg, c);
     cell_geom(xc, g);
     double v = g.vol;
     if (mon) {
@@ -224,10 +224,8 @@ int volume_stats_device(mv_mesh* m, const double* x, const double* mon, const do
   const int64_t C = m->Cown;
   MV_L k_init_volstats<<<1, 1, 0, g_stream>>>(dout);
   const int grid = grid_for(C);
-  if (m->dim == 2)
-    MV_L k_volumes<2><<<grid, MV_BLOCK, 0, g_stream>>>(x, m->cells, C, mon, vol0, volume, m->red.partials, m->red.counter, dout);
-  else
-    MV_L k_volumes<3><<<grid, MV_BLOCK, 0, g_stream>>>(x, m->cells, C, mon, vol0, volume, m->red.partials, m->red.counter, dout);
+  MV_DISPATCH_DIM(m->dim, MV_L k_volumes<DIM><<<grid, MV_BLOCK, 0, g_stream>>>(x, m->cells, m->dg, C, mon, vol0, volume, m->red.partials,
+                                                                          m->red.counter, dout));
   MV_KERNEL_CHECK();
   if (comm_active()) MV_CHECK(allreduce_volstats_dev(dout));
   MV_L k_volume_var<<<grid, MV_BLOCK, 0, g_stream>>>(volume, C, 1.0 / (double)global_cells, m->red.partials, m->red.counter, dout);
@@ -297,15 +295,11 @@ extern "C" int mv_sync(void) {
 extern "C" int mv_tangle_init(mv_mesh* m, const double* coords, double* detJ0) {
   if (!m || !coords || !detJ0) return MV_ERR_BADARG;
   Staged sx, sd;
-  MV_CHECK(sx.in(coords, m->V * m->dim * sizeof(double)));
+  MV_CHECK(sx.in(coords, m->Vc * m->dim * sizeof(double)));
   MV_CHECK(sd.out_begin(detJ0, m->C * sizeof(double)));
   const int grid = grid_for(m->C);
-  if (m->dim == 1)
-    MV_L k_tangle<1, true><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, m->C, m->C, sd.as<double>(), nullptr, nullptr);
-  else if (m->dim == 2)
-    MV_L k_tangle<2, true><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, m->C, m->C, sd.as<double>(), nullptr, nullptr);
-  else
-    MV_L k_tangle<3, true><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, m->C, m->C, sd.as<double>(), nullptr, nullptr);
+  MV_DISPATCH_DIM(m->dim, MV_L k_tangle<DIM, true><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, m->dg, m->C, m->C, sd.as<double>(),
+                                                                              nullptr, nullptr));
   MV_KERNEL_CHECK();
   return sd.out_end(detJ0, m->C * sizeof(double));
 }
@@ -313,7 +307,7 @@ extern "C" int mv_tangle_init(mv_mesh* m, const double* coords, double* detJ0) {
 extern "C" int mv_tangle_check(mv_mesh* m, const double* coords, const double* detJ0, double* ratio, int64_t* count) {
   if (!m || !coords || !detJ0 || !count) return MV_ERR_BADARG;
   Staged sx, sd, sr;
-  MV_CHECK(sx.in(coords, m->V * m->dim * sizeof(double)));
+  MV_CHECK(sx.in(coords, m->Vc * m->dim * sizeof(double)));
   MV_CHECK(sd.in(detJ0, m->C * sizeof(double)));
   MV_CHECK(sr.out_begin(ratio, m->C * sizeof(double)));
   unsigned long long* d_count = (unsigned long long*)(m->red.counter + 2);  // 8-byte aligned slot
@@ -321,12 +315,8 @@ extern "C" int mv_tangle_check(mv_mesh* m, const double* coords, const double* d
   // the ratio field is written for all local cells, only owned cells are counted
   const int64_t C = ratio ? m->C : m->Cown;
   const int grid = grid_for(C);
-  if (m->dim == 1)
-    MV_L k_tangle<1, false><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, C, m->Cown, sd.as<double>(), sr.as<double>(), d_count);
-  else if (m->dim == 2)
-    MV_L k_tangle<2, false><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, C, m->Cown, sd.as<double>(), sr.as<double>(), d_count);
-  else
-    MV_L k_tangle<3, false><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, C, m->Cown, sd.as<double>(), sr.as<double>(), d_count);
+  MV_DISPATCH_DIM(m->dim, MV_L k_tangle<DIM, false><<<grid, MV_BLOCK, 0, g_stream>>>(sx.as<double>(), m->cells, m->dg, C, m->Cown, sd.as<double>(),
+                                                                               sr.as<double>(), d_count));
   MV_KERNEL_CHECK();
   unsigned long long h = 0;
   MV_CUDA(cudaMemcpyAsync(&h, d_count, sizeof(h), cudaMemcpyDeviceToHost, g_stream));
@@ -337,12 +327,8 @@ extern "C" int mv_tangle_check(mv_mesh* m, const double* coords, const double* d
 
 extern "C" int mv_cell_volumes(mv_mesh* m, const double* coords, double* volume, double* stats) {
   if (!m || !coords || !volume) return MV_ERR_BADARG;
-  if (m->dim < 2) {
-    set_error("mv_cell_volumes: not available on 1D meshes (geometry for the tangling check only)");
-    return MV_ERR_UNSUPPORTED;
-  }
   Staged sx, sv;
-  MV_CHECK(sx.in(coords, m->V * m->dim * sizeof(double)));
+  MV_CHECK(sx.in(coords, m->Vc * m->dim * sizeof(double)));
   MV_CHECK(sv.out_begin(volume, m->C * sizeof(double)));
   double* dout = nullptr;
   MV_CUDA(cudaMallocAsync((void**)&dout, 4 * sizeof(double), g_stream));

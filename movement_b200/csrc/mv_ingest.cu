@@ -173,20 +173,20 @@ __global__ void k_fill_cols(const int* __restrict__ cells, const int* __restrict
 
 // ------------------------------------------------------------------ values
 template <int D>
-__global__ void k_cell_volume(const double* __restrict__ x, const int* __restrict__ cells, int64_t C, double* __restrict__ vol) {
+__global__ void k_cell_volume(const double* __restrict__ x, const int* __restrict__ cells, int dg, int64_t C, double* __restrict__ vol) {
   for (int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; c < C; c += (int64_t)gridDim.x * blockDim.x) {
     int cv[D + 1];
     double xc[D + 1][D];
     CellGeom<D> g;
     load_cell<D>(cells, c, cv);
-    load_cell_coords<D>(x, cv, xc);
+    load_cell_coords<D>(x, cv, xc, dg, c);
     cell_geom(xc, g);
     vol[c] = g.vol;
   }
 }
 
 template <int D>
-__global__ void k_assemble_MK(const double* __restrict__ x, const int* __restrict__ cells, const int* __restrict__ v2c_ptr,
+__global__ void k_assemble_MK(const double* __restrict__ x, const int* __restrict__ cells, int dg, const int* __restrict__ v2c_ptr,
                               const int* __restrict__ v2c, int64_t nrows, const int64_t* __restrict__ slice_ptr,
                               const int* __restrict__ cols, double* __restrict__ Mval, double* __restrict__ Kval,
                               double* __restrict__ ml, double* __restrict__ dinvM, double* __restrict__ dinvK) {
@@ -210,7 +210,7 @@ __global__ void k_assemble_MK(const double* __restrict__ x, const int* __restric
       double xc[D + 1][D];
       CellGeom<D> g;
       load_cell<D>(cells, c, cv);
-      load_cell_coords<D>(x, cv, xc);
+      load_cell_coords<D>(x, cv, xc, dg, c);
       cell_geom(xc, g);
       mlv += g.vol / (D + 1);
       double gl[D];
@@ -284,7 +284,11 @@ __global__ void k_facet_geometry(const double* __restrict__ x, const int* __rest
     }
     bf_cell[f] = cell;
     double n[D], area;
-    if (D == 2) {
+    if constexpr (D == 1) {
+      // a boundary "facet" of an interval mesh is a point: measure 1, normal pointing away from the cell
+      area = 1.0;
+      n[0] = 1.0;
+    } else if constexpr (D == 2) {
       const double ex = x[(size_t)fv[1] * D] - x[(size_t)fv[0] * D], ey = x[(size_t)fv[1] * D + 1] - x[(size_t)fv[0] * D + 1];
       area = sqrt(ex * ex + ey * ey);
       n[0] = ey / area;
@@ -363,9 +367,9 @@ static int ingest_impl(mv_mesh* m) {
   MV_CHECK(dev_alloc(&m->vol, C));
   MV_CUDA(cudaMemsetAsync(m->Mval, 0, p.len * sizeof(double), g_stream));
   MV_CUDA(cudaMemsetAsync(m->Kval, 0, p.len * sizeof(double), g_stream));
-  if (C > 0) MV_L k_cell_volume<D><<<grid_for(C), MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, C, m->vol);
+  if (C > 0) MV_L k_cell_volume<D><<<grid_for(C), MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->dg, C, m->vol);
   MV_KERNEL_CHECK();
-  MV_L k_assemble_MK<D><<<grid_for(Vown), MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, Vown, p.slice_ptr, p.cols,
+  MV_L k_assemble_MK<D><<<grid_for(Vown), MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->dg, m->v2c_ptr, m->v2c, Vown, p.slice_ptr, p.cols,
                                                             m->Mval, m->Kval, m->ml, m->dinvM, m->dinvK);
   MV_KERNEL_CHECK();
   // scalars (fixed-order sums)
@@ -418,11 +422,27 @@ static int ingest_impl(mv_mesh* m) {
 
 using namespace mv;
 
+// P1 vertex -> its coordinate node in the last cell that contains it (periodic meshes)
+__global__ void k_dg_rep(int64_t nnodes, const int* __restrict__ cells_flat, int* __restrict__ rep) {
+  for (int64_t n = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; n < nnodes; n += (int64_t)gridDim.x * blockDim.x)
+    atomicMax(&rep[cells_flat[n]], (int)n);
+}
+
 extern "C" int mv_mesh_create(int dim, int64_t V, int64_t C, const double* coords, const int32_t* cells, int64_t F,
                               const int32_t* bfacet_verts, const int32_t* bfacet_tags, int64_t n_owned_vertices,
                               int64_t n_owned_cells, mv_mesh** out) {
+  return mv_mesh_create_ex(dim, V, C, coords, cells, F, bfacet_verts, bfacet_tags, n_owned_vertices, n_owned_cells, 0, out);
+}
+
+extern "C" int mv_mesh_create_ex(int dim, int64_t V, int64_t C, const double* coords, const int32_t* cells, int64_t F,
+                                 const int32_t* bfacet_verts, const int32_t* bfacet_tags, int64_t n_owned_vertices,
+                                 int64_t n_owned_cells, int coord_dg, mv_mesh** out) {
   if (!out) return MV_ERR_BADARG;
   *out = nullptr;
+  if (coord_dg && (F != 0 || n_owned_vertices != V || n_owned_cells != C)) {
+    set_error("mv_mesh_create_ex: a DG coordinate field (periodic mesh) has no boundary facets and is not partitioned");
+    return MV_ERR_UNSUPPORTED;
+  }
   if (dim < 1 || dim > 3) {
     set_error("mv_mesh_create: dim must be 1, 2 or 3 (got %d)", dim);
     return MV_ERR_UNSUPPORTED;
@@ -448,13 +468,15 @@ extern "C" int mv_mesh_create(int dim, int64_t V, int64_t C, const double* coord
   }
   mv_mesh* m = new mv_mesh();
   m->dim = dim; m->V = V; m->C = C; m->F = F; m->Vown = n_owned_vertices; m->Cown = n_owned_cells;
+  m->dg = coord_dg ? 1 : 0;
+  m->Vc = coord_dg ? C * (int64_t)(dim + 1) : V;
   int st = MV_OK;
   auto fail = [&](int s) { mv_mesh_destroy(m); return s; };
-  if ((st = dev_alloc(&m->xi, V * dim)) != MV_OK) return fail(st);
+  if ((st = dev_alloc(&m->xi, m->Vc * dim)) != MV_OK) return fail(st);
   if ((st = dev_alloc(&m->cells, C * (dim + 1))) != MV_OK) return fail(st);
   if ((st = dev_alloc(&m->bf_verts, F * dim)) != MV_OK) return fail(st);
   if ((st = dev_alloc(&m->bf_tags, F)) != MV_OK) return fail(st);
-  cudaError_t e = cudaMemcpyAsync(m->xi, coords, V * dim * sizeof(double), cudaMemcpyDefault, g_stream);
+  cudaError_t e = cudaMemcpyAsync(m->xi, coords, m->Vc * dim * sizeof(double), cudaMemcpyDefault, g_stream);
   if (e == cudaSuccess && C) e = cudaMemcpyAsync(m->cells, cells, C * (dim + 1) * sizeof(int), cudaMemcpyDefault, g_stream);
   if (e == cudaSuccess && F) e = cudaMemcpyAsync(m->bf_verts, bfacet_verts, F * dim * sizeof(int), cudaMemcpyDefault, g_stream);
   if (e == cudaSuccess && F) e = cudaMemcpyAsync(m->bf_tags, bfacet_tags, F * sizeof(int), cudaMemcpyDefault, g_stream);
@@ -468,16 +490,12 @@ extern "C" int mv_mesh_create(int dim, int64_t V, int64_t C, const double* coord
     if (e == cudaSuccess) e = cudaStreamSynchronize(g_stream);
     if (e != cudaSuccess) { set_error("mv_mesh_create: %s", cudaGetErrorString(e)); return fail(MV_ERR_CUDA); }
   }
-  if (dim == 1) {
-    // interval meshes: geometry only, for the tangling check (movement/tangling.py on UnitIntervalMesh,
-    // test/test_tangling.py:14-37); the movers reject 1D meshes above the ABI, no operators are built
-    if ((st = dev_alloc(&m->red.partials, (size_t)MV_MAX_BLOCKS * MV_RED_SLOTS)) != MV_OK) return fail(st);
-    if ((st = dev_alloc(&m->red.counter, 4)) != MV_OK) return fail(st);
-    if (cudaMemsetAsync(m->red.counter, 0, 4 * sizeof(unsigned), g_stream) != cudaSuccess) return fail(MV_ERR_CUDA);
-    *out = m;
-    return MV_OK;
+  if (m->dg) {
+    if ((st = dev_alloc(&m->rep, V)) != MV_OK) return fail(st);
+    if (cudaMemsetAsync(m->rep, 0, V * sizeof(int), g_stream) != cudaSuccess) return fail(MV_ERR_CUDA);
+    MV_L k_dg_rep<<<grid_for(m->Vc), MV_BLOCK, 0, g_stream>>>(m->Vc, m->cells, m->rep);
   }
-  st = dim == 2 ? ingest_impl<2>(m) : ingest_impl<3>(m);
+  st = dim == 1 ? ingest_impl<1>(m) : (dim == 2 ? ingest_impl<2>(m) : ingest_impl<3>(m));
   if (st != MV_OK) return fail(st);
   *out = m;
   return MV_OK;
@@ -491,7 +509,7 @@ extern "C" void mv_mesh_destroy(mv_mesh* m) {
   dev_free(m->v2f_ptr); dev_free(m->v2f);
   dev_free(m->pat.slice_ptr); dev_free(m->pat.cols); dev_free(m->pat.row_nnz); dev_free(m->pat.sched);
   dev_free(m->Mval); dev_free(m->Kval); dev_free(m->MKval); dev_free(m->ml); dev_free(m->vol);
-  dev_free(m->dinvM); dev_free(m->dinvK); dev_free(m->dinvMK); dev_free(m->edge_opp); dev_free(m->cell_gid);
+  dev_free(m->dinvM); dev_free(m->dinvK); dev_free(m->dinvMK); dev_free(m->edge_opp); dev_free(m->cell_gid); dev_free(m->rep);
   dev_free(m->red.partials); dev_free(m->red.counter);
   dev_free(m->pcg.r); dev_free(m->pcg.p); dev_free(m->pcg.q); dev_free(m->pcg.xs); dev_free(m->pcg.scal); dev_free(m->pcg.flags);
   if (m->pcg.h_flags) cudaFreeHost(m->pcg.h_flags);

@@ -210,7 +210,13 @@ struct Amg {
 struct mv_mesh {
   int dim = 0;
   int64_t V = 0, C = 0, F = 0, Vown = 0, Cown = 0;
-  double* xi = nullptr;     // [V*dim] coordinates at ingest (computational mesh)
+  // periodic meshes (movement/mover.py:70-75, monge_ampere.py:236-239): `cells` is the periodic P1 map, the coordinate
+  // field is DG1 -- node c*(dim+1)+j belongs to corner j of cell c, Vc = C*(dim+1) coordinate nodes (dg = 1);
+  // rep[v] = the coordinate node of P1 vertex v in the last cell that contains it
+  int dg = 0;
+  int64_t Vc = 0;
+  int* rep = nullptr;       // [V] (dg only)
+  double* xi = nullptr;     // [Vc*dim] coordinates at ingest (computational mesh)
   int* cells = nullptr;     // [C*(dim+1)]
   int* v2c_ptr = nullptr;   // [Vown+1]
   int* v2c = nullptr;       // entries cell*(dim+1)+loc, ascending per vertex
@@ -344,6 +350,13 @@ int bcast_bytes(void* buf, size_t bytes, int root);
 int neighbor_exchange_bytes(int nn, const int* ranks, const void* const* sbuf, const size_t* sbytes, void* const* rbuf,
                             const size_t* rbytes);
 int grid_for(int64_t nthreads_needed, int blocks_per_sm = 8);
+// run a statement with DIM = the mesh dimension as a compile-time constant
+#define MV_DISPATCH_DIM(dim, ...)                                   \
+  do {                                                              \
+    if ((dim) == 1) { constexpr int DIM = 1; __VA_ARGS__; }         \
+    else if ((dim) == 2) { constexpr int DIM = 2; __VA_ARGS__; }    \
+    else { constexpr int DIM = 3; __VA_ARGS__; }                    \
+  } while (0)
 int exclusive_scan_i64(const int64_t* in, int64_t* out, int64_t n);
 // multigrid (mv_amg.cu / mv_amg_cycle.cu)
 int amg_get(mv_mesh* m, int op, const uint16_t* mask, int ncomp, int singular, Amg** out);  // *out = nullptr -> use Jacobi
@@ -432,13 +445,24 @@ struct CellGeom {
   double g[D + 1][D];
 };
 
+// coordinates of the corners of cell c: through the P1 map (cv), or, on a periodic mesh (dg), the cell's own DG nodes
 template <int D>
 __device__ __forceinline__ void load_cell_coords(const double* __restrict__ x, const int* cv,
-                                                 double (&xc)[D + 1][D]) {
+                                                 double (&xc)[D + 1][D], int dg = 0, int64_t c = 0) {
 #pragma unroll
-  for (int j = 0; j <= D; ++j)
+  for (int j = 0; j <= D; ++j) {
+    const size_t node = dg ? (size_t)c * (D + 1) + j : (size_t)cv[j];
 #pragma unroll
-    for (int a = 0; a < D; ++a) xc[j][a] = __ldg(&x[(size_t)cv[j] * D + a]);
+    for (int a = 0; a < D; ++a) xc[j][a] = __ldg(&x[node * D + a]);
+  }
+}
+
+__device__ __forceinline__ void cell_geom(const double (&xc)[2][1], CellGeom<1>& o) {
+  const double det = xc[1][0] - xc[0][0];
+  o.det = det;
+  o.vol = fabs(det);
+  o.g[1][0] = 1.0 / det;
+  o.g[0][0] = -o.g[1][0];
 }
 
 __device__ __forceinline__ void cell_geom(const double (&xc)[3][2], CellGeom<2>& o) {

@@ -40,7 +40,14 @@ __constant__ double c_q3_w[14] = {0.11268792571801585080, 0.11268792571801585080
                                   0.04254602077708146644, 0.04254602077708146644, 0.04254602077708146644, 0.04254602077708146644,
                                   0.04254602077708146644, 0.04254602077708146644};
 
+// 1D: two-point Gauss rule, exact to degree 3 = d+2
+__constant__ double c_q1_lam[2][2] = {{0.78867513459481288225, 0.21132486540518711775}, {0.21132486540518711775, 0.78867513459481288225}};
 template <int D> struct Quad;
+template <> struct Quad<1> {
+  static constexpr int Q = 2;
+  __device__ static double lam(int q, int j) { return c_q1_lam[q][j]; }
+  __device__ static double w(int q) { return 0.5; }
+};
 template <> struct Quad<2> {
   static constexpr int Q = 6;
   __device__ static double lam(int q, int j) { return c_q2_lam[q][j]; }
@@ -52,6 +59,7 @@ template <> struct Quad<3> {
   __device__ static double w(int q) { return c_q3_w[q]; }
 };
 
+__device__ __forceinline__ double det_I_plus(const double (&h)[1][1]) { return 1.0 + h[0][0]; }
 __device__ __forceinline__ double det_I_plus(const double (&h)[2][2]) {
   return (1.0 + h[0][0]) * (1.0 + h[1][1]) - h[0][1] * h[1][0];
 }
@@ -65,7 +73,7 @@ __device__ __forceinline__ double det_I_plus(const double (&h)[3][3]) {
 // b_a,i = sum_{K ni i} vol(K)/(d+1) * (grad phi|_K)_a       (monge_ampere.py:328)
 template <int D>
 __global__ void __launch_bounds__(MV_BLOCK)
-k_l2_rhs(const double* __restrict__ xi, const int* __restrict__ cells, const int* __restrict__ v2c_ptr,
+k_l2_rhs(const double* __restrict__ xi, const int* __restrict__ cells, int dg, const int* __restrict__ v2c_ptr,
          const int* __restrict__ v2c, int64_t nrows, const double* __restrict__ phi, double* __restrict__ b) {
   for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < nrows; v += (int64_t)gridDim.x * blockDim.x) {
     double acc[D];
@@ -78,7 +86,7 @@ k_l2_rhs(const double* __restrict__ xi, const int* __restrict__ cells, const int
       double xc[D + 1][D];
       CellGeom<D> g;
       load_cell<D>(cells, c, cv);
-      load_cell_coords<D>(xi, cv, xc);
+      load_cell_coords<D>(xi, cv, xc, dg, c);
       cell_geom(xc, g);
       const double wgt = g.vol / (D + 1);
 #pragma unroll
@@ -99,7 +107,7 @@ k_l2_rhs(const double* __restrict__ xi, const int* __restrict__ cells, const int
 // t = g - (g.n) n with g = grad phi on the cell behind F      (monge_ampere.py:477-480)
 template <int D>
 __global__ void __launch_bounds__(MV_BLOCK)
-k_hess_rhs(const double* __restrict__ xi, const int* __restrict__ cells, const int* __restrict__ v2c_ptr,
+k_hess_rhs(const double* __restrict__ xi, const int* __restrict__ cells, int dg, const int* __restrict__ v2c_ptr,
            const int* __restrict__ v2c, const int* __restrict__ v2f_ptr, const int* __restrict__ v2f,
            const int* __restrict__ bf_cell, const double* __restrict__ bf_normal, const double* __restrict__ bf_area,
            int64_t nrows, const double* __restrict__ phi, double* __restrict__ out) {
@@ -118,7 +126,7 @@ k_hess_rhs(const double* __restrict__ xi, const int* __restrict__ cells, const i
       double xc[D + 1][D];
       CellGeom<D> g;
       load_cell<D>(cells, c, cv);
-      load_cell_coords<D>(xi, cv, xc);
+      load_cell_coords<D>(xi, cv, xc, dg, c);
       cell_geom(xc, g);
       double gk[D], gl[D];
 #pragma unroll
@@ -175,7 +183,7 @@ k_hess_rhs(const double* __restrict__ xi, const int* __restrict__ cells, const i
 // replaces: monge_ampere.py:406 (theta_form), :409 (_residual_l2_form)
 template <int D>
 __global__ void __launch_bounds__(MV_BLOCK)
-k_assemble_a(const double* __restrict__ xi, const int* __restrict__ cells, const int* __restrict__ v2c_ptr,
+k_assemble_a(const double* __restrict__ xi, const int* __restrict__ cells, int dg, const int* __restrict__ v2c_ptr,
              const int* __restrict__ v2c, int64_t nrows, const double* __restrict__ mon, const double* __restrict__ H,
              double* __restrict__ a_out, double* __restrict__ partials, unsigned* __restrict__ counter,
              double* __restrict__ dscal) {
@@ -191,7 +199,7 @@ k_assemble_a(const double* __restrict__ xi, const int* __restrict__ cells, const
       double xc[D + 1][D];
       CellGeom<D> g;
       load_cell<D>(cells, c, cv);
-      load_cell_coords<D>(xi, cv, xc);
+      load_cell_coords<D>(xi, cv, xc, dg, c);
       cell_geom(xc, g);
       double mj[D + 1], Hj[D + 1][D][D];
 #pragma unroll
@@ -299,6 +307,7 @@ k_assemble_a_gather(const int* __restrict__ v2c_ptr, const int* __restrict__ v2c
 }
 
 // cof(I + h) : dh  (directional derivative of det(I + h) in direction dh)
+__device__ __forceinline__ double cof_contract(const double (&)[1][1], const double (&dh)[1][1]) { return dh[0][0]; }
 __device__ __forceinline__ double cof_contract(const double (&h)[2][2], const double (&dh)[2][2]) {
   return (1.0 + h[1][1]) * dh[0][0] - h[1][0] * dh[0][1] - h[0][1] * dh[1][0] + (1.0 + h[0][0]) * dh[1][1];
 }
@@ -326,7 +335,7 @@ __device__ __forceinline__ double cof_contract(const double (&h)[3][3], const do
 // replaces: the UFL-derived Jacobian of movement/monge_ampere.py:640-645 (psi-row, H-column block)
 template <int D>
 __global__ void __launch_bounds__(MV_BLOCK)
-k_jac_A(const double* __restrict__ xi, const int* __restrict__ cells, const int* __restrict__ v2c_ptr,
+k_jac_A(const double* __restrict__ xi, const int* __restrict__ cells, int dg, const int* __restrict__ v2c_ptr,
         const int* __restrict__ v2c, int64_t nrows, const double* __restrict__ mon, const double* __restrict__ H,
         const double* __restrict__ dH, double sign, double* __restrict__ out) {
   for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < nrows; v += (int64_t)gridDim.x * blockDim.x) {
@@ -340,7 +349,7 @@ k_jac_A(const double* __restrict__ xi, const int* __restrict__ cells, const int*
       double xc[D + 1][D];
       CellGeom<D> g;
       load_cell<D>(cells, c, cv);
-      load_cell_coords<D>(xi, cv, xc);
+      load_cell_coords<D>(xi, cv, xc, dg, c);
       cell_geom(xc, g);
       double cell = 0.0;
 #pragma unroll 1
@@ -456,20 +465,23 @@ __device__ __forceinline__ double monitor_raw(const MonParams& mp, const double 
 __host__ __device__ inline bool monitor_normalised(int kind) { return kind == MV_MON_GAUSS_HESS || kind == MV_MON_SINATAN3; }
 
 // x = xi + g (optional) ; raw monitor at x ; running max for the normalised kinds
+// rep != nullptr (periodic mesh, DG coordinate field): the loop runs over the P1 vertices, vertex v is evaluated at its
+// representative coordinate node rep[v]; the DG field x itself is written by k_update_x_dg
 template <int D, bool UPDATE_X>
 __global__ void __launch_bounds__(MV_BLOCK)
 k_update_x_monitor(int64_t n, const double* __restrict__ xi, const double* __restrict__ g, double* __restrict__ x,
-                   MonParams mp, double* __restrict__ mon, double* __restrict__ dscal) {
+                   MonParams mp, double* __restrict__ mon, double* __restrict__ dscal, const int* __restrict__ rep) {
   double vmax = 0.0;
   for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < n; v += (int64_t)gridDim.x * blockDim.x) {
     double xv[D];
+    const int64_t node = rep ? (int64_t)rep[v] : v;
 #pragma unroll
     for (int a = 0; a < D; ++a) {
       if (UPDATE_X) {
-        xv[a] = xi[v * D + a] + g[v * D + a];
-        x[v * D + a] = xv[a];
+        xv[a] = xi[node * D + a] + g[v * D + a];
+        if (!rep) x[v * D + a] = xv[a];
       } else {
-        xv[a] = x[v * D + a];
+        xv[a] = x[node * D + a];
       }
     }
     if (mp.kind != MV_MON_USER) {
@@ -490,6 +502,19 @@ k_monitor_normalise(int64_t n, double alpha, double* __restrict__ mon, const dou
   const double s = alpha / dscal[D_MONMAX];
   for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < n; v += (int64_t)gridDim.x * blockDim.x)
     mon[v] = fma(s, mon[v], 1.0);
+}
+
+// periodic meshes: x = xi + grad_phi interpolated from the periodic P1 space into the DG coordinate space
+// (movement/monge_ampere.py:236-239), one thread per coordinate node
+template <int D>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_update_x_dg(int64_t nnodes, const int* __restrict__ cells_flat, const double* __restrict__ xi, const double* __restrict__ g,
+              double* __restrict__ x) {
+  for (int64_t nd = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; nd < nnodes; nd += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t v = cells_flat[nd];
+#pragma unroll
+    for (int a = 0; a < D; ++a) x[nd * D + a] = xi[nd * D + a] + g[v * D + a];
+  }
 }
 
 __global__ void k_set_scalar(double* p, double v) { *p = v; }
@@ -525,10 +550,12 @@ static int eval_monitor(mv_ma* ma, bool update_x, const double* xin, double* xou
   const int64_t n = m->V;  // ghosts too: every rank evaluates the monitor at all its local vertices
   const int grid = grid_for(n);
   if (monitor_normalised(mp.kind)) MV_L k_set_scalar<<<1, 1, 0, g_stream>>>(ma->dscal + D_MONMAX, 0.0);
-  if (update_x)
-    MV_L k_update_x_monitor<D, true><<<grid, MV_BLOCK, 0, g_stream>>>(n, xin, ma->f[MV_F_GRAD_PHI], xout, mp, mon, ma->dscal);
-  else
-    MV_L k_update_x_monitor<D, false><<<grid, MV_BLOCK, 0, g_stream>>>(n, nullptr, nullptr, xout, mp, mon, ma->dscal);
+  if (update_x) {
+    MV_L k_update_x_monitor<D, true><<<grid, MV_BLOCK, 0, g_stream>>>(n, xin, ma->f[MV_F_GRAD_PHI], xout, mp, mon, ma->dscal, m->rep);
+    if (m->dg) MV_L k_update_x_dg<D><<<grid_for(m->Vc), MV_BLOCK, 0, g_stream>>>(m->Vc, m->cells, xin, ma->f[MV_F_GRAD_PHI], xout);
+  } else {
+    MV_L k_update_x_monitor<D, false><<<grid, MV_BLOCK, 0, g_stream>>>(n, nullptr, nullptr, xout, mp, mon, ma->dscal, m->rep);
+  }
   MV_KERNEL_CHECK();
   if (monitor_normalised(mp.kind)) {
     // NB the reference demos take a rank-local max (demos/monge_ampere_3d.py:67); a global
@@ -553,10 +580,6 @@ using namespace mv;
 
 extern "C" int mv_ma_create(mv_mesh* m, mv_ma** out) {
   if (!m || !out) return MV_ERR_BADARG;
-  if (m->dim < 2) {
-    set_error("mv_ma_create: 1D meshes are outside the accelerated path (SURVEY 8f-2)");
-    return MV_ERR_UNSUPPORTED;
-  }
   mv_ma* ma = new mv_ma();
   ma->mesh = m;
   const size_t maxc = (size_t)m->dim * m->dim;
@@ -648,7 +671,7 @@ extern "C" int mv_ma_set_boundary(mv_ma* ma, int n_fixed, const int32_t* fixed_t
   for (size_t k = 0; k < tags.size(); ++k) {
     bool fixed = false;
     for (int i = 0; i < n_fixed; ++i) fixed |= (fixed_tags[i] == tags[k]);
-    if (fixed) { bits[k] = all; continue; }
+    if (fixed || d == 1) { bits[k] = all; continue; }   // any tag in 1D: the whole vector is fixed (monge_ampere.py:258-260)
     int nzero = 0, idx = -1;
     for (int a = 0; a < d; ++a) {
       if (fabs(absn[k * d + a]) <= 1e-8) ++nzero; else idx = a;   // np.isclose(., 0.0)
@@ -685,31 +708,21 @@ extern "C" int mv_ma_get_bcmask(mv_ma* ma, uint16_t* dst) {
 namespace mv {
 int l2_rhs_dev(mv_mesh* m, const double* phi, double* b) {
   const int grid = grid_for(m->Vown);
-  if (m->dim == 2)
-    MV_L k_l2_rhs<2><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->Vown, phi, b);
-  else
-    MV_L k_l2_rhs<3><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->Vown, phi, b);
+  MV_DISPATCH_DIM(m->dim, MV_L k_l2_rhs<DIM><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->dg, m->v2c_ptr, m->v2c, m->Vown, phi, b));
   MV_KERNEL_CHECK();
   return MV_OK;
 }
 int hess_rhs_dev(mv_mesh* m, const double* phi, double* c) {
   const int grid = grid_for(m->Vown);
-  if (m->dim == 2)
-    MV_L k_hess_rhs<2><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->v2f_ptr, m->v2f, m->bf_cell,
-                                                   m->bf_normal, m->bf_area, m->Vown, phi, c);
-  else
-    MV_L k_hess_rhs<3><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->v2f_ptr, m->v2f, m->bf_cell,
-                                                   m->bf_normal, m->bf_area, m->Vown, phi, c);
+  MV_DISPATCH_DIM(m->dim, MV_L k_hess_rhs<DIM><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->dg, m->v2c_ptr, m->v2c, m->v2f_ptr, m->v2f,
+                                                                           m->bf_cell, m->bf_normal, m->bf_area, m->Vown, phi, c));
   MV_KERNEL_CHECK();
   return MV_OK;
 }
 int assemble_a_dev(mv_mesh* m, const double* mon, const double* H, double* a, double* dscal) {
   if (!m->cell_tmp) MV_CHECK(dev_alloc(&m->cell_tmp, (size_t)m->C * (m->dim + 1)));
   const int gc = grid_for(m->C), gv = grid_for(m->Vown);
-  if (m->dim == 2)
-    MV_L k_assemble_a_cells<2><<<gc, MV_BLOCK, 0, g_stream>>>(m->cells, m->vol, m->C, mon, H, m->cell_tmp);
-  else
-    MV_L k_assemble_a_cells<3><<<gc, MV_BLOCK, 0, g_stream>>>(m->cells, m->vol, m->C, mon, H, m->cell_tmp);
+  MV_DISPATCH_DIM(m->dim, MV_L k_assemble_a_cells<DIM><<<gc, MV_BLOCK, 0, g_stream>>>(m->cells, m->vol, m->C, mon, H, m->cell_tmp));
   MV_L k_assemble_a_gather<<<gv, MV_BLOCK, 0, g_stream>>>(m->v2c_ptr, m->v2c, m->Vown, m->cell_tmp, a, m->red.partials, m->red.counter,
                                                      dscal);
   MV_KERNEL_CHECK();
@@ -718,10 +731,7 @@ int assemble_a_dev(mv_mesh* m, const double* mon, const double* H, double* a, do
 
 int jac_A_dev(mv_mesh* m, const double* mon, const double* H, const double* dH, double sign, double* out) {
   const int grid = grid_for(m->Vown);
-  if (m->dim == 2)
-    MV_L k_jac_A<2><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->Vown, mon, H, dH, sign, out);
-  else
-    MV_L k_jac_A<3><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->v2c_ptr, m->v2c, m->Vown, mon, H, dH, sign, out);
+  MV_DISPATCH_DIM(m->dim, MV_L k_jac_A<DIM><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->dg, m->v2c_ptr, m->v2c, m->Vown, mon, H, dH, sign, out));
   MV_KERNEL_CHECK();
   return MV_OK;
 }
@@ -777,8 +787,8 @@ extern "C" int mv_ma_update_coordinates(mv_ma* ma) {
   MA_REQUIRE(ma, MV_F_X);
   MA_REQUIRE(ma, MV_F_GRAD_PHI);
   if (ma->mon_kind != MV_MON_USER) MA_REQUIRE(ma, MV_F_MONITOR);
-  if (ma->mesh->dim == 2) return eval_monitor<2>(ma, true, ma->f[MV_F_XI], ma->f[MV_F_X], ma->f[MV_F_MONITOR]);
-  return eval_monitor<3>(ma, true, ma->f[MV_F_XI], ma->f[MV_F_X], ma->f[MV_F_MONITOR]);
+  MV_DISPATCH_DIM(ma->mesh->dim, return eval_monitor<DIM>(ma, true, ma->f[MV_F_XI], ma->f[MV_F_X], ma->f[MV_F_MONITOR]));
+  return MV_OK;
 }
 
 extern "C" int mv_ma_eval_monitor(mv_ma* ma, const double* coords, double* m_out) {
@@ -791,8 +801,8 @@ extern "C" int mv_ma_eval_monitor(mv_ma* ma, const double* coords, double* m_out
     set_error("mv_ma_eval_monitor: device pointers required");
     return MV_ERR_BADARG;
   }
-  if (ma->mesh->dim == 2) return eval_monitor<2>(ma, false, nullptr, (double*)coords, m_out);
-  return eval_monitor<3>(ma, false, nullptr, (double*)coords, m_out);
+  MV_DISPATCH_DIM(ma->mesh->dim, return eval_monitor<DIM>(ma, false, nullptr, (double*)coords, m_out));
+  return MV_OK;
 }
 
 extern "C" int mv_ma_diagnostics(mv_ma* ma, int use_H_old, double* out) {

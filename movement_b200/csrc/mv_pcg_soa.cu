@@ -126,14 +126,20 @@ k_spmv_soa(int64_t nslices, int64_t nrows, const int64_t* __restrict__ slice_ptr
 
 // ------------------------------------------------------------------ PCG pieces
 // r = P (b - mean - A x), p = z = D^-1 r ; sums r.z and b.D^-1.b over the free dofs.  b is interleaved [n,C].
-template <int C>
+// EUCL (multigrid-preconditioned solves, C <= 3): also the Euclidean r.r and b.b, kept at component index 8 + c of the
+// same scalar rows -- the solve then stops only when BOTH sqrt(r.M^-1 r) and ||r||_2 have dropped by rtol, so that
+// "rtol" holds in the unpreconditioned 2-norm the true-residual audit measures (the two norms differ by up to
+// sqrt(cond) on fine meshes: 2.2e-11 instead of 1e-12 at 256^2)
+#define EU 8
+template <int C, bool EUCL>
 __global__ void __launch_bounds__(MV_BLOCK)
 k_init_soa(int64_t n, int64_t ld, const double* __restrict__ b, const double* __restrict__ q, const double* __restrict__ dinv,
            const uint16_t* __restrict__ mask, double* __restrict__ r, double* __restrict__ p, double* __restrict__ partials,
            unsigned* __restrict__ counter, double* __restrict__ scal, double inv_nglobal, int project_mean) {
-  double acc[2 * C];
+  constexpr int NA = EUCL ? 4 * C : 2 * C;
+  double acc[NA];
 #pragma unroll
-  for (int c = 0; c < 2 * C; ++c) acc[c] = 0.0;
+  for (int c = 0; c < NA; ++c) acc[c] = 0.0;
   double mean[C];
 #pragma unroll
   for (int c = 0; c < C; ++c) mean[c] = project_mean ? scal[SC(S_SUM, c)] * inv_nglobal : 0.0;
@@ -149,13 +155,21 @@ k_init_soa(int64_t n, int64_t ld, const double* __restrict__ b, const double* __
       p[c * ld + v] = zz;
       acc[c] = fma(rr, zz, acc[c]);
       acc[C + c] = fix ? acc[C + c] : fma(bb * di, bb, acc[C + c]);
+      if (EUCL) {
+        acc[2 * C + c] = fma(rr, rr, acc[2 * C + c]);
+        acc[3 * C + c] = fix ? acc[3 * C + c] : fma(bb, bb, acc[3 * C + c]);
+      }
     }
   }
-  grid_reduce_sum<2 * C>(acc, partials, counter, [&](double(&t)[2 * C]) {
+  grid_reduce_sum<NA>(acc, partials, counter, [&](double(&t)[NA]) {
 #pragma unroll
     for (int c = 0; c < C; ++c) {
       scal[SC(S_RZ, c)] = t[c];
       scal[SC(S_BB, c)] = t[C + c];
+      if (EUCL) {
+        scal[SC(S_RZ, EU + c)] = t[2 * C + c];
+        scal[SC(S_BB, EU + c)] = t[3 * C + c];
+      }
     }
   });
 }
@@ -175,7 +189,7 @@ __global__ void k_ref_ratio(int C, int phase, double* __restrict__ scal) {
   }
 }
 
-__global__ void k_setup_soa(int C, double rtol, double atol, double* __restrict__ scal, int* __restrict__ flags) {
+__global__ void k_setup_soa(int C, int eucl, double rtol, double atol, double* __restrict__ scal, int* __restrict__ flags) {
   bool all = true;
   for (int c = 0; c < C; ++c) {
     const double rz = scal[SC(S_RZ, c)], bb = scal[SC(S_BB, c)];
@@ -184,6 +198,14 @@ __global__ void k_setup_soa(int C, double rtol, double atol, double* __restrict_
     const double thr = fmax(rtol * rtol * ref, atol * atol);
     scal[SC(S_THR, c)] = thr;
     all = all && (rz <= thr);
+    if (C <= EU) {
+      // Euclidean twin of the test (eucl == 0: switched off, threshold +inf and a zero in the r.r slot)
+      const double rr = eucl ? scal[SC(S_RZ, EU + c)] : 0.0, b2 = eucl ? scal[SC(S_BB, EU + c)] : 0.0;
+      const double thr2 = eucl ? fmax(rtol * rtol * fmax(rr, b2), atol * atol) : 1.7976931348623157e308;
+      scal[SC(S_THR, EU + c)] = thr2;
+      scal[SC(S_RZNEW, EU + c)] = rr;
+      all = all && (rr <= thr2);
+    }
   }
   flags[0] = all ? 1 : 0;
   flags[1] = 0;
@@ -197,6 +219,7 @@ __device__ __forceinline__ void post_update_soa(int C, double* __restrict__ scal
     scal[SC(S_BETA, c)] = rz > 0.0 ? rzn / rz : 0.0;
     scal[SC(S_RZ, c)] = rzn;
     all = all && (rzn <= scal[SC(S_THR, c)]);
+    if (C <= EU) all = all && (scal[SC(S_RZNEW, EU + c)] <= scal[SC(S_THR, EU + c)]);
     if (!(rzn == rzn)) flags[2] = 1;  // NaN: breakdown
   }
   flags[1] += 1;
@@ -283,17 +306,24 @@ __global__ void __launch_bounds__(MV_BLOCK)
 k_dot_rz_soa(int64_t n, int64_t ld, const double* __restrict__ r, const double* __restrict__ z, int* __restrict__ flags,
              double* __restrict__ partials, unsigned* __restrict__ counter, double* __restrict__ scal, int slot, int slot2) {
   if (POST && flags[0]) return;
-  double acc[C];
+  constexpr bool EUCL = POST != 0 && C <= 3;   // the iteration's r.z carries the Euclidean r.r along (same pass over r)
+  constexpr int NA = EUCL ? 2 * C : C;
+  double acc[NA];
 #pragma unroll
-  for (int c = 0; c < C; ++c) acc[c] = 0.0;
+  for (int c = 0; c < NA; ++c) acc[c] = 0.0;
   VERTEX_LOOP(v, n)
 #pragma unroll
-    for (int c = 0; c < C; ++c) acc[c] = fma(r[c * ld + v], z[c * ld + v], acc[c]);
-  grid_reduce_sum<C>(acc, partials, counter, [&](double(&t)[C]) {
+    for (int c = 0; c < C; ++c) {
+      const double rv = r[c * ld + v];
+      acc[c] = fma(rv, z[c * ld + v], acc[c]);
+      if (EUCL) acc[C + c] = fma(rv, rv, acc[C + c]);
+    }
+  grid_reduce_sum<NA>(acc, partials, counter, [&](double(&t)[NA]) {
 #pragma unroll
     for (int c = 0; c < C; ++c) {
       scal[SC(slot, c)] = t[c];
       if (slot2 >= 0) scal[SC(slot2, c)] = t[c];
+      if (EUCL) scal[SC(slot, EU + c)] = t[C + c];
     }
     if (POST == 1) post_update_soa(C, scal, flags);
   });
@@ -447,12 +477,23 @@ int pcg_soa(mv_mesh* m, const double* val, const double* dinv, const double* rhs
   if (C > 1) MV_L k_aos_to_soa<C><<<grid_for(n), MV_BLOCK, 0, g_stream>>>(n, x, xs, ld);
   if (dist) MV_CHECK(halo_exchange_soa(m->halo, n, C, xs, ld));
   MV_CHECK(spmv_soa_launch<C>(m, val, xs, w.q, ld, false));
-  MV_L k_init_soa<C><<<gv, MV_BLOCK, 0, g_stream>>>(n, ld, rhs, w.q, dinv, mask, w.r, w.p, m->red.partials, m->red.counter, w.scal,
-                                               inv_ng, project_mean && rhs ? 1 : 0);
+  constexpr bool CAN_EUCL = C <= 3;
+  const bool eucl = CAN_EUCL && pc != nullptr;
+  const int nred = eucl ? EU + C : C;   // r.z in [0, C) and r.r in [EU, EU + C) of one scalar row: one allreduce
+  if (eucl) {
+    MV_CUDA(cudaMemsetAsync(w.scal + SC(S_RZ, 0), 0, 16 * sizeof(double), g_stream));
+    MV_CUDA(cudaMemsetAsync(w.scal + SC(S_BB, 0), 0, 16 * sizeof(double), g_stream));
+    MV_CUDA(cudaMemsetAsync(w.scal + SC(S_RZNEW, 0), 0, 16 * sizeof(double), g_stream));
+    MV_L k_init_soa<C, CAN_EUCL><<<gv, MV_BLOCK, 0, g_stream>>>(n, ld, rhs, w.q, dinv, mask, w.r, w.p, m->red.partials, m->red.counter,
+                                                           w.scal, inv_ng, project_mean && rhs ? 1 : 0);
+  } else {
+    MV_L k_init_soa<C, false><<<gv, MV_BLOCK, 0, g_stream>>>(n, ld, rhs, w.q, dinv, mask, w.r, w.p, m->red.partials, m->red.counter, w.scal,
+                                                        inv_ng, project_mean && rhs ? 1 : 0);
+  }
   MV_KERNEL_CHECK();
   if (dist) {
-    MV_CHECK(allreduce_sum_dev(w.scal + SC(S_RZ, 0), C));
-    MV_CHECK(allreduce_sum_dev(w.scal + SC(S_BB, 0), C));
+    MV_CHECK(allreduce_sum_dev(w.scal + SC(S_RZ, 0), nred));
+    MV_CHECK(allreduce_sum_dev(w.scal + SC(S_BB, 0), nred));
   }
   if (pc) {
     // z0 = M^-1 r0 by one V-cycle; reference norm r0.z0
@@ -468,7 +509,7 @@ int pcg_soa(mv_mesh* m, const double* val, const double* dinv, const double* rhs
     MV_L k_dir_z_soa<C><<<gv, MV_BLOCK, 0, g_stream>>>(n, ld, pc->z, w.p, w.flags, w.scal, 1);
     MV_KERNEL_CHECK();
   }
-  MV_L k_setup_soa<<<1, 1, 0, g_stream>>>(C, rtol, atol, w.scal, w.flags);
+  MV_L k_setup_soa<<<1, 1, 0, g_stream>>>(C, eucl ? 1 : 0, rtol, atol, w.scal, w.flags);
   MV_KERNEL_CHECK();
 
   int it = 0, batch = pc ? 4 : 8;
@@ -492,7 +533,7 @@ int pcg_soa(mv_mesh* m, const double* val, const double* dinv, const double* rhs
         if (dist) {
           MV_L k_dot_rz_soa<C, 2><<<gv, MV_BLOCK, 0, g_stream>>>(n, ld, w.r, pc->z, w.flags, m->red.partials, m->red.counter, w.scal,
                                                             S_RZNEW, -1);
-          MV_CHECK(allreduce_sum_dev(w.scal + SC(S_RZNEW, 0), C));
+          MV_CHECK(allreduce_sum_dev(w.scal + SC(S_RZNEW, 0), nred));
           MV_L k_post_update_soa<<<1, 1, 0, g_stream>>>(C, w.scal, w.flags);
         } else {
           MV_L k_dot_rz_soa<C, 1><<<gv, MV_BLOCK, 0, g_stream>>>(n, ld, w.r, pc->z, w.flags, m->red.partials, m->red.counter, w.scal,

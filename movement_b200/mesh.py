@@ -155,7 +155,7 @@ class FunctionSpace:
         m, d = self.mesh, self.mesh.geometric_dimension
         return {
             "P1": (m.num_vertices(),), "P1_vec": (m.num_vertices(), d), "P1_ten": (m.num_vertices(), d, d),
-            "P0": (m.num_cells(),),
+            "P0": (m.num_cells(),), "DG1_vec": (m.num_cells() * (d + 1), d),
         }[self.kind]
 
     def __eq__(self, other):
@@ -216,23 +216,31 @@ class Mesh:
     function as its coordinates -- the idiom of movement/mover.py:49.
     """
 
-    def __init__(self, coords, cells=None, bfacets=None, btags=None, device=None, part=None, degree=1):
+    def __init__(self, coords, cells=None, bfacets=None, btags=None, device=None, part=None, degree=1, periodic=False):
         if isinstance(coords, Function):
             src = coords.space.mesh
             self.cells, self.bfacets, self.btags = src.cells, src.bfacets, src.btags
             self.device, self.part, self._degree = src.device, src.part, src._degree
             self._dim = src._dim
             self._nv = src._nv
+            self.periodic = src.periodic
             self._spaces = {}
-            self.coordinates = Function(self.function_space("P1_vec"), name="Coordinates")
+            self.coordinates = Function(self.function_space(src.coordinates.space.kind), name="Coordinates")
             self.coordinates.assign(coords)
             return
         coords = np.ascontiguousarray(coords, dtype=np.float64)
         if coords.ndim == 1:
             coords = coords[:, None]
         self._dim = coords.shape[1]
-        self._nv = int(coords.shape[0])
         self.cells = np.ascontiguousarray(cells, dtype=np.int32)
+        # periodic: `cells` is the periodic P1 cell-node map and the coordinate field is DG1, one copy of every corner
+        # per cell (row c*(d+1)+j = corner j of cell c) -- Firedrake's layout (movement/mover.py:70-75)
+        self.periodic = bool(periodic)
+        if self.periodic:
+            assert coords.shape[0] == self.cells.shape[0] * self.cells.shape[1], "DG coordinates: one row per cell corner"
+            self._nv = int(self.cells.max()) + 1
+        else:
+            self._nv = int(coords.shape[0])
         d = self._dim
         self.bfacets = np.zeros((0, d), np.int32) if bfacets is None else np.ascontiguousarray(bfacets, dtype=np.int32).reshape(-1, d)
         self.btags = np.zeros((0,), np.int32) if btags is None else np.ascontiguousarray(btags, dtype=np.int32)
@@ -240,8 +248,19 @@ class Mesh:
         self.part = part          # None on one GPU; a partition.LocalPart when distributed
         self._degree = degree
         self._spaces = {}
-        self.coordinates = Function(self.function_space("P1_vec"), name="Coordinates")
+        self.coordinates = Function(self.function_space("DG1_vec" if self.periodic else "P1_vec"), name="Coordinates")
         self.coordinates.assign(coords)
+
+    def vertex_coordinates(self):
+        """One position per P1 vertex as a device tensor [V,d]: the coordinate field itself, or, on a periodic mesh, the
+        copy held by the last cell that contains the vertex (what a nodal monitor is evaluated at)."""
+        if not self.periodic:
+            return self.coordinates.tensor
+        if not hasattr(self, "_rep"):
+            rep = np.zeros(self._nv, dtype=np.int64)
+            rep[self.cells.ravel()] = np.arange(self.cells.size)
+            self._rep = torch.as_tensor(rep, device=self.device)
+        return self.coordinates.tensor[self._rep]
 
     # -- Firedrake-like queries ----------------------------------------------------------
     @property
@@ -381,10 +400,44 @@ def UnitTriangleMesh():
                 np.array([[1, 2], [0, 2], [0, 1]]), np.array([1, 1, 1]))
 
 
+def interval_arrays(n):
+    return (np.linspace(0.0, 1.0, n + 1)[:, None], np.stack([np.arange(n), np.arange(n) + 1], axis=1).astype(np.int32),
+            np.array([[0], [n]], dtype=np.int32), np.array([1, 2], dtype=np.int32))
+
+
 def UnitIntervalMesh(n):
-    """1D meshes exist only so that argument validation can reject them like the reference does."""
-    return Mesh(np.linspace(0.0, 1.0, n + 1)[:, None], np.stack([np.arange(n), np.arange(n) + 1], axis=1),
-                np.array([[0], [n]]), np.array([1, 2]))
+    return Mesh(*interval_arrays(n))
+
+
+def _periodic(arrays, shape):
+    """Identify opposite faces of a structured unit mesh numbered on the vertex lattice `shape` (first index slowest):
+    periodic P1 cell-node map + DG coordinates (PeriodicUnit*Mesh, both / all directions)."""
+    from . import parallel
+
+    if parallel.is_active():
+        raise NotImplementedError("periodic meshes are not partitioned over several GPUs yet")
+    coords, cells = arrays[0], arrays[1]
+    per = np.arange(int(np.prod([s - 1 for s in shape]))).reshape([s - 1 for s in shape])
+    for ax in range(len(shape)):
+        per = np.concatenate([per, np.take(per, [0], axis=ax)], axis=ax)
+    pcells = per.ravel()[cells].astype(np.int32)
+    return Mesh(coords[cells].reshape(-1, coords.shape[1]), pcells, None, None, periodic=True)
+
+
+def PeriodicUnitIntervalMesh(n):
+    return _periodic(interval_arrays(n), (n + 1,))
+
+
+def PeriodicUnitSquareMesh(nx, ny=None):
+    """demos/monge_ampere_periodic.py:16."""
+    ny = nx if ny is None else ny
+    return _periodic(square_arrays(nx, ny), (nx + 1, ny + 1))
+
+
+def PeriodicUnitCubeMesh(nx, ny=None, nz=None):
+    ny = nx if ny is None else ny
+    nz = nx if nz is None else nz
+    return _periodic(cube_arrays(nx, ny, nz), (nz + 1, ny + 1, nx + 1))
 
 
 def from_firedrake(fmesh):

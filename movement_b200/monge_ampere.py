@@ -51,8 +51,6 @@ class MongeAmpereMover_Base(PrimeMover, metaclass=abc.ABCMeta):
             raise ValueError("Please supply a monitor function.")
         if mesh.coordinate_degree() != 1:
             raise NotImplementedError(f"{type(self).__name__} not implemented on curved meshes.")
-        if mesh.topological_dimension == 1:
-            raise NotImplementedError(f"{type(self).__name__}: 1D meshes are outside the accelerated path (SURVEY 8f-2).")
         self.maxiter = kwargs.pop("maxiter", 1000)
         self.rtol = kwargs.pop("rtol", 1.0e-08)
         self.dtol = kwargs.pop("dtol", 2.0)
@@ -81,8 +79,7 @@ class MongeAmpereMover_Base(PrimeMover, metaclass=abc.ABCMeta):
     def _create_functions(self):
         super()._create_functions()
         self.monitor = Function(self.P1, name="Monitor function")
-        self._grad_phi = Function(self.P1_vec)
-        self.grad_phi = self._grad_phi  # P1 coordinates: one field serves both (monge_ampere.py:178-179,235)
+        self._grad_phi = Function(self.P1_vec)   # P1 coordinates: one field serves both (monge_ampere.py:178-179,235)
         self.original_volume = Function(self.volume)
         self.total_volume = self._dm.total_volume
         self.phi = Function(self.P1)
@@ -90,6 +87,16 @@ class MongeAmpereMover_Base(PrimeMover, metaclass=abc.ABCMeta):
         self.phi_old = Function(self.P1)
         self.H_old = Function(self.P1_ten)
         self._residual = Function(self.P1, name="Assembled residual")
+
+    @property
+    def grad_phi(self):
+        """grad(phi) in the coordinate space (monge_ampere.py:179): the P1 field itself, or its interpolation into the
+        DG coordinate space on a periodic mesh (:236-239)."""
+        if not self.mesh.periodic:
+            return self._grad_phi
+        g = Function(self.coord_space)
+        g.assign(self._grad_phi.tensor[torch.as_tensor(self.mesh.cells.reshape(-1).astype(np.int64), device=self.mesh.device)])
+        return g
 
     # ---- device state -------------------------------------------------------------------
     def _bind(self):
@@ -322,6 +329,10 @@ class MongeAmpereMover_Relaxation(MongeAmpereMover_Base):
         info = (C.c_int * 3)()
         res0 = C.c_double(0.0)
         i0 = 0
+        import time as _time
+
+        self.chunk_wall = []     # (last iteration of the chunk, seconds since move() entered the loop)
+        t_start = _time.perf_counter()
         while True:
             try:
                 L.check(lib.mv_ma_relax_move(self._ma, self.pseudo_dt, i0, n, int(self.maxiter), float(self.rtol),
@@ -333,6 +344,7 @@ class MongeAmpereMover_Relaxation(MongeAmpereMover_Base):
                     self._convergence_error(exception=e)
                 raise
             i, status, done = int(info[0]), int(info[1]), int(info[2])
+            self.chunk_wall.append((i, _time.perf_counter() - t_start))
             for k in range(done):
                 t = trace[6 * k:6 * k + 6]
                 self.theta = t[0]

@@ -33,18 +33,46 @@ from scipy.special import roots_jacobi
 
 
 class OMesh:
-    """Plain container: coords [V,d] f64, cells [C,d+1] i32, boundary facets + tags."""
+    """Plain container: coords [V,d] f64, cells [C,d+1] i32, boundary facets + tags.
 
-    def __init__(self, coords, cells, bfacets, btags):
+    periodic=True: the Firedrake layout of a periodic mesh (movement/mover.py:70-75, monge_ampere.py:236-239) --
+    ``cells`` is the PERIODIC P1 cell-node map (vertices identified across the seam) while the coordinate field is
+    DG1, one copy of every vertex per cell: coords [C*(d+1), d] with coordinate cell-node map
+    ``ccells[c, j] = c*(d+1) + j``; there are no boundary facets."""
+
+    def __init__(self, coords, cells, bfacets, btags, periodic=False):
         self.coords = np.ascontiguousarray(coords, dtype=np.float64)
+        if self.coords.ndim == 1:
+            self.coords = self.coords[:, None]
         self.cells = np.ascontiguousarray(cells, dtype=np.int32)
-        self.bfacets = np.ascontiguousarray(bfacets, dtype=np.int32)
-        self.btags = np.ascontiguousarray(btags, dtype=np.int32)
         self.dim = self.coords.shape[1]
+        self.bfacets = np.ascontiguousarray(bfacets, dtype=np.int32).reshape(-1, self.dim)
+        self.btags = np.ascontiguousarray(btags, dtype=np.int32)
+        self.periodic = bool(periodic)
+        if self.periodic:
+            C, d1 = self.cells.shape
+            assert self.coords.shape[0] == C * d1
+            self.ccells = np.arange(C * d1, dtype=np.int32).reshape(C, d1)
+            # P1 vertex -> coordinate node: the copy held by the LAST cell that contains the vertex (Firedrake's
+            # interpolation of a coordinate expression into the periodic P1 space writes cell by cell, last one wins)
+            self.rep = np.zeros(int(self.cells.max()) + 1, dtype=np.int64)
+            self.rep[self.cells.ravel()] = np.arange(C * d1)
+        else:
+            self.ccells = self.cells
+            self.rep = None
 
     @property
     def num_vertices(self):
-        return self.coords.shape[0]
+        return int(self.cells.max()) + 1 if self.periodic else self.coords.shape[0]
+
+    def to_coordinate_nodes(self, g):
+        """P1 nodal field -> values at the coordinate nodes (identity on a P1 mesh; CG -> DG interpolation of
+        movement/monge_ampere.py:236-239 on a periodic one)."""
+        return g[self.cells].reshape((-1,) + g.shape[1:]) if self.periodic else g
+
+    def at_vertices(self, x):
+        """coordinate field -> one position per P1 vertex (for nodal monitor evaluation)."""
+        return x[self.rep] if self.periodic else x
 
     @property
     def num_cells(self):
@@ -117,6 +145,37 @@ def unit_interval_mesh(n):
     coords = np.linspace(0.0, 1.0, n + 1)[:, None]
     cells = np.stack([np.arange(n), np.arange(n) + 1], axis=1)
     return OMesh(coords, cells, np.array([[0], [n]]), np.array([1, 2]))
+
+
+def _periodic_from(mesh, shape):
+    """Identify opposite faces of a structured unit mesh whose vertices are numbered on the lattice `shape`
+    (vertex counts per direction, first index slowest): periodic P1 map + DG coordinates."""
+    idx = np.arange(int(np.prod(shape))).reshape(shape)
+    per = np.arange(int(np.prod([s - 1 for s in shape]))).reshape([s - 1 for s in shape])
+    wrap = per
+    for ax, s in enumerate(shape):
+        wrap = np.concatenate([wrap, np.take(wrap, [0], axis=ax)], axis=ax)
+    g2p = np.empty(idx.size, dtype=np.int64)
+    g2p[idx.ravel()] = wrap.ravel()
+    cells = g2p[mesh.cells].astype(np.int32)
+    coords = mesh.coords[mesh.cells].reshape(-1, mesh.dim)
+    return OMesh(coords, cells, np.zeros((0, mesh.dim), np.int32), np.zeros(0, np.int32), periodic=True)
+
+
+def periodic_unit_interval_mesh(n):
+    return _periodic_from(unit_interval_mesh(n), (n + 1,))
+
+
+def periodic_unit_square_mesh(nx, ny=None):
+    """PeriodicUnitSquareMesh(nx, ny), both directions (demos/monge_ampere_periodic.py:16)."""
+    ny = nx if ny is None else ny
+    return _periodic_from(unit_square_mesh(nx, ny), (nx + 1, ny + 1))
+
+
+def periodic_unit_cube_mesh(nx, ny=None, nz=None):
+    ny = nx if ny is None else ny
+    nz = nx if nz is None else nz
+    return _periodic_from(unit_cube_mesh(nx, ny, nz), (nz + 1, ny + 1, nx + 1))
 
 
 # --------------------------------------------------------------------------------------
@@ -389,7 +448,8 @@ class MAOperators:
         V = self.V = mesh.num_vertices
         self.xi = mesh.coords.copy()
         self.cells = mesh.cells
-        self.vol, self.grads = cell_geometry(self.xi, self.cells)
+        self.ccells = mesh.ccells
+        self.vol, self.grads = cell_geometry(self.xi, self.ccells)
         self.total_volume = self.vol.sum()
         self.M = assemble_mass(V, self.cells, self.vol)
         self.K = assemble_stiffness(V, self.cells, self.vol, self.grads)
@@ -598,7 +658,7 @@ class MAOperators:
 
     # -- A4: volume diagnostic  (movement/monge_ampere.py:507-510) -----------------
     def monitor_volumes(self, x, m, vol0):
-        volx, _ = cell_geometry(x, self.cells)
+        volx, _ = cell_geometry(x, self.ccells)
         return volx * m[self.cells].mean(axis=1) / vol0
 
 
@@ -620,7 +680,7 @@ class OracleRelaxation:
         self.phi = np.zeros(V)
         self.H = np.zeros((V, d, d))
         self.vol0 = self.ops.vol.copy()
-        self.tangling = OracleTanglingChecker(self.xi, self.ops.cells, raise_error=raise_convergence_errors)
+        self.tangling = OracleTanglingChecker(self.xi, self.ops.ccells, raise_error=raise_convergence_errors)
         self.trace = []
         self.verbose = verbose
 
@@ -632,9 +692,9 @@ class OracleRelaxation:
         i = 0
         for i in range(self.maxiter):
             self.grad_phi = o.l2_project_grad(self.phi_old)
-            self.x = self.xi + self.grad_phi
+            self.x = self.xi + o.mesh.to_coordinate_nodes(self.grad_phi)   # CG -> DG on periodic meshes (:236-239)
             self.tangling.check(self.xi)  # quirk: mesh.coordinates holds xi here
-            self.m = self.monitor(self.x)
+            self.m = self.monitor(o.mesh.at_vertices(self.x))
             self.volume = o.monitor_volumes(self.x, self.m, self.vol0)
             _, self.theta, r, residual = o.theta_residual(self.m, self.H_old)
             if i == 0:
@@ -704,8 +764,8 @@ class OracleQuasiNewton:
     def update_monitor(self, phi, H):
         o = self.ops
         g = o.l2_project_grad(phi)
-        self.x = self.xi + g
-        self.m = self.monitor(self.x)
+        self.x = self.xi + o.mesh.to_coordinate_nodes(g)
+        self.m = self.monitor(o.mesh.at_vertices(self.x))
         a = o.assemble_a(self.m, H)
         self.theta = a.sum() / o.total_volume
         return a

@@ -315,3 +315,59 @@ def test_quadrature_rules_exact_for_degree_d_plus_2():
             exact = math.factorial(d) * math.prod(math.factorial(a) for a in alpha) / math.factorial(sum(alpha) + d)
             got = (w * np.prod(lam ** np.array(alpha), axis=1)).sum()
             assert abs(got - exact) < 1e-15
+
+
+# ------------------------------------------------------------------ periodic meshes
+def _periodic_ring(x):
+    """demos/monge_ampere_periodic.py:24-30 (gamma enters unsquared)."""
+    r = ((x - 0.5) ** 2).sum(axis=1)
+    return 1.0 + 20.0 / np.cosh(200.0 * (r - 0.15)) ** 2
+
+
+@pytest.mark.slow
+def test_periodic_demo_quasi_newton_trace():
+    """demos/monge_ampere_periodic.py:41-131: the 90-line trace the reference prints for PeriodicUnitSquareMesh(20, 20).
+    Iteration 0 is an exact known answer (11.49 / 9.71e-01 / 9.19e-01); the plateau near 1.59e-01 and the fixed point
+    (8.81 / 3.49e-01) pin the periodic P1 map + DG coordinate field of movement/monge_ampere.py:236-239; the iteration
+    count differs by the linear solver (exact Newton solves here, GMRES to 1e-5 in the reference: 89)."""
+    blk = GOLD["demos/monge_ampere_periodic.py"][0]
+    mesh = mo.periodic_unit_square_mesh(20)
+    assert mesh.num_vertices == 400 and mesh.coords.shape == (2400, 2)
+    q = mo.OracleQuasiNewton(mesh, _periodic_ring, rtol=1e-8)
+    nit = q.move()
+    assert _fmt(*q.trace[0][1:]) == blk["text"][0]
+    assert abs(nit - blk["converged_in"]) <= 15
+    ref = blk["rows"]
+    for it in range(12, 40):  # the plateau (demos/monge_ampere_periodic.py:53-80)
+        assert abs(q.trace[it][3] - ref[it][3]) <= 0.04 * ref[it][3]
+        assert abs(q.trace[it][2] - ref[it][2]) <= 0.02 * ref[it][2]
+    assert _fmt(*q.trace[-1][1:])[:2] == blk["text"][-1][:2]  # 8.81 / 3.49e-01
+    # the domain keeps its area and the seam copies of a vertex move together (demo :150-170)
+    vol, _ = mo.cell_geometry(q.x, mesh.ccells)
+    assert abs(vol.sum() - 1.0) < 1e-12
+
+
+@pytest.mark.parametrize("dim", [1, 2, 3])
+def test_periodic_relaxation_no_boundary_conditions(dim):
+    """test/test_monge_ampere.py:296-311: no boundary conditions on periodic unit domains, volume conserved."""
+    n = {1: 10, 2: 10, 3: 4}[dim]
+    mesh = (mo.periodic_unit_interval_mesh, mo.periodic_unit_square_mesh, mo.periodic_unit_cube_mesh)[dim - 1](n)
+    o = mo.OracleRelaxation(mesh, mo.monitor_test_ring, rtol=1e-3)
+    assert not o.ops.bc_mask.any()
+    o.move()
+    vol, _ = mo.cell_geometry(o.x, mesh.ccells)
+    assert abs(vol.sum() - 1.0) < 1e-12
+    assert o.trace[-1][3] < 1e-3
+
+
+def test_interval_relaxation_constant_and_ring():
+    """test/test_monge_ampere.py:174-202 in 1D: a constant monitor converges at iteration 0 and leaves the mesh alone;
+    the ring monitor moves interior vertices while both end points (any tag in 1D, monge_ampere.py:258-260) stay."""
+    mesh = mo.unit_interval_mesh(10)
+    o = mo.OracleRelaxation(mesh, mo.monitor_const, rtol=1e-3)
+    assert o.move() == 0 and np.abs(o.x - mesh.coords).max() == 0.0
+    o = mo.OracleRelaxation(mesh, mo.monitor_test_ring, rtol=1e-3)
+    o.move()
+    assert o.ops.bc_mask[[0, 10]].all() and not o.ops.bc_mask[1:10].any()
+    assert np.abs(o.x[[0, 10]] - mesh.coords[[0, 10]]).max() == 0.0
+    assert np.abs(o.x - mesh.coords).max() > 1e-3
