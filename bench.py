@@ -349,21 +349,41 @@ def run_relaxation(args, dim):
     peak, peak_src = peaks()
     have_mask = bool(getattr(mover, "_have_bc", True))
     classes = {}
+    mixed = cheb and os.environ.get("MV_CHEB_MIXED", "1") != "0"
+    #   mixed-precision Chebyshev (default): single-precision iteration: 8 B per non-zero; dinv, r, d_{k-1} in, d_{k+1} out,
+    #   own d_k = 4 + 16 C B per row; double-precision residual pass (timed as class C + 4): 12 B per non-zero; dinv, b, x in,
+    #   r and d_1 out (single) = 8 + 24 C B per row
     for c in (1, dim, dim * dim):
         if spmv_cnt[c] > 0:
             fused = cheb and c != 1
-            per_row = (4.0 + 8.0 + 32.0 * c + (2.0 if (c == dim and have_mask) else 0.0)) if fused else (4.0 + 16.0 * c)
-            alg = 12.0 * dm.nnz + per_row * dm.Vown
+            if fused and mixed:
+                alg = 8.0 * dm.nnz + (4.0 + 4.0 + 16.0 * c + (2.0 if (c == dim and have_mask) else 0.0)) * dm.Vown
+                kern = "k_cheb_tma<float>" if c == 9 else "k_mcheb (fp32 iteration)"
+            else:
+                per_row = (4.0 + 8.0 + 32.0 * c + (2.0 if (c == dim and have_mask) else 0.0)) if fused else (4.0 + 16.0 * c)
+                alg = 12.0 * dm.nnz + per_row * dm.Vown
+                kern = ("k_cheb_tma" if c == 9 else "k_cheb_soa") if fused else "k_spmv_soa"
             avg = spmv_ms[c] / spmv_cnt[c]
-            classes[c] = {"rhs": c, "kernel": ("k_cheb_tma" if c == 9 else "k_cheb_soa") if fused else "k_spmv_soa", "launches_timed": int(spmv_cnt[c]),
+            classes[c] = {"rhs": c, "kernel": kern, "launches_timed": int(spmv_cnt[c]),
                           "avg_launch_ms": avg, "algorithmic_bytes_per_launch": alg,
                           "achieved_GBs": alg / (avg * 1e-3) / 1e9, "share_of_step": spmv_ms[c] / ms}
+            if fused and mixed and spmv_cnt[c + 4] > 0:
+                alg = 12.0 * dm.nnz + (4.0 + 8.0 + 24.0 * c + (2.0 if (c == dim and have_mask) else 0.0)) * dm.Vown
+                avg = spmv_ms[c + 4] / spmv_cnt[c + 4]
+                classes[c + 4] = {"rhs": c, "kernel": "fp64 residual pass of the mixed-precision Chebyshev solver", "launches_timed": int(spmv_cnt[c + 4]),
+                                  "avg_launch_ms": avg, "algorithmic_bytes_per_launch": alg,
+                                  "achieved_GBs": alg / (avg * 1e-3) / 1e9, "share_of_step": spmv_ms[c + 4] / ms}
     dom = max(classes, key=lambda c: classes[c]["share_of_step"])
     traffic = ncu_traffic()
-    role = {1: "stiffness matrix, Poisson PCG", dim: "mass matrix, L2 projection of grad phi", dim * dim: "mass matrix, Hessian recovery"}[dom]
-    kname = (f"fused Chebyshev iteration, {'TMA-staged matrix stream, k_cheb_tma' if dom == 9 else 'k_cheb_soa'}<{dom},...> ({role})"
-             if cheb and dom != 1 else f"SELL-32 SpMV + fused p.q, k_spmv_soa<{dom},true> ({role})")
-    tr = (traffic or {}).get(("cheb" if cheb and dom != 1 else "spmv") + str(dom)) or {}
+    domc = classes[dom]["rhs"]
+    role = {1: "stiffness matrix, Poisson PCG", dim: "mass matrix, L2 projection of grad phi", dim * dim: "mass matrix, Hessian recovery"}[domc]
+    if cheb and domc != 1 and mixed:
+        kname = f"{classes[dom]['kernel']}, C = {domc} ({role})"
+    elif cheb and domc != 1:
+        kname = f"fused Chebyshev iteration, {'TMA-staged matrix stream, k_cheb_tma' if dom == 9 else 'k_cheb_soa'}<{dom},...> ({role})"
+    else:
+        kname = f"SELL-32 SpMV + fused p.q, k_spmv_soa<{dom},true> ({role})"
+    tr = (traffic or {}).get(("mcheb" if mixed and domc != 1 else ("cheb" if cheb and domc != 1 else "spmv")) + str(domc)) or {}
     roofline = {"bound": "hbm", "kernel": kname,
                 "achieved": classes[dom]["achieved_GBs"], "peak": peak, "unit": "GB/s", "frac": classes[dom]["achieved_GBs"] / peak,
                 "peak_source": peak_src, "frac_of_nominal_8TBs": classes[dom]["achieved_GBs"] / 8000.0,
@@ -380,6 +400,9 @@ def run_relaxation(args, dim):
     bcg = lambda c: 12 * nnzv + 4 + 104 * c  # noqa: E731
     bmass = (lambda c: 12 * nnzv + 12 + 32 * c) if cheb else bcg  # noqa: E731
     step_bytes = float(np.mean(cg[:, 0] * bmass(d) + cg[:, 1] * bcg(1) + cg[:, 2] * bmass(d * d))) * Vglobal
+    if mixed:   # mass solves: the launches of the timed region with their own byte counts (this rank's share x world)
+        step_bytes = float(np.mean(cg[:, 1] * bcg(1))) * Vglobal + world * sum(
+            v["algorithmic_bytes_per_launch"] * v["launches_timed"] for k, v in classes.items() if v["rhs"] != 1) / args.steps
     step_gbs = step_bytes / (ms / args.steps * 1e-3) / 1e9
 
     # ---- where a step goes: two more (untimed above) iterations with CUDA events between the phases, max over ranks;

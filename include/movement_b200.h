@@ -47,7 +47,7 @@ enum { MV_OP_MASS = 0, MV_OP_STIFFNESS = 1, MV_OP_MASS_PLUS_STIFFNESS = 2 };
 /* preconditioner of the stiffness-type operators (the mass solves always use Jacobi):
  * replaces the `pc_type` choices of movement/solver_parameters.py:62-71 (bjacobi/ilu, gamg) */
 enum { MV_PC_JACOBI = 0, MV_PC_AMG = 1 };
-enum { MV_MASS_PCG = 0, MV_MASS_CHEBYSHEV = 1 };
+enum { MV_MASS_PCG = 0, MV_MASS_CHEBYSHEV = 1, MV_MASS_CHEBYSHEV_FP64 = 2 };
 
 /* built-in (fused) monitor functions -- replaces: movement/monitor.py:138-143,
  * test/monitors.py:9-16, demos/monge_ampere_helmholtz.py:54-61,115-122,
@@ -172,8 +172,9 @@ int mv_set_preconditioner(mv_mesh* m, int kind);
 /* Solver behind MV_OP_MASS in mv_pcg_solve and the Monge-Ampere mass solves (replaces: KSP cg + bjacobi/ilu,
  * movement/solver_parameters.py:62-66 at monge_ampere.py:340,483).  MV_MASS_CHEBYSHEV (default): one fused kernel
  * per iteration on Wathen's a-priori interval [1/2, 1 + d/2] of diag(M)^-1 M for P1 simplices, same measured
- * stopping rule as the PCG (sqrt(r.D^-1 r) <= max(rtol*ref, atol)); MV_MASS_PCG: Jacobi-preconditioned CG.
- * Process-wide.                                                                                              */
+ * stopping rule as the PCG (sqrt(r.D^-1 r) <= max(rtol*ref, atol)), carried out as iterative refinement: residual
+ * passes and the solution in double, sweeps of <= 16 Chebyshev iterations on the correction in single precision;
+ * MV_MASS_CHEBYSHEV_FP64: every iteration in double; MV_MASS_PCG: Jacobi-preconditioned CG.  Process-wide.      */
 int mv_set_mass_solver(int kind);
 /* Hierarchy of the cached multigrid preconditioner of `op` (after a solve): info[0] = levels
  * (0 = none built), info[1] = rows of the coarsest level, info[2] = 1 if that level is solved
@@ -189,10 +190,20 @@ int mv_amg_level_get(mv_mesh* m, int op, int level, int which, int64_t* size, in
 int mv_ma_create(mv_mesh* m, mv_ma** out);
 void mv_ma_destroy(mv_ma* ma);
 int mv_ma_bind(mv_ma* ma, int field, double* device_ptr);
-/* replaces: monge_ampere.py:246-272 (axis-aligned branch).  fixed_tags: boundary tags with
- * a full zero Dirichlet condition.  Returns MV_ERR_UNSUPPORTED if a segment is not
- * axis-aligned (EquationBC branch, monge_ampere.py:274-309, not built yet).          */
+/* replaces: monge_ampere.py:246-309, the boundary conditions of the L2 projector, decided per boundary tag like
+ * _l2_projector_bcs does: tags in fixed_tags (and every tag in 1D) get a full zero Dirichlet condition; a free
+ * axis-aligned segment (assemble(abs(n_i) ds) close to zero for all but one i) has that component fixed; any other free
+ * segment takes the EquationBC branch (:274-309): before every projection the tangential gradient of phi_old is
+ * L2-projected onto the segment with its boundary mass matrix, nodes shared with another segment pinned to zero, and
+ * the result is Dirichlet data of the mass solve (csrc/mv_eqbc.cu).  The straight-line / plane check of :288-299 is the
+ * host mirror's (movement_b200/monge_ampere.py).
+ * _ex: all_tags = every boundary tag of the whole mesh (the same list on every rank): the abs(n_i) integrals are
+ * summed over the ranks before the decision, so all ranks take the same branch; kinds (optional, one per sorted
+ * unique tag) receives 0 = Dirichlet, 1 + i = component i fixed, -1 = EquationBC.  EquationBC segments on a
+ * partitioned mesh: MV_ERR_UNSUPPORTED on every rank.                                                             */
 int mv_ma_set_boundary(mv_ma* ma, int n_fixed, const int32_t* fixed_tags);
+int mv_ma_set_boundary_ex(mv_ma* ma, int n_fixed, const int32_t* fixed_tags, int n_all, const int32_t* all_tags,
+                          int32_t* kinds);
 /* uint16 per owned vertex, bit c set = component c of grad_phi is a Dirichlet dof */
 int mv_ma_get_bcmask(mv_ma* ma, uint16_t* dst);
 int mv_ma_set_solver(mv_ma* ma, double rtol, double atol, int maxit_mass, int maxit_poisson);

@@ -7,7 +7,7 @@ importing the package does not need a GPU, constructing a mover does -- there is
 """
 from .exceptions import ConvergenceError  # noqa: F401
 from .laplacian_smoothing import *  # noqa: F401,F403
-from .mesh import (DirichletBC, Function, Mesh, PeriodicUnitCubeMesh, PeriodicUnitIntervalMesh,  # noqa: F401
+from .mesh import (DirichletBC, EquationBC, Function, Mesh, PeriodicUnitCubeMesh, PeriodicUnitIntervalMesh,  # noqa: F401
                    PeriodicUnitSquareMesh, RectangleMesh, UnitCubeMesh, UnitIntervalMesh, UnitSquareMesh,
                    UnitTriangleMesh, from_firedrake)
 from .monge_ampere import *  # noqa: F401,F403

@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libmovement_b200.so")
 MV_OK, MV_ERR_BADARG, MV_ERR_CUDA, MV_ERR_NOT_CONVERGED, MV_ERR_VALENCE, MV_ERR_COMM, MV_ERR_UNSUPPORTED = range(7)
 MV_OP_MASS, MV_OP_STIFFNESS, MV_OP_MASS_PLUS_STIFFNESS = 0, 1, 2
 MV_PC_JACOBI, MV_PC_AMG = 0, 1
-MV_MASS_PCG, MV_MASS_CHEBYSHEV = 0, 1
+MV_MASS_PCG, MV_MASS_CHEBYSHEV, MV_MASS_CHEBYSHEV_FP64 = 0, 1, 2
 MV_MON_CONST, MV_MON_BALL, MV_MON_BALL_RAW, MV_MON_GAUSS_HESS, MV_MON_SINATAN3, MV_MON_USER = 0, 1, 2, 3, 4, 100
 (MV_F_XI, MV_F_X, MV_F_PHI, MV_F_PHI_OLD, MV_F_H, MV_F_H_OLD, MV_F_GRAD_PHI, MV_F_MONITOR, MV_F_VOLUME,
  MV_F_ORIG_VOLUME, MV_F_RESIDUAL) = range(11)
@@ -55,6 +55,7 @@ SIGNATURES = {
     "mv_ma_destroy": (None, [_vp]),
     "mv_ma_bind": (_i, [_vp, _i, _vp]),
     "mv_ma_set_boundary": (_i, [_vp, _i, _vp]),
+    "mv_ma_set_boundary_ex": (_i, [_vp, _i, _vp, _i, _vp, _vp]),
     "mv_ma_get_bcmask": (_i, [_vp, _vp]),
     "mv_ma_set_solver": (_i, [_vp, _d, _d, _i, _i]),
     "mv_ma_set_monitor": (_i, [_vp, _i, _i, _pd]),

@@ -61,6 +61,7 @@ Amg::~Amg() {
     dev_free(L.Pval);
     dev_free(L.Rval);
     L.Rc.release();
+    L.Ac.release();
     dev_free(L.x0);
     if (l > 0) dev_free(L.b);
     dev_free(L.x1); dev_free(L.r); dev_free(L.d0); dev_free(L.d1);
@@ -996,6 +997,16 @@ static int amg_build(mv_mesh* m, int op, const uint16_t* mask_bit0, int singular
       if (st == MV_OK) MV_L k_to_float<<<grid_for(F.pat.len), MV_BLOCK, 0, g_stream>>>(F.pat.len, F.val, F.valf);
     }
   }
+  // Coarse levels of a few 10^4 rows with ~80 non-zeros per row: one thread per row walks the row serially (36 us per
+  // pass at 21 k rows, ncu round 2: 9 % of any unit -- latency); kept in CSR as well and smoothed one warp per row.
+  if (st == MV_OK && env_int("MV_AMG_CSR_COARSE", 1)) {
+    const size_t nsm = a->lv.size() - (a->coarse_inv ? 1 : 0);
+    for (size_t l = 1; l < nsm && st == MV_OK; ++l) {
+      AmgLevel& S = a->lv[l];
+      if (S.dist || !S.val || S.n == 0 || S.n > 400000 || S.pat.nnz < 24 * S.n) continue;
+      st = sell_rows_to_csr(S.pat, S.val, 0, S.n, S.ntot, nullptr, S.Ac);
+    }
+  }
   // Work split of large replicated levels: the tail of a multi-GPU hierarchy is replicated, so its cost does not
   // shrink with the number of ranks (256^3: level 1 has 1.5 M rows, ~25 ms per relaxation step on every rank,
   // half of the step at 8 GPUs).  Each rank then smooths only its chunk of slices and the vectors are allgathered.
@@ -1004,7 +1015,7 @@ static int amg_build(mv_mesh* m, int op, const uint16_t* mask_bit0, int singular
     const size_t nsm = a->lv.size() - (a->coarse_inv ? 1 : 0);
     for (size_t l = 1; l < nsm; ++l) {
       AmgLevel& S = a->lv[l];
-      if (S.dist || S.n < split_min || S.ntot != S.n) continue;
+      if (S.dist || S.n < split_min || S.ntot != S.n || S.Ac.ptr) continue;
       const int64_t per = (S.pat.nslices + comm_size() - 1) / comm_size();
       S.split_chunk = per * MV_SLICE;
       S.split_lo = std::min<int64_t>(S.n, (int64_t)comm_rank() * S.split_chunk);

@@ -191,6 +191,63 @@ k_csr_apply_warp(int64_t nrows, const int64_t* __restrict__ ptr, const int* __re
   }
 }
 
+// The smoother passes of a small coarse level in CSR, one warp per row (rows of ~80 non-zeros: the SELL kernels above walk
+// them serially, one thread per row).  Same arithmetic per row up to the order of the row sum (fixed shuffle tree).
+template <int C>
+__device__ __forceinline__ void csr_row_dot(const int64_t* __restrict__ ptr, const int* __restrict__ col, const double* __restrict__ val,
+                                            const double* __restrict__ x, int64_t ld, int64_t row, int lane, double (&acc)[C]) {
+#pragma unroll
+  for (int c = 0; c < C; ++c) acc[c] = 0.0;
+  const int64_t b = ptr[row], e = ptr[row + 1];
+  for (int64_t t = b + lane; t < e; t += 32) {
+    const double a = val[t];
+    const double* xp = x + col[t];
+#pragma unroll
+    for (int c = 0; c < C; ++c) acc[c] = fma(a, __ldg(xp + c * ld), acc[c]);
+  }
+#pragma unroll
+  for (int c = 0; c < C; ++c) acc[c] = warp_sum(acc[c]);
+}
+#define ROW_LOOP                                                                           \
+  const int lane = threadIdx.x & 31;                                                       \
+  const int64_t warp0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;             \
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;                           \
+  for (int64_t row = warp0; row < nrows; row += nwarps)
+
+// MODE 0: k_smooth_first, 1: k_smooth_next, 2: k_residual (arguments as there; unused ones nullptr)
+template <int C, int MODE>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_smooth_csr(int64_t nrows, int64_t ld, const int64_t* __restrict__ ptr, const int* __restrict__ col, const double* __restrict__ val,
+             const double* __restrict__ b, const double* __restrict__ xin, const double* __restrict__ dinv, double c1, double c2,
+             double* __restrict__ xout, double* __restrict__ dout, double* __restrict__ rout, const int* __restrict__ done) {
+  if (done && *done) return;
+  ROW_LOOP {
+    double acc[C];
+    csr_row_dot<C>(ptr, col, val, xin, ld, row, lane, acc);
+    if (lane < C) {
+      double a = acc[0];
+#pragma unroll
+      for (int c = 1; c < C; ++c) a = lane == c ? acc[c] : a;
+      const int64_t i = lane * ld + row;
+      const double di = dinv[row];
+      const double t = di != 0.0 ? b[i] - a : 0.0;
+      if (MODE == 0) {            // b = right-hand side, xin = iterate: x' = x + sc D^-1 r
+        const double dd = c2 * di * t;
+        xout[i] = xin[i] + dd;
+        if (dout) dout[i] = dd;
+        if (rout) rout[i] = t;
+      } else if (MODE == 1) {     // b = r_in, xin = d_in: d' = c1 d + c2 D^-1 (r - A d), x += d'
+        const double dd = c1 * xin[i] + c2 * di * t;
+        dout[i] = dd;
+        xout[i] += dd;
+        if (rout) rout[i] = t;
+      } else {
+        rout[i] = t;
+      }
+    }
+  }
+}
+
 // x = Ainv b on the coarsest level: one warp per owned row (global row goff + row), lanes stride the N
 // columns, fixed-order shuffle sum.  Multi-GPU: b is the gathered right-hand side of all ranks.
 template <int C>
@@ -287,7 +344,10 @@ static int smooth(AmgLevel& L, const double* b, const double* xin, double* xout,
     MV_L k_smooth_zero<C><<<grid_for(L.n), MV_BLOCK, 0, g_stream>>>(L.n, L.ntot, b, L.dinv, 1.0 / theta, xout, dcur, done);
   } else {
     x_partial = split;
-    if (L.valf)
+    if (L.Ac.ptr)
+      MV_L k_smooth_csr<C, 0><<<grid_for(L.n * 32), MV_BLOCK, 0, g_stream>>>(L.n, L.ntot, L.Ac.ptr, L.Ac.col, L.Ac.val, b, xin, L.dinv, 0.0, 1.0 / theta,
+                                                                        xout, dcur, deg > 1 ? L.r : nullptr, done);
+    else if (L.valf)
       MV_L k_smooth_first<C, float><<<grid, MV_BLOCK, 0, g_stream>>>(s0, s1, L.n, L.ntot, p.slice_ptr, p.cols, L.valf, b, xin, L.dinv, 1.0 / theta,
                                                                 xout, dcur, deg > 1 ? L.r : nullptr, done);
     else
@@ -302,7 +362,10 @@ static int smooth(AmgLevel& L, const double* b, const double* xin, double* xout,
     if (L.dist) MV_CHECK(halo_exchange_soa(L.halo, L.n, C, dcur, L.ntot));
     if (split && x_partial) MV_CHECK(allgather_rows_dev(dcur, L.ntot, C, L.split_chunk));   // (after k_smooth_zero d is complete everywhere)
     x_partial = split;
-    if (L.valf)
+    if (L.Ac.ptr)
+      MV_L k_smooth_csr<C, 1><<<grid_for(L.n * 32), MV_BLOCK, 0, g_stream>>>(L.n, L.ntot, L.Ac.ptr, L.Ac.col, L.Ac.val, rin, dcur, L.dinv, rho_n * rho_k,
+                                                                        2.0 * rho_n / delta, xout, dnext, last ? nullptr : L.r, done);
+    else if (L.valf)
       MV_L k_smooth_next<C, float><<<grid, MV_BLOCK, 0, g_stream>>>(s0, s1, L.n, L.ntot, p.slice_ptr, p.cols, L.valf, dcur, dnext, rin,
                                                                last ? nullptr : L.r, L.dinv, rho_n * rho_k, 2.0 * rho_n / delta, xout, done);
     else
@@ -331,7 +394,10 @@ static int vcycle(mv_mesh* m, Amg* a, const double* rfine, double* z, const int*
       const int64_t s0 = split ? L.split_lo / MV_SLICE : 0;
       const int64_t s1 = split ? (L.split_hi > L.split_lo ? (L.split_hi + MV_SLICE - 1) / MV_SLICE : s0) : L.pat.nslices;
       const int rg = split ? grid_for((s1 - s0 > 0 ? s1 - s0 : 1) * MV_SLICE, 8) : slice_grid(L.pat);
-      if (L.valf)
+      if (L.Ac.ptr)
+        MV_L k_smooth_csr<C, 2><<<grid_for(L.n * 32), MV_BLOCK, 0, g_stream>>>(L.n, L.ntot, L.Ac.ptr, L.Ac.col, L.Ac.val, b, L.x0, L.dinv, 0.0, 0.0, nullptr,
+                                                                          nullptr, L.r, done);
+      else if (L.valf)
         MV_L k_residual<C, float><<<rg, MV_BLOCK, 0, g_stream>>>(s0, s1, L.n, L.ntot, L.pat.slice_ptr, L.pat.cols, L.valf, b, L.x0, L.dinv, L.r, done);
       else
         MV_L k_residual<C, double><<<rg, MV_BLOCK, 0, g_stream>>>(s0, s1, L.n, L.ntot, L.pat.slice_ptr, L.pat.cols, L.val, b, L.x0, L.dinv, L.r, done);

@@ -286,6 +286,35 @@ int halo_exchange_soa(const Halo& h, int64_t nown, int C, double* vec, int64_t l
   return MV_OK;
 }
 
+// single-precision vectors (the correction iterates of the mixed-precision Chebyshev sweeps); the send buffer of the
+// plan is sized for MV_MAX_COMP doubles per entry, so the float payload always fits
+__global__ void k_halo_pack_soa_f32(int64_t nsend, int C, const int* __restrict__ idx, const float* __restrict__ vec, int64_t ld,
+                                    float* __restrict__ buf) {
+  const int64_t n = nsend * C;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t c = i / nsend, t = i - c * nsend;
+    buf[i] = vec[c * ld + idx[t]];
+  }
+}
+int halo_exchange_soa_f32(const Halo& h, int64_t nown, int C, float* vec, int64_t ld) {
+  if (!comm_active() || h.nn == 0) return MV_OK;
+  if (C <= h.p2p_maxC) return p2p_halo_exchange_f32(h, nown, C, vec, ld, nullptr);
+  const int64_t nsend = h.send_ptr[h.nn];
+  float* sbuf = reinterpret_cast<float*>(h.send_buf);
+  if (nsend > 0) MV_L k_halo_pack_soa_f32<<<grid_for(nsend * C), MV_BLOCK, 0, g_stream>>>(nsend, C, h.send_idx, vec, ld, sbuf);
+  MV_KERNEL_CHECK();
+  MV_NCCL(g_nccl.GroupStart());
+  for (int k = 0; k < h.nn; ++k) {
+    const int64_t ns = h.send_ptr[k + 1] - h.send_ptr[k], nr = h.recv_ptr[k + 1] - h.recv_ptr[k];
+    for (int c = 0; c < C; ++c) {
+      if (ns > 0) MV_NCCL(g_nccl.Send(sbuf + c * nsend + h.send_ptr[k], (size_t)ns, ncclFloat, h.ranks[k], g_comm, g_stream));
+      if (nr > 0) MV_NCCL(g_nccl.Recv(vec + c * ld + nown + h.recv_ptr[k], (size_t)nr, ncclFloat, h.ranks[k], g_comm, g_stream));
+    }
+  }
+  MV_NCCL(g_nccl.GroupEnd());
+  return MV_OK;
+}
+
 }  // namespace mv
 
 using namespace mv;

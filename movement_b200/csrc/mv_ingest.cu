@@ -512,6 +512,8 @@ extern "C" void mv_mesh_destroy(mv_mesh* m) {
   dev_free(m->dinvM); dev_free(m->dinvK); dev_free(m->dinvMK); dev_free(m->edge_opp); dev_free(m->cell_gid); dev_free(m->rep);
   dev_free(m->red.partials); dev_free(m->red.counter);
   dev_free(m->pcg.r); dev_free(m->pcg.p); dev_free(m->pcg.q); dev_free(m->pcg.xs); dev_free(m->pcg.scal); dev_free(m->pcg.flags);
+  for (int i = 0; i < 3; ++i) dev_free(m->pcg.f32[i]);
+  dev_free(m->pcg.valf); dev_free(m->pcg.dinvf);
   if (m->pcg.h_flags) cudaFreeHost(m->pcg.h_flags);
   if (m->pcg.h_scal) cudaFreeHost(m->pcg.h_scal);
   dev_free(m->halo.send_idx); dev_free(m->halo.send_buf);

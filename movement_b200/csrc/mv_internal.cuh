@@ -148,6 +148,12 @@ struct PcgWork {
   int* flags = nullptr;     // device: [0]=done, [1]=iterations, [2]=breakdown
   int* h_flags = nullptr;   // pinned host mirror
   double* h_scal = nullptr; // pinned host mirror
+  // mixed-precision Chebyshev (mv_cheb.cu): residual and two correction iterates in single, [V*MV_MAX_COMP] each,
+  // single-precision copy of the operator values / inverse diagonal the sweeps stream
+  float* f32[3] = {nullptr, nullptr, nullptr};
+  float* valf = nullptr;
+  float* dinvf = nullptr;
+  const double* f32_src = nullptr;
 };
 
 // ---------------------------------------------------------------------------------
@@ -175,6 +181,7 @@ struct AmgLevel {
   Sell P;  double* Pval = nullptr;   // [n x n_coarse]
   Sell R;  double* Rval = nullptr;   // [n_coarse x n] = P^T
   Csr Rc;                   // the same in CSR when its rows are long (coarse levels): applied one warp per row
+  Csr Ac;                   // small coarse levels with long rows: the operator in CSR, smoothed one warp per row
   double *x0 = nullptr, *x1 = nullptr, *b = nullptr, *r = nullptr, *d0 = nullptr, *d1 = nullptr;  // [ntot*C]
   int work_C = 0;
   // multi-GPU: forward halo of this level (level 0 borrows the mesh's), global numbering
@@ -254,8 +261,10 @@ struct mv_mesh {
   std::vector<mv::Amg*> amg;   // cached hierarchies (one per operator / constrained set)
 };
 
+namespace mv { struct EqBC; }
 struct mv_ma {
   mv_mesh* mesh = nullptr;
+  mv::EqBC* eqbc = nullptr;     // non-axis-aligned free boundary segments (mv_eqbc.cu)
   double* f[MV_F_COUNT] = {nullptr};
   uint16_t* bc_mask = nullptr;  // [V]
   bool have_bc = false;
@@ -287,6 +296,13 @@ namespace mv {
 // device scalar slots of mv_ma::dscal (mv_ma.cu, mv_qn.cu)
 enum { D_MONMAX = 0, D_SUMA = 1, D_THETA = 2, D_RES2 = 3, D_VSUM = 4, D_VMAX = 5, D_VMIN = 6, D_VSSD = 7, D_N = 16 };
 
+// EquationBC branch of the L2 projector (mv_eqbc.cu)
+int eqbc_build(mv_ma* ma, const std::vector<int>& tagidx, const std::vector<char>& is_eq, const std::vector<int>& verts,
+               const std::vector<double>& area);
+int eqbc_apply(mv_ma* ma, const double* phi, double* grad_phi);
+void eqbc_free(mv_ma* ma);
+int64_t eqbc_counts(const mv_ma* ma, int64_t* nu);
+
 // PCG device scalar slots: scal[slot*16 + comp]
 enum { S_RZ = 0, S_PQ = 1, S_RZNEW = 2, S_BETA = 3, S_THR = 4, S_REF = 5, S_BB = 6, S_SUM = 7, S_NSLOTS = 8 };
 #define SC(slot, c) ((slot) * 16 + (c))
@@ -315,6 +331,7 @@ int soa_to_aos(int C, int64_t n, const double* src, int64_t ld, double* dst);
 int ensure_slice_schedule(mv_mesh* m);
 // fused Chebyshev iteration for the consistent mass matrix (mv_cheb.cu)
 extern int g_mass_solver;
+extern int g_mass_mixed;
 int cheb_mass_solve(mv_mesh* m, int ncomp, const double* val, const double* dinv, const double* rhs, double* x,
                     const uint16_t* mask, double rtol, double atol, int maxit, int* iters, double* relres);
 int halo_exchange_soa(const Halo& h, int64_t nown, int C, double* vec, int64_t ld);
@@ -325,6 +342,8 @@ int p2p_init(int rank, int nranks, int (*allgather_bytes)(const void* sendbuf, v
 void p2p_finalize();
 size_t p2p_slot_bytes();
 int p2p_halo_exchange(const Halo& h, int64_t nown, int C, double* vec, int64_t ld, bool soa, const int* done);
+int p2p_halo_exchange_f32(const Halo& h, int64_t nown, int C, float* vec, int64_t ld, const int* done);
+int halo_exchange_soa_f32(const Halo& h, int64_t nown, int C, float* vec, int64_t ld);
 bool p2p_allreduce_fits(int n);
 int p2p_allreduce(double* d, int n, int op, const int* done);
 int p2p_check_status();

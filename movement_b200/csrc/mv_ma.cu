@@ -607,6 +607,7 @@ extern "C" void mv_ma_destroy(mv_ma* ma) {
   dev_free(ma->rhs); dev_free(ma->a); dev_free(ma->dphi); dev_free(ma->dscal); dev_free(ma->bc_mask);
   for (int i = 0; i < 2; ++i) { dev_free(ma->hist_x[i]); dev_free(ma->hist_b[i]); }
   if (ma->h_scal) cudaFreeHost(ma->h_scal);
+  eqbc_free(ma);
   delete ma;
 }
 
@@ -639,19 +640,30 @@ extern "C" int mv_ma_set_monitor(mv_ma* ma, int kind, int nparams, const double*
 }
 
 extern "C" int mv_ma_set_boundary(mv_ma* ma, int n_fixed, const int32_t* fixed_tags) {
-  if (!ma) return MV_ERR_BADARG;
+  return mv_ma_set_boundary_ex(ma, n_fixed, fixed_tags, 0, nullptr, nullptr);
+}
+
+extern "C" int mv_ma_set_boundary_ex(mv_ma* ma, int n_fixed, const int32_t* fixed_tags, int n_all, const int32_t* all_tags,
+                                     int32_t* kinds) {
+  if (!ma || (n_all > 0 && !all_tags)) return MV_ERR_BADARG;
   mv_mesh* m = ma->mesh;
   const int d = m->dim;
   const int64_t F = m->F;
   MV_CUDA(cudaMemsetAsync(ma->bc_mask, 0, (m->V + 2) * sizeof(uint16_t), g_stream));
   ma->have_bc = false;
-  if (F == 0) return MV_OK;
+  eqbc_free(ma);
+  if (F == 0 && n_all == 0) return MV_OK;
   std::vector<double> nrm(F * d), area(F);
-  MV_CUDA(cudaMemcpyAsync(nrm.data(), m->bf_normal, F * d * sizeof(double), cudaMemcpyDeviceToHost, g_stream));
-  MV_CUDA(cudaMemcpyAsync(area.data(), m->bf_area, F * sizeof(double), cudaMemcpyDeviceToHost, g_stream));
-  MV_CUDA(cudaStreamSynchronize(g_stream));
-  // unique tags
-  std::vector<int> tags(m->h_bf_tags);
+  if (F > 0) {
+    MV_CUDA(cudaMemcpyAsync(nrm.data(), m->bf_normal, F * d * sizeof(double), cudaMemcpyDeviceToHost, g_stream));
+    MV_CUDA(cudaMemcpyAsync(area.data(), m->bf_area, F * sizeof(double), cudaMemcpyDeviceToHost, g_stream));
+    MV_CUDA(cudaStreamSynchronize(g_stream));
+  }
+  // the tags the decision is taken over: the caller's list (every tag of the whole mesh, the same on every rank), else
+  // the tags of this rank's facets
+  std::vector<int> tags;
+  if (n_all > 0) tags.assign(all_tags, all_tags + n_all);
+  else tags = m->h_bf_tags;
   std::sort(tags.begin(), tags.end());
   tags.erase(std::unique(tags.begin(), tags.end()), tags.end());
   for (int i = 0; i < n_fixed; ++i)
@@ -663,25 +675,49 @@ extern "C" int mv_ma_set_boundary(mv_ma* ma, int n_fixed, const int32_t* fixed_t
   std::vector<double> absn(tags.size() * d, 0.0);
   for (int64_t f = 0; f < F; ++f) {
     const int k = (int)(std::lower_bound(tags.begin(), tags.end(), m->h_bf_tags[f]) - tags.begin());
+    if (k >= (int)tags.size() || tags[k] != m->h_bf_tags[f]) {
+      set_error("mv_ma_set_boundary_ex: facet tag %d is not in the list of all tags", m->h_bf_tags[f]);
+      return MV_ERR_BADARG;
+    }
     tagidx[f] = k;
     for (int a = 0; a < d; ++a) absn[k * d + a] += fabs(nrm[f * d + a]) * area[f];
   }
+  // assemble(abs(n_i) * ds(tag)) is a global integral: sum the ranks' parts, so that every rank takes the same branch
+  if (comm_active() && n_all > 0) MV_CHECK(allreduce_host(absn.data(), (int)absn.size(), 0));
   std::vector<unsigned> bits(tags.size(), 0u);
+  std::vector<char> is_eq(tags.size(), 0);
   const unsigned all = (1u << d) - 1u;
+  bool any_eq = false;
   for (size_t k = 0; k < tags.size(); ++k) {
     bool fixed = false;
     for (int i = 0; i < n_fixed; ++i) fixed |= (fixed_tags[i] == tags[k]);
+    if (kinds) kinds[k] = 0;
     if (fixed || d == 1) { bits[k] = all; continue; }   // any tag in 1D: the whole vector is fixed (monge_ampere.py:258-260)
     int nzero = 0, idx = -1;
     for (int a = 0; a < d; ++a) {
-      if (fabs(absn[k * d + a]) <= 1e-8) ++nzero; else idx = a;   // np.isclose(., 0.0)
+      if (fabs(absn[k * d + a]) <= 1e-8) ++nzero; else idx = a;   // np.isclose(., 0.0); NaN (degenerate facets) is not close
     }
     if (nzero == d - 1) {
       bits[k] = 1u << idx;
+      if (kinds) kinds[k] = 1 + idx;
     } else {
-      set_error("boundary segment '%d' is not axis-aligned: EquationBC branch (monge_ampere.py:274-309) not built", tags[k]);
-      return MV_ERR_UNSUPPORTED;
+      // EquationBC branch (monge_ampere.py:274-309): every component at the segment's nodes is prescribed by the boundary solve
+      bits[k] = all;
+      is_eq[k] = 1;
+      any_eq = true;
+      if (kinds) kinds[k] = -1;
     }
+  }
+  if (any_eq && comm_active()) {   // the same verdict on every rank (absn was summed over the ranks)
+    set_error("non-axis-aligned free boundary segments (EquationBC branch) are not partitioned over several GPUs yet");
+    return MV_ERR_UNSUPPORTED;
+  }
+  if (F == 0) return MV_OK;
+  if (any_eq) {
+    std::vector<int> verts(F * d);
+    MV_CUDA(cudaMemcpyAsync(verts.data(), m->bf_verts, F * d * sizeof(int), cudaMemcpyDeviceToHost, g_stream));
+    MV_CUDA(cudaStreamSynchronize(g_stream));
+    MV_CHECK(eqbc_build(ma, tagidx, is_eq, verts, area));
   }
   int* d_tagidx = nullptr;
   unsigned* d_bits = nullptr;
@@ -775,6 +811,7 @@ extern "C" int mv_ma_l2_project(mv_ma* ma, int* iters) {
   mv_mesh* m = ma->mesh;
   if (comm_active()) MV_CHECK(halo_exchange(m, 1, ma->f[MV_F_PHI_OLD]));
   MV_CHECK(l2_rhs_dev(m, ma->f[MV_F_PHI_OLD], ma->rhs));
+  MV_CHECK(eqbc_apply(ma, ma->f[MV_F_PHI_OLD], ma->f[MV_F_GRAD_PHI]));   // EquationBC segments: boundary solve first, its values are data
   MV_CHECK(pcg_solve(m, MV_OP_MASS, m->dim, ma->rhs, ma->f[MV_F_GRAD_PHI], ma->have_bc ? ma->bc_mask : nullptr, ma->rtol,
                      ma->atol, ma->maxit_mass, 0, iters, nullptr));
   if (comm_active()) MV_CHECK(halo_exchange(m, m->dim, ma->f[MV_F_GRAD_PHI]));

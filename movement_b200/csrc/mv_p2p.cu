@@ -76,9 +76,9 @@ struct HaloArgs {
 };
 
 // vec: component-major [C][ld] (SOA) or interleaved [ld][C]; owned rows [0, nown), ghosts after.
-template <bool SOA>
+template <bool SOA, typename T>
 __global__ void __launch_bounds__(MV_BLOCK)
-k_p2p_halo(HaloArgs h, int me, int C, const int* __restrict__ send_idx, double* __restrict__ vec, int64_t ld, int64_t nown,
+k_p2p_halo(HaloArgs h, int me, int C, const int* __restrict__ send_idx, T* __restrict__ vec, int64_t ld, int64_t nown,
            unsigned char* __restrict__ mywin, P2PWindowLayout lay, unsigned long long* __restrict__ seq,
            unsigned* __restrict__ ticket, int* __restrict__ status, const int* __restrict__ done) {
   if (done && *done) return;
@@ -91,7 +91,7 @@ k_p2p_halo(HaloArgs h, int me, int C, const int* __restrict__ send_idx, double* 
   for (int k = 0; k < h.nn; ++k) {
     const int64_t ns = h.send_ptr[k + 1] - h.send_ptr[k];
     const int* idx = send_idx + h.send_ptr[k];
-    double* dst = reinterpret_cast<double*>(h.peer_win[k] + lay.off_slots + ((size_t)me * 2 + (s_seq[k] & 1ull)) * lay.slot_bytes);
+    T* dst = reinterpret_cast<T*>(h.peer_win[k] + lay.off_slots + ((size_t)me * 2 + (s_seq[k] & 1ull)) * lay.slot_bytes);
     const int64_t tot = ns * C;
     for (int64_t i = tid; i < tot; i += nth) {
       const int64_t c = i / ns, t = i - c * ns;
@@ -124,11 +124,11 @@ k_p2p_halo(HaloArgs h, int me, int C, const int* __restrict__ send_idx, double* 
       if (threadIdx.x == 0) *status = 1;
       return;
     }
-    const double* src = reinterpret_cast<const double*>(mywin + lay.off_slots + ((size_t)h.ranks[k] * 2 + (s_seq[k] & 1ull)) * lay.slot_bytes);
+    const T* src = reinterpret_cast<const T*>(mywin + lay.off_slots + ((size_t)h.ranks[k] * 2 + (s_seq[k] & 1ull)) * lay.slot_bytes);
     const int64_t tot = nr * C, g0 = nown + h.recv_ptr[k];
     for (int64_t i = tid; i < tot; i += nth) {
       const int64_t c = i / nr, t = i - c * nr;
-      const double val = __ldcv(&src[i]);      // written by the peer: never from a stale cache line
+      const T val = __ldcv(&src[i]);      // written by the peer: never from a stale cache line
       if (SOA) vec[c * ld + g0 + t] = val;
       else vec[(g0 + t) * C + c] = val;
     }
@@ -270,7 +270,8 @@ void p2p_finalize() {
 
 size_t p2p_slot_bytes() { return g_p2p.on ? g_p2p.lay.slot_bytes : 0; }
 
-int p2p_halo_exchange(const Halo& h, int64_t nown, int C, double* vec, int64_t ld, bool soa, const int* done) {
+template <typename T>
+static int p2p_halo_exchange_t(const Halo& h, int64_t nown, int C, T* vec, int64_t ld, bool soa, const int* done) {
   P2P& p = g_p2p;
   HaloArgs a;
   a.nn = h.nn;
@@ -288,12 +289,19 @@ int p2p_halo_exchange(const Halo& h, int64_t nown, int C, double* vec, int64_t l
   if (grid > cap) grid = cap;
   if (grid < 1) grid = 1;
   if (soa)
-    MV_L k_p2p_halo<true><<<grid, MV_BLOCK, 0, g_stream>>>(a, p.rank, C, h.send_idx, vec, ld, nown, p.win, p.lay, p.seq, p.ticket, p.status, done);
+    MV_L k_p2p_halo<true, T><<<grid, MV_BLOCK, 0, g_stream>>>(a, p.rank, C, h.send_idx, vec, ld, nown, p.win, p.lay, p.seq, p.ticket, p.status, done);
   else
-    MV_L k_p2p_halo<false><<<grid, MV_BLOCK, 0, g_stream>>>(a, p.rank, C, h.send_idx, vec, ld, nown, p.win, p.lay, p.seq, p.ticket, p.status, done);
+    MV_L k_p2p_halo<false, T><<<grid, MV_BLOCK, 0, g_stream>>>(a, p.rank, C, h.send_idx, vec, ld, nown, p.win, p.lay, p.seq, p.ticket, p.status, done);
   MV_KERNEL_CHECK();
   ++p.n_halo;
   return MV_OK;
+}
+
+int p2p_halo_exchange(const Halo& h, int64_t nown, int C, double* vec, int64_t ld, bool soa, const int* done) {
+  return p2p_halo_exchange_t<double>(h, nown, C, vec, ld, soa, done);
+}
+int p2p_halo_exchange_f32(const Halo& h, int64_t nown, int C, float* vec, int64_t ld, const int* done) {
+  return p2p_halo_exchange_t<float>(h, nown, C, vec, ld, true, done);
 }
 
 int p2p_allreduce(double* d, int n, int op, const int* done) {

@@ -208,6 +208,20 @@ class DirichletBC:
         return torch.from_numpy(a.copy()).to(dev)
 
 
+class EquationBC:
+    """Descriptor of one of the two ``firedrake.EquationBC``s the reference puts on a straight, non-axis-aligned, free
+    boundary segment (movement/monge_ampere.py:274-309): ``part`` is "normal" (bc1) or "tangential" (bc2).  The
+    condition itself is imposed by the library (csrc/mv_eqbc.cu)."""
+
+    def __init__(self, space, sub_domain, part):
+        self._space = space
+        self.sub_domain = (sub_domain,)
+        self.part = part
+
+    def function_space(self):
+        return self._space
+
+
 class Mesh:
     """P1 simplex mesh: device-resident coordinates + host topology.
 

@@ -17,7 +17,7 @@ import numpy as np
 import torch
 
 from . import _lib as L
-from .mesh import DirichletBC, Function
+from .mesh import DirichletBC, EquationBC, Function
 from .monitor import BuiltinMonitor
 from .mover import PrimeMover, _print
 
@@ -117,18 +117,27 @@ class MongeAmpereMover_Base(PrimeMover, metaclass=abc.ABCMeta):
             from . import parallel
 
             self.total_volume = parallel.allreduce_host(total[0], "sum")
-        # boundary conditions of the L2 projector (monge_ampere.py:246-272, axis-aligned branch)
+        # boundary conditions of the L2 projector (monge_ampere.py:246-309), decided per tag over the WHOLE mesh: the
+        # library sums assemble(abs(n_i) * ds(tag)) over the ranks, so every rank takes the same branch for a tag
         tags = np.ascontiguousarray(list(self.fixed_boundary_segments), dtype=np.int32)
-        local = set(self.mesh.exterior_facets.unique_markers)
-        ltags = np.ascontiguousarray([t for t in tags if t in local], dtype=np.int32)
+        all_tags = np.ascontiguousarray(sorted(set(int(t) for t in self._all_boundary_segments)), dtype=np.int32)
+        kinds = np.zeros(max(len(all_tags), 1), dtype=np.int32)
         try:
-            L.check(lib.mv_ma_set_boundary(h, len(ltags), L.ptr(ltags) if len(ltags) else None))
+            L.check(lib.mv_ma_set_boundary_ex(h, len(tags), L.ptr(tags) if len(tags) else None, len(all_tags),
+                                              L.ptr(all_tags) if len(all_tags) else None, L.ptr(kinds)))
         except L.MovementB200Error as e:
             if e.status == L.MV_ERR_UNSUPPORTED:
                 raise NotImplementedError(
-                    "Non-axis-aligned boundary segments (the EquationBC branch of "
-                    "movement/monge_ampere.py:274-309) are not on the accelerated path yet.") from e
+                    "Non-axis-aligned boundary segments (the EquationBC branch of movement/monge_ampere.py:274-309) "
+                    "are not partitioned over several GPUs yet.") from e
             raise
+        self._bc_kinds = {int(t): int(k) for t, k in zip(all_tags, kinds)}
+        # straight-line / plane check of the EquationBC segments (monge_ampere.py:288-299); like the reference's lazily
+        # built projector, the error surfaces in move()
+        self._bc_error = None
+        for t in all_tags:
+            if self._bc_kinds[int(t)] == -1 and self._bc_error is None:
+                self._bc_error = self._check_hyperplane(int(t))
         mask = np.empty(self._dm.Vown, dtype=np.uint16)
         L.check(lib.mv_ma_get_bcmask(h, L.ptr(mask)))
         self._bc_mask = mask
@@ -145,11 +154,45 @@ class MongeAmpereMover_Base(PrimeMover, metaclass=abc.ABCMeta):
         self.inner_maxit_poisson = self.inner_maxit_poisson if maxit_poisson is None else int(maxit_poisson)
         L.check(L.load().mv_ma_set_solver(self._ma, self.inner_rtol, 1e-300, self.inner_maxit_mass, self.inner_maxit_poisson))
 
+    def _check_hyperplane(self, tag):
+        """movement/monge_ampere.py:288-299 with movement/math.py:7-42: the hyperplane through the nodes the segment
+        shares with other segments must contain every node of the segment (np.isclose).  The reference picks the d
+        defining points at random; here: the first, the one farthest from it, the one farthest from their line.
+        Returns the exception the reference would raise, or None."""
+        mesh, d = self.mesh, self.dim
+        name = {2: "line", 3: "plane"}[d]
+        nodes = np.unique(mesh.bfacets[mesh.btags == tag])
+        corners = np.intersect1d(nodes, np.unique(mesh.bfacets[mesh.btags != tag]))
+        xyz = np.asarray(mesh.coordinates.dat.data_ro)
+        pts = xyz[corners]
+        assert len(pts) >= d
+        p0 = pts[0]
+        dist0 = np.linalg.norm(pts - p0, axis=1)
+        if not dist0.max() > 0:
+            return ValueError(f"Could not determine a {name} for the provided points.")
+        p1 = pts[int(np.argmax(dist0))]
+        if d == 2:
+            e = (p1 - p0) / np.linalg.norm(p1 - p0)
+            x = xyz[nodes] - p0
+            dist = np.abs(x[:, 0] * e[1] - x[:, 1] * e[0])
+        else:
+            cr = np.cross(p1 - p0, pts - p0)
+            k = int(np.argmax(np.linalg.norm(cr, axis=1)))
+            if not np.linalg.norm(cr[k]) > 1e-14 * dist0.max() ** 2:
+                return ValueError(f"Could not determine a {name} for the provided points.")
+            dist = np.abs((xyz[nodes] - p0) @ (cr[k] / np.linalg.norm(cr[k])))
+        if not np.all(np.isclose(dist, 0)):
+            return ValueError(f"Boundary segment '{tag}' is not {'linear' if d == 2 else 'planar'}.")
+        return None
+
     def _describe_bcs(self):
-        """One descriptor per (boundary tag, constrained component set), like the DirichletBC list
-        the reference builds at monge_ampere.py:331-335."""
+        """One descriptor per boundary condition, like the list the reference builds at monge_ampere.py:331-335:
+        a DirichletBC per fixed or axis-aligned segment, two EquationBCs per other segment (:274-309)."""
         bcs = []
         for tag in self._all_boundary_segments:
+            if self._bc_kinds.get(int(tag), 0) == -1:
+                bcs.extend([EquationBC(self.P1_vec, tag, "normal"), EquationBC(self.P1_vec, tag, "tangential")])
+                continue
             sel = self.mesh.btags == tag
             nodes = np.unique(self.mesh.bfacets[sel])
             nodes = nodes[nodes < self._dm.Vown]
@@ -212,6 +255,8 @@ class MongeAmpereMover_Base(PrimeMover, metaclass=abc.ABCMeta):
     # ---- pieces of the iteration ---------------------------------------------------------------
     def _begin(self):
         """Entry of move(): computational coordinates, host edits flushed, monitor mode resolved."""
+        if self._bc_error is not None:
+            raise self._bc_error
         self.to_computational_coordinates()
         self._sync()
         self._fused = self._resolve_monitor()

@@ -464,18 +464,29 @@ class MAOperators:
             if t not in tags:
                 raise ValueError(f"Provided boundary_tag '{t}' is invalid.")
         mask = np.zeros((V, d), dtype=bool)  # True = constrained dof
+        self.eq_tags = []                     # non-axis-aligned free segments: EquationBC branch (monge_ampere.py:274-309)
+        self.bc_kinds = []                    # per tag, in tag order: "dirichlet" | "component" | "equation"
         for t in tags:
             sel = mesh.btags == t
             nodes = np.unique(mesh.bfacets[sel])
             if t in fixed_boundary_segments or d == 1:
                 mask[nodes, :] = True
+                self.bc_kinds.append("dirichlet")
                 continue
-            absn = (np.abs(self.fnormal[sel]) * self.farea[sel, None]).sum(axis=0)
+            with np.errstate(invalid="ignore"):
+                absn = (np.abs(self.fnormal[sel]) * self.farea[sel, None]).sum(axis=0)
             iszero = np.isclose(absn, 0.0)
-            if iszero.sum() != d - 1:
-                raise NotImplementedError("non-axis-aligned boundary segment (EquationBC branch)")
-            mask[nodes, int(np.where(~iszero)[0][0])] = True
+            assert iszero.sum() < d
+            if iszero.sum() == d - 1:
+                mask[nodes, int(np.where(~iszero)[0][0])] = True
+                self.bc_kinds.append("component")
+                continue
+            self.eq_tags.append(t)
+            self.bc_kinds.append("equation")
+            mask[nodes, :] = True             # every component of these nodes is prescribed by the boundary solve
         self.bc_mask = mask
+        self.bc_error = None
+        self._eq = [self._equation_bc(t) for t in self.eq_tags]
         self._Mlu = None
         self._Mbc_lu = {}
         self._Klu = None
@@ -529,6 +540,88 @@ class MAOperators:
                 raise RuntimeError(f"oracle cg: true residual stagnated at {tn / bn:.2e}")
             X[:, c] = x
         return X.reshape(b.shape)
+
+    # -- EquationBC branch of the L2 projector (movement/monge_ampere.py:274-309) -----------------------------------
+    def _equation_bc(self, tag):
+        """Structures of one straight / planar, non-axis-aligned, free boundary segment.
+
+        The reference imposes two EquationBCs on the segment's rows: int (v.n)(u.n) ds = 0 (bc1) and
+        int v_t . u_t ds = int v_t . grad(phi_old)_t ds with the nodes shared with any other segment pinned to zero
+        (bc2, its nested DirichletBC `ffacet_bc`).  Both are assembled into the same rows (Firedrake adds the forms
+        of successive EquationBCs), and n n^T + (I - n n^T) = I, so the rows read int v . u ds = int v . P_t grad(phi_old) ds:
+        the boundary-mass (L2(Gamma)) projection of the tangential gradient.  Its unique solution has u = 0 at the
+        shared ('corner') nodes and u.n = 0 everywhere on the segment; the interior rows then see these values as
+        inhomogeneous Dirichlet data.  Also performs the reference's straight-line / plane check (:288-299), whose
+        error is raised at the first projection like the reference's lazily built solver does."""
+        mesh, d = self.mesh, self.dim
+        sel = np.where(mesh.btags == tag)[0]
+        nodes = np.unique(mesh.bfacets[sel])
+        others = np.unique(mesh.bfacets[mesh.btags != tag])
+        corners = np.intersect1d(nodes, others)
+        # hyperplane through the corner nodes (math.py:7-42; a deterministic choice of the d points)
+        name = {2: "line", 3: "plane"}[d]
+        pts = mesh.coords[corners]
+        assert len(pts) >= d
+        p0 = pts[0]
+        dist0 = np.linalg.norm(pts - p0, axis=1)
+        p1 = pts[int(np.argmax(dist0))]
+        err = None
+        if not dist0.max() > 0:
+            err = ValueError(f"Could not determine a {name} for the provided points.")
+        elif d == 2:
+            e = (p1 - p0) / np.linalg.norm(p1 - p0)
+            x = mesh.coords[nodes] - p0
+            dist = np.abs(x[:, 0] * e[1] - x[:, 1] * e[0])
+        else:
+            cr = np.cross(p1 - p0, pts - p0)
+            k = int(np.argmax(np.linalg.norm(cr, axis=1)))
+            if not np.linalg.norm(cr[k]) > 1e-14 * dist0.max() ** 2:
+                err = ValueError(f"Could not determine a {name} for the provided points.")
+            else:
+                nrm = cr[k] / np.linalg.norm(cr[k])
+                dist = np.abs((mesh.coords[nodes] - p0) @ nrm)
+        if err is None and not np.all(np.isclose(dist, 0)):
+            err = ValueError(f"Boundary segment '{tag}' is not {'linear' if d == 2 else 'planar'}.")
+        if err is not None and self.bc_error is None:
+            self.bc_error = err
+        unknown = np.setdiff1d(nodes, corners)
+        loc = -np.ones(self.V, dtype=np.int64)
+        loc[unknown] = np.arange(len(unknown))
+        # boundary mass matrix of the segment over the unknown nodes: facet matrix area / (d (d+1)) (1 + delta_ab)
+        fv = mesh.bfacets[sel]
+        a = self.farea[sel] / (d * (d + 1))
+        rows, cols, vals = [], [], []
+        for i in range(d):
+            for j in range(d):
+                ok = (loc[fv[:, i]] >= 0) & (loc[fv[:, j]] >= 0)
+                rows.append(loc[fv[ok, i]]); cols.append(loc[fv[ok, j]]); vals.append(a[ok] * (2.0 if i == j else 1.0))
+        nu = len(unknown)
+        Mb = sp.csr_matrix((np.concatenate(vals), (np.concatenate(rows), np.concatenate(cols))), shape=(nu, nu))
+        return dict(tag=tag, facets=sel, nodes=nodes, corners=corners, unknown=unknown, loc=loc,
+                    lu=spla.splu(Mb.tocsc()) if nu else None)
+
+    def equation_bc_values(self, phi):
+        """[V,d] values of grad(phi) at the nodes of the EquationBC segments (zero elsewhere)."""
+        d = self.dim
+        g = np.zeros((self.V, d))
+        if not self._eq:
+            return g
+        gK = np.einsum("cj,cja->ca", phi[self.cells], self.grads)
+        for eq in self._eq:
+            sel = eq["facets"]
+            n = self.fnormal[sel]
+            gf = gK[self.fcell[sel]]
+            gt = gf - n * np.einsum("fa,fa->f", n, gf)[:, None]            # tangential(grad phi, n), per facet
+            contrib = (self.farea[sel] / d)[:, None] * gt                  # int_f psi_i ds = area / d
+            rhs = np.zeros((len(eq["unknown"]), d))
+            fv = self.mesh.bfacets[sel]
+            for i in range(d):
+                li = eq["loc"][fv[:, i]]
+                ok = li >= 0
+                np.add.at(rhs, li[ok], contrib[ok])
+            if len(eq["unknown"]):
+                g[eq["unknown"]] = eq["lu"].solve(rhs)
+        return g
 
     def solve_mass(self, rhs):
         if self.solver == "cg":
@@ -591,6 +684,58 @@ class MAOperators:
             xprev, x = x, xnew
         raise RuntimeError(f"chebyshev: not converged in {maxit} iterations")
 
+    def solve_mass_chebyshev_mixed(self, rhs, x0=None, fixed=None, rtol=1e-12, atol=1e-50, maxit=500, sweep=16):
+        """CPU restatement of the GPU path's default mass solver (movement_b200/csrc/mv_cheb.cu, cheb_mixed): the same
+        Chebyshev polynomial as `solve_mass_chebyshev` used as the inner solver of an iterative refinement.  A
+        residual pass in double (r = b - M x, the stopping test of `solve_mass_chebyshev` on r.D^-1 r) is followed by
+        a sweep of k Chebyshev iterations on the correction M d = r, d_0 = 0, carried out in single precision
+        (float32 copies of M, D^-1, r and the iterates), and x += d_k in double; k = clamp(ceil(log(need / 4) /
+        log(fac)), 2, sweep) with need = min_c sqrt(thr_c / rz_c) and fac = (sqrt(kappa) - 1) / (sqrt(kappa) + 1).
+        Same linear systems as movement/monge_ampere.py:340,483 (KSP `cg`, movement/solver_parameters.py:62-66), so
+        results agree with `solve_mass` to the tolerance.  Returns (x, iterations = single-precision iterations +
+        residual passes after the first, residual passes)."""
+        b = np.asarray(rhs, dtype=float)
+        one = b.ndim == 1
+        b = b.reshape(self.V, -1)
+        x = np.zeros_like(b) if x0 is None else np.array(x0, dtype=float).reshape(self.V, -1)
+        fix = np.zeros(b.shape, bool) if fixed is None else np.asarray(fixed, bool).reshape(self.V, -1)
+        dinv = 1.0 / self.M.diagonal()
+        M32 = self.M.astype(np.float32)
+        dinv32 = dinv.astype(np.float32)[:, None]
+        lmin, lmax = 0.5, 1.0 + 0.5 * self.dim
+        theta, delta = 0.5 * (lmax + lmin), 0.5 * (lmax - lmin)
+        sigma1 = theta / delta
+        fac = (np.sqrt(lmax / lmin) - 1.0) / (np.sqrt(lmax / lmin) + 1.0)
+        its, passes, thr = 0, 0, None
+        while True:
+            r = np.where(fix, 0.0, b - self.M @ x)
+            z = dinv[:, None] * r
+            rz = (r * z).sum(axis=0)
+            passes += 1
+            if thr is None:
+                bb = np.where(fix, 0.0, b * dinv[:, None] * b).sum(axis=0)
+                thr = np.maximum(rtol ** 2 * np.maximum(rz, bb), atol ** 2)
+            if np.all(rz <= thr):
+                return (x[:, 0] if one else x), its + passes - 1, passes
+            if its + passes - 1 >= maxit:
+                raise RuntimeError(f"chebyshev: not converged in {maxit} iterations")
+            live = (rz > thr) & (rz > 0)
+            need = min(1.0, float(np.sqrt(thr[live] / rz[live]).min()))
+            k = int(min(max(np.ceil(np.log(0.25 * need) / np.log(fac)), 2), max(sweep, 2)))
+            r32 = r.astype(np.float32)
+            d = (z / theta).astype(np.float32)           # d_1, computed in double by the residual pass
+            dprev = np.zeros_like(d)
+            rho = 1.0 / sigma1
+            for _ in range(1, k):
+                rk = 1.0 / (2.0 * sigma1 - rho)
+                ak, ck = np.float32(rk * rho), np.float32(2.0 * rk / delta)
+                rho = rk
+                res = np.where(fix, np.float32(0), r32 - M32 @ d)
+                dn = np.where(fix, np.float32(0), d + ak * (d - dprev) + ck * (dinv32 * res)).astype(np.float32)
+                dprev, d = d, dn
+            x = x + d.astype(float)
+            its += k
+
     def solve_poisson_nullspace(self, rhs):
         """K u = rhs with constant nullspace: rhs and u projected to zero mean."""
         V = self.V
@@ -613,8 +758,16 @@ class MAOperators:
         return b
 
     def l2_project_grad(self, phi):
+        if self.bc_error is not None:
+            raise self.bc_error
         b = self.l2_rhs(phi)
-        return np.stack([self.solve_mass_bc(b[:, a], a) for a in range(self.dim)], axis=1)
+        if not self._eq:
+            return np.stack([self.solve_mass_bc(b[:, a], a) for a in range(self.dim)], axis=1)
+        # EquationBC segments: their nodes carry the boundary solve's values, the remaining rows see them as data
+        gB = self.equation_bc_values(phi)
+        b = b - self.M @ gB
+        g = np.stack([self.solve_mass_bc(b[:, a], a) for a in range(self.dim)], axis=1)
+        return g + gB
 
     # -- A5: theta and residual  (movement/monge_ampere.py:405-410,514,517,212-223) --
     def assemble_a(self, m, H):

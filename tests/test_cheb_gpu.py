@@ -49,14 +49,14 @@ def test_chebyshev_matches_exact_solve_and_pcg(dim, n, ncomp, solver):
     bt = torch.as_tensor(b).cuda()
     ref = ops.solve_mass(b)
     out = {}
-    for kind in (L.MV_MASS_CHEBYSHEV, L.MV_MASS_PCG):
+    for kind in (L.MV_MASS_CHEBYSHEV, L.MV_MASS_CHEBYSHEV_FP64, L.MV_MASS_PCG):
         solver(kind)
         x = dm.zeros(V, ncomp) if ncomp > 1 else dm.zeros(V)
         it, rel = dm.pcg(L.MV_OP_MASS, bt if ncomp > 1 else bt[:, 0].contiguous(), x, rtol=1e-12)
         out[kind] = (it, x.cpu().numpy().reshape(V, ncomp))
         assert rel.max() <= 1e-12
         assert np.abs(out[kind][1] - ref).max() < 1e-10 * np.abs(ref).max()
-    it_c, it_p = out[L.MV_MASS_CHEBYSHEV][0], out[L.MV_MASS_PCG][0]
+    it_c, it_p = out[L.MV_MASS_CHEBYSHEV_FP64][0], out[L.MV_MASS_PCG][0]
     # a-priori bound: 2 rho^k <= 1e-12 with rho = (sqrt(kappa)-1)/(sqrt(kappa)+1), kappa = 2 + d
     kappa = 2.0 + dim
     rho = (np.sqrt(kappa) - 1) / (np.sqrt(kappa) + 1)
@@ -65,8 +65,14 @@ def test_chebyshev_matches_exact_solve_and_pcg(dim, n, ncomp, solver):
     # the oracle's restatement of the same iteration (same interval, same check schedule): same count
     x_o, it_o = ops.solve_mass_chebyshev(b, rtol=1e-12)
     assert abs(it_c - it_o) <= 1
-    assert np.abs(out[L.MV_MASS_CHEBYSHEV][1] - x_o.reshape(V, ncomp)).max() < 1e-10 * np.abs(ref).max()
+    assert np.abs(out[L.MV_MASS_CHEBYSHEV_FP64][1] - x_o.reshape(V, ncomp)).max() < 1e-10 * np.abs(ref).max()
     assert np.abs(out[L.MV_MASS_CHEBYSHEV][1] - out[L.MV_MASS_PCG][1]).max() < 1e-10 * np.abs(ref).max()
+    # the default solver: the same polynomial as single-precision sweeps between double-precision residual passes;
+    # the oracle's restatement takes the same sweeps (3 residual passes from a cold start: two sweeps to 1e-12)
+    x_m, it_m, passes = ops.solve_mass_chebyshev_mixed(b, rtol=1e-12)
+    assert abs(out[L.MV_MASS_CHEBYSHEV][0] - it_m) <= 1 and passes == 3
+    assert out[L.MV_MASS_CHEBYSHEV][0] <= it_c + 5
+    assert np.abs(out[L.MV_MASS_CHEBYSHEV][1] - x_m.reshape(V, ncomp)).max() < 1e-10 * np.abs(ref).max()
 
 
 @pytest.mark.parametrize("dim,n", [(2, 16), (3, 6)])

@@ -371,3 +371,76 @@ def test_interval_relaxation_constant_and_ring():
     assert o.ops.bc_mask[[0, 10]].all() and not o.ops.bc_mask[1:10].any()
     assert np.abs(o.x[[0, 10]] - mesh.coords[[0, 10]]).max() == 0.0
     assert np.abs(o.x - mesh.coords).max() > 1e-3
+
+
+# ---- EquationBC branch of the L2 projector (movement/monge_ampere.py:274-309) --------------------------------
+# The reference cannot run here and holds no golden trace for rotated domains; the oracle is checked against the
+# properties the reference's own test asserts (test/test_monge_ampere.py:357-437) and against the algebra of the
+# two boundary equations (normal component zero, corners pinned, boundary-mass projection of the tangential gradient).
+def _rotated_unit_domain(dim, n):
+    cs = sn = np.cos(np.pi / 4)
+    R = np.array([[cs, sn], [-sn, cs]]) if dim == 2 else np.array([[cs, sn, 0.0], [-sn, cs, 0.0], [0.0, 0.0, 1.0]])
+    base = mo.unit_square_mesh(n) if dim == 2 else mo.unit_cube_mesh(n)
+    return mo.OMesh(base.coords @ R.T, base.cells, base.bfacets, base.btags), R
+
+
+@pytest.mark.parametrize("dim,n", [(2, 8), (3, 4)])
+def test_equation_bc_rows_of_the_projection(dim, n):
+    mesh, _ = _rotated_unit_domain(dim, n)
+    ops = mo.MAOperators(mesh, (1,))
+    assert ops.bc_kinds[:4] == ["dirichlet", "equation", "equation", "equation"]
+    phi = np.random.default_rng(0).standard_normal(mesh.num_vertices)
+    g = ops.l2_project_grad(phi)
+    b = ops.l2_rhs(phi)
+    boundary = np.unique(mesh.bfacets)
+    interior = np.setdiff1d(np.arange(mesh.num_vertices), boundary)
+    # rows of the vertices without any condition: the plain projection equations, boundary values as data
+    assert np.abs((ops.M @ g - b)[interior]).max() < 1e-12
+    gK = np.einsum("cj,cja->ca", phi[ops.cells], ops.grads)
+    for eq in ops._eq:
+        sel = eq["facets"]
+        nrm = ops.fnormal[sel][0]
+        assert np.abs(g[eq["nodes"]] @ nrm).max() < 1e-13            # bc1: no movement normal to the segment
+        assert np.all(g[eq["corners"]] == 0.0)                       # ffacet_bc
+        # bc2, tested with the hat function of every unknown node: int psi_i u_t ds = int psi_i grad(phi)_t ds
+        d = dim
+        lhs = np.zeros((mesh.num_vertices, d))
+        rhs = np.zeros((mesh.num_vertices, d))
+        fv = mesh.bfacets[sel]
+        gt = gK[ops.fcell[sel]]
+        gt = gt - nrm * (gt @ nrm)[:, None]
+        for i in range(d):
+            for j in range(d):
+                np.add.at(lhs, fv[:, i], (ops.farea[sel] / (d * (d + 1)) * (2.0 if i == j else 1.0))[:, None] * g[fv[:, j]])
+            np.add.at(rhs, fv[:, i], (ops.farea[sel] / d)[:, None] * gt)
+        assert np.abs((lhs - rhs)[eq["unknown"]]).max() < 1e-13
+
+
+@pytest.mark.parametrize("dim,n,fixed", [(2, 10, ()), (2, 10, (1,)), (3, 5, ())])
+def test_equation_bc_boundary_and_volume_preservation(dim, n, fixed):
+    mesh, R = _rotated_unit_domain(dim, n)
+    orc = mo.OracleRelaxation(mesh, mo.monitor_test_ring, rtol=1e-3, fixed_boundary_segments=fixed)
+    orc.move()
+    before, after = mesh.coords @ R, orc.x @ R
+    for ax in range(dim):
+        for val in (0.0, 1.0):
+            on = np.isclose(before[:, ax], val)
+            assert np.allclose(after[on, ax], val, atol=1e-13)
+    vol, _ = mo.cell_geometry(orc.x, mesh.cells)
+    assert abs(vol.sum() - 1.0) < 1e-12 and vol.min() > 0
+    assert np.abs(orc.x - mesh.coords).max() > 1e-3
+    if fixed:
+        nodes = np.unique(mesh.bfacets[mesh.btags == 1])
+        assert np.all(orc.x[nodes] == mesh.coords[nodes])
+
+
+def test_equation_bc_non_straight_and_non_planar_segments():
+    for dim, n, name in ((2, 3, "linear"), (3, 3, "planar")):
+        mesh = mo.unit_square_mesh(n) if dim == 2 else mo.unit_cube_mesh(n)
+        target = np.array([0.0, 1.0 / 3.0, 1.0 / 3.0][:dim])
+        v = int(np.argmin(np.abs(mesh.coords - target).sum(axis=1)))
+        coords = mesh.coords.copy()
+        coords[v, 0] -= 0.25
+        orc = mo.OracleRelaxation(mo.OMesh(coords, mesh.cells, mesh.bfacets, mesh.btags), mo.monitor_test_ring)
+        with pytest.raises(ValueError, match=f"Boundary segment '1' is not {name}."):
+            orc.move()
