@@ -186,6 +186,16 @@ int mv_amg_info(mv_mesh* m, int op, int64_t* info, int max_levels, double* rho, 
 int mv_amg_level_get(mv_mesh* m, int op, int level, int which, int64_t* size, int64_t* slice_ptr,
                      int32_t* cols, double* vals, int32_t* row_nnz);
 
+/* ---- recovery operators of the solution-based monitors ---------------------------------------------------------
+ * replaces: animate.recovery as called from movement/monitor.py:232-240 and :286-293 (third-party, un-pinned; restated
+ * in oracle/movement_oracle.py).  Device pointers; the fields live on the mesh `m` was ingested with.
+ * mv_recover_gradient_l2: g [V,d] = L2 projection of grad(u), u [V] in P1 (consistent mass solve to rtol).
+ * mv_clement_gradient:    out [V,ncomp,d] = volume-weighted mean over the cells around each vertex of the cellwise
+ *                         gradient of u [V,ncomp]; ncomp = 1 (gradient) or d (Hessian of a recovered gradient).
+ * Ghost entries of u are refreshed first on a partitioned mesh (hence non-const).                                 */
+int mv_recover_gradient_l2(mv_mesh* m, double* u, double* g, double rtol, int maxit, int* iters);
+int mv_clement_gradient(mv_mesh* m, int ncomp, double* u, double* out);
+
 /* ---- Monge-Ampere pieces ---------------------------------------------------------- */
 int mv_ma_create(mv_mesh* m, mv_ma** out);
 void mv_ma_destroy(mv_ma* ma);

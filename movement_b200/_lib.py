@@ -54,6 +54,8 @@ SIGNATURES = {
     "mv_ma_create": (_i, [_vp, C.POINTER(_vp)]),
     "mv_ma_destroy": (None, [_vp]),
     "mv_ma_bind": (_i, [_vp, _i, _vp]),
+    "mv_recover_gradient_l2": (_i, [_vp, _vp, _vp, _d, _i, _vp]),
+    "mv_clement_gradient": (_i, [_vp, _i, _vp, _vp]),
     "mv_ma_set_boundary": (_i, [_vp, _i, _vp]),
     "mv_ma_set_boundary_ex": (_i, [_vp, _i, _vp, _i, _vp, _vp]),
     "mv_ma_get_bcmask": (_i, [_vp, _vp]),

@@ -907,11 +907,14 @@ int cheb_mass_solve(mv_mesh* m, int ncomp, const double* val, const double* dinv
       case 1: return cheb_mixed<1, 1, 8, 4, 0, 1, 8, 4, 0>(CHEB_ARGS);
       case 2: return cheb_mixed<2, 2, 8, 4, 0, 2, 8, 4, 0>(CHEB_ARGS);
       case 3:
-        if (var == 21) return cheb_mixed<3, 3, 8, 6, 0, 3, 8, 4, 0>(CHEB_ARGS);
+        if (var == 21) return cheb_mixed<3, 3, 8, 4, 0, 3, 8, 4, 0>(CHEB_ARGS);
         if (var == 22) return cheb_mixed<3, 3, 8, 6, 0, 3, 8, 3, 2>(CHEB_ARGS);
         if (var == 23) return cheb_mixed<3, 3, 8, 6, 0, 1, 4, 4, 2>(CHEB_ARGS);
         if (var == 24) return cheb_mixed<3, 3, 8, 6, 0, 1, 4, 4, 0>(CHEB_ARGS);
-        return cheb_mixed<3, 3, 8, 6, 0, 3, 8, 6, 0>(CHEB_ARGS);
+        if (var == 25) return cheb_mixed<3, 3, 8, 6, 0, 3, 8, 6, 0>(CHEB_ARGS);
+        // measured at 256^3, cold start to 1e-12 (33 matrix passes): iteration kernel <3,8,4> (64 registers, no spills)
+        // 19.6 ms per solve, <3,8,6> (40 registers) 23.9, TMA-staged <3,8,3> 21.2; all-double solver 30.1
+        return cheb_mixed<3, 3, 8, 6, 0, 3, 8, 4, 0>(CHEB_ARGS);
       case 4: return cheb_mixed<4, 4, 8, 4, 0, 4, 8, 4, 0>(CHEB_ARGS);
       case 9:
         if (var == 11) return cheb_mixed<9, 3, 4, 3, 2, 9, 8, 2, 0>(CHEB_ARGS);

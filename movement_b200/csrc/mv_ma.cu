@@ -876,6 +876,7 @@ extern "C" int mv_ma_diagnostics(mv_ma* ma, int use_H_old, double* out) {
   if (dist) MV_CHECK(allreduce_sum_dev(ma->dscal + D_RES2, 1));
   MV_CUDA(cudaMemcpyAsync(ma->h_scal, ma->dscal, D_N * sizeof(double), cudaMemcpyDeviceToHost, g_stream));
   MV_CUDA(cudaStreamSynchronize(g_stream));
+  if (comm_active()) MV_CHECK(p2p_check_status());   // once per relaxation iteration: a timed-out peer-memory wait is an error, not a wrong number
   const double* h = ma->h_scal;
   const double theta = h[D_THETA];
   const double mean = h[D_VSUM] / gcells;

@@ -266,6 +266,7 @@ extern "C" int mv_laplace_move(mv_mesh* m, double* v, const uint16_t* mask, doub
   double h = 0.0;
   MV_CUDA(cudaMemcpyAsync(&h, dout, sizeof(double), cudaMemcpyDeviceToHost, g_stream));
   MV_CUDA(cudaStreamSynchronize(g_stream));
+  if (comm_active()) MV_CHECK(p2p_check_status());
   if (displacement_norm) *displacement_norm = sqrt(h);
   return MV_OK;
 }
@@ -366,6 +367,7 @@ extern "C" int mv_spring_move(mv_mesh* m, double* coords, const double* forcing,
   double h = 0.0;
   MV_CUDA(cudaMemcpyAsync(&h, dout, sizeof(double), cudaMemcpyDeviceToHost, g_stream));
   MV_CUDA(cudaStreamSynchronize(g_stream));
+  if (comm_active()) MV_CHECK(p2p_check_status());
   if (displacement_norm) *displacement_norm = sqrt(h);
   return MV_OK;
 }

@@ -14,7 +14,7 @@ import abc
 from . import _lib as L
 
 __all__ = ["BuiltinMonitor", "MonitorBuilder", "ConstantMonitorBuilder", "BallMonitorBuilder", "RingMonitorBuilder",
-           "GradientMonitorBuilder", "HessianMonitorBuilder", "GradientHessianMonitorBuilder",
+           "SolutionBasedMonitorBuilder", "GradientMonitorBuilder", "HessianMonitorBuilder", "GradientHessianMonitorBuilder",
            "helmholtz_hessian_monitor", "sinatan3_hessian_monitor", "ring_test_monitor"]
 
 
@@ -88,29 +88,149 @@ class RingMonitorBuilder(BallMonitorBuilder):
         super().__init__(2, centre, radius, amplitude, width)
 
 
-class _SolutionBased(MonitorBuilder):
-    """movement/monitor.py:174-365 need ``animate``'s recovery operators and cross-mesh projection
-    (marked 'next'); not on the accelerated path yet."""
+class SolutionBasedMonitorBuilder(MonitorBuilder, metaclass=abc.ABCMeta):
+    """Abstract base class for monitor factories based on solution data (movement/monitor.py:174-201).
 
-    def __init__(self, *args, **kwargs):
-        raise NotImplementedError(
-            f"{type(self).__name__}: solution-based monitors are outside the accelerated path "
-            "(SURVEY 8f-3); pass a torch callable that returns nodal monitor values instead.")
+    The recovery operators run on the device (csrc/mv_recovery.cu) on the mesh the monitor is asked for.
+    ``projection`` is the identity when that mesh has the coordinates of the solution's mesh (the case of every test of
+    the reference, test/test_monitor.py); projecting between meshes with different coordinates is Firedrake's
+    supermesh projection, which this package does not have: NotImplementedError."""
 
-    def _monitor(self, mesh):  # pragma: no cover
-        raise NotImplementedError
+    recovery_rtol = 1.0e-12
+
+    @abc.abstractmethod
+    def __init__(self, dim, solution):
+        from .mesh import Function
+
+        super().__init__(dim)
+        assert isinstance(solution, Function)
+        self.solution = solution
+        self._dm = None
+        self._dm_key = None
+
+    def projection(self, mesh):
+        """movement/monitor.py:191-201."""
+        import torch
+
+        from .mesh import Function
+
+        src = self.solution.space.mesh
+        same = mesh is src or (mesh.cells is src.cells or (mesh.cells.shape == src.cells.shape and bool((mesh.cells == src.cells).all())))
+        if not same or not torch.equal(mesh.coordinates.tensor, src.coordinates.tensor):
+            raise NotImplementedError(
+                f"{type(self).__name__}.projection: the solution lives on a mesh with other coordinates; the reference "
+                "projects between the two meshes (Firedrake supermesh projection, movement/monitor.py:200-201), "
+                "which is not available here.  Re-evaluate the solution on the moved mesh in a torch callable instead.")
+        out = Function(mesh.function_space(self.solution.space.kind))
+        out.assign(self.solution)
+        return out
+
+    def _device_mesh(self, mesh):
+        """Operators of `mesh` at its current coordinates (ingested again only when the coordinates changed)."""
+        import torch
+
+        from .core import device_mesh_from
+
+        x = mesh.coordinates.tensor
+        key = (id(mesh), float(x.sum()), float((x * x).sum()))
+        if self._dm is None or key != self._dm_key:
+            self._dm, self._dm_key = device_mesh_from(mesh), key
+        return self._dm
+
+    def _normalised(self, sq):
+        """sq / norm(sq, "linf"), the l-infinity norm over every rank (adapt_common.norms.norm)."""
+        from . import parallel
+
+        mx = float(sq.abs().max())
+        if parallel.is_active():
+            mx = parallel.allreduce_host(mx, "max")
+        return sq / mx
 
 
-class GradientMonitorBuilder(_SolutionBased):
-    pass
+# TODO of the reference kept: gradient with the Clement interpolant is not offered there either
+class GradientMonitorBuilder(SolutionBasedMonitorBuilder):
+    r"""m = 1 + alpha grad(u).grad(u) / max grad(u).grad(u)  (movement/monitor.py:204-255)."""
+
+    def __init__(self, dim, solution, scale_factor):
+        super().__init__(dim, solution)
+        assert scale_factor > 0
+        self.gradient_scale_factor = float(scale_factor)
+
+    def recover_gradient(self, target_space):
+        """L2-projected gradient of the solution in vector P1 (movement/monitor.py:232-240)."""
+        import ctypes as C
+
+        from .core import use_current_stream
+        from .mesh import Function
+
+        mesh = target_space.mesh
+        u = self.projection(mesh)
+        dm = self._device_mesh(mesh)
+        g = Function(target_space)
+        it = C.c_int(0)
+        use_current_stream()
+        L.check(L.load().mv_recover_gradient_l2(dm.handle, L.ptr(u.tensor), L.ptr(g.tensor), self.recovery_rtol, 1000, C.byref(it)))
+        return g.written()
+
+    def _gradient_part(self, mesh):
+        g = self.recover_gradient(mesh.function_space("P1_vec")).tensor
+        return self.gradient_scale_factor * self._normalised((g * g).sum(dim=1))
+
+    def _monitor(self, mesh):
+        from .mesh import Function
+
+        return Function(mesh.function_space("P1")).assign(1.0 + self._gradient_part(mesh))
 
 
-class HessianMonitorBuilder(_SolutionBased):
-    pass
+# TODO of the reference kept: Hessian by double L2 projection is not offered there either
+class HessianMonitorBuilder(SolutionBasedMonitorBuilder):
+    r"""m = 1 + beta H(u):H(u) / max H(u):H(u)  (movement/monitor.py:258-308)."""
+
+    def __init__(self, dim, solution, scale_factor):
+        super().__init__(dim, solution)
+        assert scale_factor > 0
+        self.hessian_scale_factor = float(scale_factor)
+
+    def recover_hessian(self, target_space):
+        """Hessian by two Clement interpolations (movement/monitor.py:286-293; P1 solutions)."""
+        from .core import use_current_stream
+        from .mesh import Function
+
+        mesh = target_space.mesh
+        u = self.projection(mesh)
+        if u.space.kind != "P1":
+            raise NotImplementedError("recover_hessian: only P1 solutions (the reference projects P2 and higher first)")
+        dm = self._device_mesh(mesh)
+        g = Function(mesh.function_space("P1_vec"))
+        H = Function(target_space)
+        use_current_stream()
+        lib = L.load()
+        L.check(lib.mv_clement_gradient(dm.handle, 1, L.ptr(u.tensor), L.ptr(g.tensor)))
+        L.check(lib.mv_clement_gradient(dm.handle, mesh.geometric_dimension, L.ptr(g.tensor), L.ptr(H.tensor)))
+        return H.written()
+
+    def _hessian_part(self, mesh):
+        H = self.recover_hessian(mesh.function_space("P1_ten")).tensor
+        return self.hessian_scale_factor * self._normalised((H * H).sum(dim=(1, 2)))
+
+    def _monitor(self, mesh):
+        from .mesh import Function
+
+        return Function(mesh.function_space("P1")).assign(1.0 + self._hessian_part(mesh))
 
 
-class GradientHessianMonitorBuilder(_SolutionBased):
-    pass
+class GradientHessianMonitorBuilder(GradientMonitorBuilder, HessianMonitorBuilder):
+    r"""m = 1 + alpha gg / max gg + beta HH / max HH  (movement/monitor.py:311-365)."""
+
+    def __init__(self, dim, solution, gradient_scale_factor, hessian_scale_factor):
+        SolutionBasedMonitorBuilder.__init__(self, dim, solution)
+        self.gradient_scale_factor = float(gradient_scale_factor)
+        self.hessian_scale_factor = float(hessian_scale_factor)
+
+    def _monitor(self, mesh):
+        from .mesh import Function
+
+        return Function(mesh.function_space("P1")).assign(1.0 + self._gradient_part(mesh) + self._hessian_part(mesh))
 
 
 # ---- demo / test monitors as fused kernels ---------------------------------------------------

@@ -320,6 +320,67 @@ def boundary_facet_geometry(mesh: OMesh):
 # --------------------------------------------------------------------------------------
 
 
+# --------------------------------------------------------------------------------------
+# Solution-based monitors (movement/monitor.py:174-365)
+# --------------------------------------------------------------------------------------
+# The recovery operators come from `animate.recovery`, a third-party dependency that is neither vendored nor pinned by the
+# reference (pyproject: "animate" from git, no version) and is absent from /root/reference: PARITY UNPINNED for this
+# block.  Restated from its documented algorithm:
+#   recover_gradient_l2(f, target_space)  = firedrake.project(grad(f), P1_vec): consistent-mass L2 projection
+#   clement_interpolant(P0 field)         = at every vertex, the volume-weighted mean of the field over the cells that
+#                                           contain the vertex (no boundary treatment: boundary=False is the default)
+#   recover_hessian_clement(f), f in P1   = g = clement(grad f),  H = clement(grad g);  returns (g, H)
+# The known answers of test/test_monitor.py:64-152 that need no P2 space are reproduced by tests/test_oracle_golden.py.
+
+
+def recover_gradient_l2(mesh, u):
+    """L2 projection of grad(u), u in P1, into P1_vec (movement/monitor.py:232-240)."""
+    vol, grads = cell_geometry(mesh.coords, mesh.ccells)
+    V, d = mesh.num_vertices, mesh.dim
+    gK = np.einsum("cj,cja->ca", u[mesh.cells], grads)
+    b = np.zeros((V, d))
+    for loc in range(d + 1):
+        np.add.at(b, mesh.cells[:, loc], (vol / (d + 1))[:, None] * gK)
+    return spla.splu(assemble_mass(V, mesh.cells, vol).tocsc()).solve(b)
+
+
+def clement_gradient(mesh, u):
+    """Clement interpolant of the cellwise gradient of the P1 field(s) u [V] or [V,c]: out[v, (c,) a] = volume-weighted
+    mean over the cells around v of d_a u_c."""
+    vol, grads = cell_geometry(mesh.coords, mesh.ccells)
+    V, d = mesh.num_vertices, mesh.dim
+    one = u.ndim == 1
+    uu = u.reshape(V, -1)
+    gK = np.einsum("cjk,cja->cka", uu[mesh.cells], grads)          # [C, c, d]
+    num = np.zeros((V,) + gK.shape[1:])
+    den = np.zeros(V)
+    for loc in range(d + 1):
+        np.add.at(num, mesh.cells[:, loc], vol[:, None, None] * gK)
+        np.add.at(den, mesh.cells[:, loc], vol)
+    out = num / den[:, None, None]
+    return out[:, 0, :] if one else out
+
+
+def recover_hessian_clement(mesh, u):
+    """(g, H) by two Clement interpolations (movement/monitor.py:286-293); H[v, i, j] = d_j g_i."""
+    g = clement_gradient(mesh, u)
+    return g, clement_gradient(mesh, g)
+
+
+def solution_monitor(mesh, u, gradient_scale_factor=None, hessian_scale_factor=None):
+    """movement/monitor.py:242-255 (gradient), :295-308 (Hessian), :346-365 (both): 1 + alpha gg / max|gg| + beta HH / max|HH|."""
+    m = np.ones(mesh.num_vertices)
+    if gradient_scale_factor is not None:
+        g = recover_gradient_l2(mesh, u)
+        gg = np.einsum("ia,ia->i", g, g)
+        m = m + gradient_scale_factor * gg / np.abs(gg).max()
+    if hessian_scale_factor is not None:
+        H = recover_hessian_clement(mesh, u)[1]
+        HH = np.einsum("iab,iab->i", H, H)
+        m = m + hessian_scale_factor * HH / np.abs(HH).max()
+    return m
+
+
 def monitor_const(x):
     return np.ones(x.shape[0])
 

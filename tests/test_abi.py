@@ -73,8 +73,12 @@ def test_host_mesh_surface_without_gpu():
     copy = mv.Mesh(mesh.coordinates.copy(deepcopy=True))
     copy.coordinates.dat.data[:] += 1.0
     assert np.allclose(copy.coordinates.dat.data - mesh.coordinates.dat.data, 1.0)
+    u = mv.Function(mesh.function_space("P1"))
     for b in (mv.GradientMonitorBuilder, mv.HessianMonitorBuilder):
-        with pytest.raises(NotImplementedError):
-            b(None, None)
+        with pytest.raises(AssertionError):          # movement/monitor.py:188: the solution must be a Function
+            b(3, None, 1.0)
+        with pytest.raises(AssertionError):          # :225 / :278: positive scale factor
+            b(3, u, 0.0)
+        assert callable(b(3, u, 1.0).get_monitor())
     spec = mv.RingMonitorBuilder((0.5, 0.5), 0.4, 20.0, 200.0)()(mesh)
     assert spec.params == (0.5, 0.5, 0.0, 0.4, 20.0, 200.0)

@@ -444,3 +444,21 @@ def test_equation_bc_non_straight_and_non_planar_segments():
         orc = mo.OracleRelaxation(mo.OMesh(coords, mesh.cells, mesh.bfacets, mesh.btags), mo.monitor_test_ring)
         with pytest.raises(ValueError, match=f"Boundary segment '1' is not {name}."):
             orc.move()
+
+
+# ---- solution-based monitors (movement/monitor.py:174-365): the reference's known answers, test/test_monitor.py:64-152 ----
+def test_solution_monitor_known_answers():
+    mesh = mo.unit_square_mesh(5)
+    x = mesh.coords[:, 0]
+    assert np.allclose(mo.solution_monitor(mesh, x ** 2, gradient_scale_factor=1e-8), 1)        # :69-73
+    assert np.allclose(mo.solution_monitor(mesh, x, gradient_scale_factor=1), 2)                 # :75-79
+    assert np.allclose(mo.solution_monitor(mesh, x ** 3, hessian_scale_factor=1e-8), 1)          # :87-91
+    assert np.allclose(mo.solution_monitor(mesh, x ** 3, 1e-8, 1e-8), 1)                         # :107-116
+    both = mo.solution_monitor(mesh, x ** 3, 1.0, 1e-8)                                          # :118-134
+    assert np.abs(both - mo.solution_monitor(mesh, x ** 3, gradient_scale_factor=1.0)).max() < 1e-7
+    both = mo.solution_monitor(mesh, x ** 3, 1e-8, 1.0)                                          # :136-152
+    assert np.abs(both - mo.solution_monitor(mesh, x ** 3, hessian_scale_factor=1.0)).max() < 1e-7
+    # the Clement Hessian of a quadratic is exact at vertices whose patch is interior and symmetric
+    g, H = mo.recover_hessian_clement(mo.unit_square_mesh(8), 0.5 * mo.unit_square_mesh(8).coords[:, 0] ** 2)
+    centre = 4 * 9 + 4
+    assert abs(H[centre, 0, 0] - 1.0) < 1e-12 and abs(H[centre, 1, 1]) < 1e-12
