@@ -7,6 +7,7 @@ importing the package does not need a GPU, constructing a mover does -- there is
 """
 from .exceptions import ConvergenceError  # noqa: F401
 from .laplacian_smoothing import *  # noqa: F401,F403
+from .io import VTKFile  # noqa: F401
 from .mesh import (DirichletBC, EquationBC, Function, Mesh, PeriodicUnitCubeMesh, PeriodicUnitIntervalMesh,  # noqa: F401
                    PeriodicUnitSquareMesh, RectangleMesh, UnitCubeMesh, UnitIntervalMesh, UnitSquareMesh,
                    UnitTriangleMesh, from_firedrake)

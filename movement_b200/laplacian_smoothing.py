@@ -10,6 +10,7 @@ from . import _lib as L
 from .core import use_current_stream
 from .mesh import DirichletBC, Function
 from .mover import PrimeMover, _print
+from .profiling import event
 
 __all__ = ["LaplacianSmoother"]
 
@@ -42,6 +43,7 @@ class LaplacianSmoother(PrimeMover):
     ksp_rtol = 1.0e-12
     ksp_max_it = 100000
 
+    @event("movement.laplacian_smoothing.LaplacianSmoother.__init__")
     def __init__(self, mesh, timestep, **kwargs):
         super().__init__(mesh, **kwargs)
         assert timestep > 0.0
@@ -86,6 +88,7 @@ class LaplacianSmoother(PrimeMover):
         self.x.written()
         self._displacement_norm = nrm.value
 
+    @event("movement.laplacian_smoothing.LaplacianSmoother.move")
     def move(self, time, update_boundary_velocity=None, boundary_conditions=None, solver_parameters=None):
         """movement/laplacian_smoothing.py:80-127."""
         if update_boundary_velocity is not None:

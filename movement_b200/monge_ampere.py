@@ -18,6 +18,7 @@ import torch
 
 from . import _lib as L
 from .mesh import DirichletBC, EquationBC, Function
+from .profiling import event
 from .monitor import BuiltinMonitor
 from .mover import PrimeMover, _print
 
@@ -261,6 +262,7 @@ class MongeAmpereMover_Base(PrimeMover, metaclass=abc.ABCMeta):
         self._sync()
         self._fused = self._resolve_monitor()
 
+    @event("movement.monge_ampere.MongeAmpereMover_Base.apply_initial_guess")
     def apply_initial_guess(self, phi_init, H_init):
         """movement/monge_ampere.py:187-210."""
         if phi_init is not None and H_init is not None:
@@ -286,12 +288,14 @@ class MongeAmpereMover_Base(PrimeMover, metaclass=abc.ABCMeta):
         self._sync()
         return self._diagnostics(True)
 
+    @event("movement.monge_ampere.MongeAmpereMover_Base.l2_projector")
     def _l2_project(self):
         it = C.c_int(0)
         self._call(L.load().mv_ma_l2_project, C.byref(it))
         self._grad_phi.written()
         return it.value
 
+    @event("movement.monge_ampere.MongeAmpereMover_Base._update_physical_coordinates")
     def _update_physical_coordinates(self, fused_monitor=False):
         """x = xi + grad(phi) (monge_ampere.py:226-244), then the tangling check -- which, as in the
         reference, looks at ``mesh.coordinates`` (the computational mesh at this point)."""
@@ -307,6 +311,7 @@ class MongeAmpereMover_Base(PrimeMover, metaclass=abc.ABCMeta):
 class MongeAmpereMover_Relaxation(MongeAmpereMover_Base):
     """Parabolised Monge-Ampere relaxation (movement/monge_ampere.py:345-540)."""
 
+    @event("movement.monge_ampere.MongeAmpereMover_Relaxation.__init__")
     def __init__(self, mesh, monitor_function, phi_init=None, H_init=None, **kwargs):
         self.pseudo_dt = float(kwargs.pop("pseudo_timestep", 0.1))
         super().__init__(mesh, monitor_function=monitor_function, **kwargs)
@@ -315,12 +320,14 @@ class MongeAmpereMover_Relaxation(MongeAmpereMover_Base):
         self.cg_iterations = []  # (l2 projection, poisson, hessian) inner iteration counts per step
         self.trace = []          # (i, volume ratio, sigma/mu, residual, theta) per iteration of the last move()
 
+    @event("movement.monge_ampere.MongeAmpereMover_Relaxation.pseudotimestepper")
     def _pseudotimestep(self):
         it = C.c_int(0)
         self._call(L.load().mv_ma_pseudotimestep, self.pseudo_dt, C.byref(it))
         self.phi.written()
         return it.value
 
+    @event("movement.monge_ampere.MongeAmpereMover_Relaxation.equidistributor")
     def _equidistribute(self):
         it = C.c_int(0)
         self._call(L.load().mv_ma_equidistribute, C.byref(it))
@@ -410,6 +417,7 @@ class MongeAmpereMover_Relaxation(MongeAmpereMover_Base):
             self._convergence_error(i + 1)
         return i
 
+    @event("movement.monge_ampere.MongeAmpereMover_Relaxation.move")
     def move(self):
         """Run the relaxation to convergence; returns the iteration count ``i`` at the break
         (movement/monge_ampere.py:488-540)."""
@@ -459,6 +467,7 @@ class MongeAmpereMover_QuasiNewton(MongeAmpereMover_Base):
     pc_max_it = 400
     linesearch = {"damping": 0.8, "maxstep": 1.05, "max_it": 5, "steptol": 1.0e-12}
 
+    @event("movement.monge_ampere.MongeAmpereMover_QuasiNewton.__init__")
     def __init__(self, mesh, monitor_function, phi_init=None, H_init=None, **kwargs):
         if mesh.topological_dimension == 1:
             raise NotImplementedError("1D case not implemented for quasi-Newton method.")
@@ -533,6 +542,7 @@ class MongeAmpereMover_QuasiNewton(MongeAmpereMover_Base):
                f"   Variation (σ/μ) {self.coefficient_of_variation:8.2e}"
                f"   Residual {residual:8.2e}")
 
+    @event("movement.monge_ampere.MongeAmpereMover_QuasiNewton.move")
     def move(self):
         """Run the quasi-Newton method to convergence; returns the SNES iteration count
         (movement/monge_ampere.py:729-750)."""

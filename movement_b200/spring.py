@@ -18,6 +18,7 @@ from . import _lib as L
 from .core import use_current_stream
 from .mesh import DirichletBC, Function
 from .mover import PrimeMover, _print
+from .profiling import event
 
 __all__ = ["SpringMover_Lineal", "SpringMover_Torsional", "SpringMover"]
 
@@ -83,17 +84,21 @@ class SpringMover_Base(PrimeMover):
         return self._edge_geometry()[0]
 
     @property
+    @event("movement.spring.SpringMover_Base.facet_areas")
     def facet_areas(self):
         return _EdgeField(self._edge_geometry()[1])
 
     @property
+    @event("movement.spring.SpringMover_Base.tangents")
     def tangents(self):
         return _EdgeField(self._edge_geometry()[2])
 
     @property
+    @event("movement.spring.SpringMover_Base.angles")
     def angles(self):
         return _EdgeField(self._edge_geometry()[3])
 
+    @event("movement.spring.SpringMover_Base._stiffness_matrix")
     def _stiffness_matrix(self):
         """Dense 2V x 2V matrix exactly as spring.py:148-181 builds it -- for inspection on small
         meshes only; ``move`` never forms it."""
@@ -137,6 +142,7 @@ class SpringMover_Base(PrimeMover):
                 self._mask[bc.nodes] = 3
         return boundary_conditions
 
+    @event("movement.spring.SpringMover_Base.assemble_stiffness_matrix")
     def assemble_stiffness_matrix(self, boundary_conditions=None):
         """Dense row-replaced matrix (spring.py:183-235); small meshes only."""
         self._apply_boundary_conditions(boundary_conditions)
@@ -151,6 +157,7 @@ class SpringMover_Base(PrimeMover):
 class SpringMover_Lineal(SpringMover_Base):
     """movement/spring.py:238-283."""
 
+    @event("movement.spring.SpringMover_Lineal.move")
     def move(self, time, update_boundary_displacement=None, boundary_conditions=None):
         if update_boundary_displacement is not None:
             update_boundary_displacement(time)

@@ -7,6 +7,7 @@ import torch
 
 from .core import device_mesh_from
 from .mesh import Function
+from .profiling import event
 
 __all__ = ["MeshTanglingChecker"]
 
@@ -31,6 +32,7 @@ class MeshTanglingChecker:
         self._count = self._dm.tangle_check(self.mesh.coordinates.tensor, self._detJ0, self._detJ_ratio.tensor)
         return self._detJ_ratio.written()
 
+    @event("movement.tangling.MeshTanglingChecker.check")
     def check(self):
         """Count cells with ratio <= 0 (owned cells; summed over ranks)."""
         num_tangled = self._dm.tangle_check(self.mesh.coordinates.tensor, self._detJ0, None)

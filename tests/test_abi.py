@@ -82,3 +82,38 @@ def test_host_mesh_surface_without_gpu():
         assert callable(b(3, u, 1.0).get_monitor())
     spec = mv.RingMonitorBuilder((0.5, 0.5), 0.4, 20.0, 200.0)()(mesh)
     assert spec.params == (0.5, 0.5, 0.0, 0.4, 20.0, 200.0)
+
+
+def test_vtk_output_and_profiling_events(tmp_path):
+    """f4: the demos' VTKFile(...).write(mesh.coordinates) and the reference's PETSc log events as named ranges."""
+    import xml.etree.ElementTree as ET
+
+    import movement_b200 as mv
+    import movement_b200.profiling as prof
+
+    mesh = mv.UnitSquareMesh(3, 2)
+    out = mv.VTKFile(str(tmp_path / "run.pvd"))
+    phi = mv.Function(mesh.function_space("P1"), name="phi").interpolate(lambda x: x[:, 0] + 2 * x[:, 1])
+    for t in (0.0, 0.5):
+        out.write(mesh.coordinates, phi, time=t)
+    sets = ET.parse(tmp_path / "run.pvd").getroot().find("Collection").findall("DataSet")
+    assert [s.get("timestep") for s in sets] == ["0", "0.5"] and sets[1].get("file") == "run_1.vtu"
+    piece = ET.parse(tmp_path / "run_1.vtu").getroot().find("UnstructuredGrid").find("Piece")
+    assert piece.get("NumberOfPoints") == "12" and piece.get("NumberOfCells") == "12"
+    names = [a.get("Name") for a in piece.find("PointData").findall("DataArray")]
+    assert names == ["Coordinates", "phi"]
+    vals = np.array(piece.find("PointData").findall("DataArray")[1].text.split(), dtype=float)
+    assert np.allclose(vals, phi.dat.data_ro)
+    prof.reset()
+    prof.enable()
+    try:
+        with prof.event("movement.monge_ampere.MongeAmpereMover_Relaxation.move"):
+            pass
+        assert prof.events()["movement.monge_ampere.MongeAmpereMover_Relaxation.move"][0] == 1
+        assert "MongeAmpereMover_Relaxation.move" in prof.log_view()
+    finally:
+        prof.enable(False)
+    # every site the reference decorates is decorated here
+    for cls, name in ((mv.MongeAmpereMover_Relaxation, "move"), (mv.MongeAmpereMover_QuasiNewton, "move"), (mv.LaplacianSmoother, "move"),
+                      (mv.SpringMover_Lineal, "move"), (mv.MeshTanglingChecker, "check")):
+        assert hasattr(getattr(cls, name), "__wrapped__")
