@@ -300,6 +300,12 @@ int mv_spring_move(mv_mesh* m, double* coords, const double* forcing, const uint
  * set = dof (v,c) is a Dirichlet row (identity).  mask may be NULL.                    */
 int mv_spring_apply(mv_mesh* m, const double* coords, const uint16_t* mask, const double* x,
                     double* y);
+/* Solver of mv_spring_move on this mesh (replaces: the solver choice at spring.py:266, a dense numpy solve there).  Meshes
+ * of at least MV_SPRING_AMG_MIN (4096) vertices assemble the xx / xy / yy blocks on the mesh pattern and precondition CG
+ * with one multigrid V-cycle per diagonal block; smaller ones run the matrix-free Jacobi-PCG.
+ * info[0], info[1] = levels of the xx / yy hierarchies (0: Jacobi path so far), info[2] = 1 if the last solve rebuilt
+ * them, info[3] = PCG iterations right after the last set-up, info[4] = solves since, info[5] = iterations of the last solve */
+int mv_spring_solver_info(const mv_mesh* m, int64_t* info);
 
 /* ---- multi-GPU (replaces: the MPI halo exchange / allreduce implicit in PyOP2 and PETSc;
  * SURVEY 5.8).  nccl_lib_path: path of libnccl.so.2; unique_id: 128 bytes from

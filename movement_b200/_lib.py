@@ -85,6 +85,7 @@ SIGNATURES = {
     "mv_spring_edge_geometry": (_i, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "mv_spring_move": (_i, [_vp, _vp, _vp, _vp, _d, _vp, _d, _d, _i, _pi, _pd]),
     "mv_spring_apply": (_i, [_vp, _vp, _vp, _vp, _vp]),
+    "mv_spring_solver_info": (_i, [_vp, _pi64]),
     "mv_comm_unique_id": (_i, [C.c_char_p, _vp]),
     "mv_comm_init": (_i, [C.c_char_p, _vp, _i, _i]),
     "mv_comm_finalize": (_i, []),

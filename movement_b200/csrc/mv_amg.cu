@@ -956,14 +956,20 @@ static int build_levels(mv_mesh* m, Amg* a, const BuildParams& bp) {
 }
 
 static int amg_build(mv_mesh* m, int op, const uint16_t* mask_bit0, int singular, Amg** out) {
+  const double *val, *dinv_unused;
+  MV_CHECK(op_arrays(m, op, &val, &dinv_unused));
+  return amg_build_values(m, op, val, mask_bit0, singular, out);
+}
+
+// hierarchy of ANY symmetric M-matrix-like operator stored on the mesh pattern (borrowed values; the caller keeps them
+// alive): the assembled operators above, the diagonal blocks of the spring stiffness (mv_movers.cu)
+int amg_build_values(mv_mesh* m, int op, const double* val, const uint16_t* mask_bit0, int singular, Amg** out) {
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   cudaEventRecord(e0, g_stream);
   Amg* a = new Amg();
   a->op = op;
   a->singular = singular;
-  const double *val, *dinv_unused;
-  MV_CHECK(op_arrays(m, op, &val, &dinv_unused));
   BuildParams bp;
   bp.theta = env_double("MV_AMG_THETA", 1e-8);
   bp.deg0 = env_int("MV_AMG_DEG0", 1);

@@ -520,6 +520,7 @@ extern "C" void mv_mesh_destroy(mv_mesh* m) {
   dev_free(m->tmp_vec);
   dev_free(m->cell_tmp);
   mv::amg_release(m);
+  mv::spring_pc_release(m);
   delete m;
 }
 

@@ -249,6 +249,14 @@ struct mv_mesh {
   double total_volume = 0, ml_sumsq = 0, ml_sum = 0;
   // spring data (lazy)
   int* edge_opp = nullptr;   // [sell_len] opposite vertex of the '+' cell for (row,col)
+  // assembled spring stiffness (xx, xy, yy blocks on the mesh pattern) and the block-diagonal multigrid preconditioner
+  // of its solves (mv_movers.cu): hierarchies of the xx and yy blocks, kept across calls while they still precondition well
+  double* spring_val[3] = {nullptr, nullptr, nullptr};
+  mv::Amg* spring_pc[2] = {nullptr, nullptr};
+  uint16_t* spring_mask[2] = {nullptr, nullptr};   // bit 0 = component constrained (the hierarchies' level-0 masks)
+  int spring_pc_its = 0;     // PCG iterations of the solve that followed the last set-up
+  int spring_pc_age = 0;     // solves since
+  int spring_pc_age_its = 0; // PCG iterations of the latest solve
   int64_t* cell_gid = nullptr;   // [C] global cell numbers (partitioned meshes only; mv_mesh_set_cell_order)
   // work
   mv::Reduce red;
@@ -382,6 +390,8 @@ int amg_get(mv_mesh* m, int op, const uint16_t* mask, int ncomp, int singular, A
 int amg_apply(mv_mesh* m, Amg* a, int ncomp, const double* r, double* z, const int* done);
 int amg_ensure_work(Amg* a, int ncomp);
 void amg_release(mv_mesh* m);
+int amg_build_values(mv_mesh* m, int op, const double* val, const uint16_t* mask_bit0, int singular, Amg** out);
+void spring_pc_release(mv_mesh* m);
 
 // ---------------------------------------------------------------------------------
 // device helpers
