@@ -280,8 +280,8 @@ struct mv_ma {
   double* a = nullptr;          // [V] assembled int psi m det(I+H)
   double* dphi = nullptr;       // [V]
   // the two previous Poisson solves (update, right-hand side): Galerkin initial guess of the next one
-  double* hist_x[2] = {nullptr, nullptr};   // [V]
-  double* hist_b[2] = {nullptr, nullptr};   // [V]
+  double* hist_x[8] = {nullptr};   // [V] K-orthonormal basis of the previous updates, newest first
+  double* hist_b[8] = {nullptr};   // [V] K x_i
   int hist_n = 0;
   double* mon_raw = nullptr;    // [V]
   double* dscal = nullptr;      // device scalars
@@ -302,7 +302,7 @@ struct mv_ma {
 namespace mv {
 
 // device scalar slots of mv_ma::dscal (mv_ma.cu, mv_qn.cu)
-enum { D_MONMAX = 0, D_SUMA = 1, D_THETA = 2, D_RES2 = 3, D_VSUM = 4, D_VMAX = 5, D_VMIN = 6, D_VSSD = 7, D_N = 16 };
+enum { D_MONMAX = 0, D_SUMA = 1, D_THETA = 2, D_RES2 = 3, D_VSUM = 4, D_VMAX = 5, D_VMIN = 6, D_VSSD = 7, D_N = 32 };
 
 // EquationBC branch of the L2 projector (mv_eqbc.cu)
 int eqbc_build(mv_ma* ma, const std::vector<int>& tagidx, const std::vector<char>& is_eq, const std::vector<int>& verts,

@@ -605,7 +605,7 @@ extern "C" void mv_ma_destroy(mv_ma* ma) {
   dev_free(ma->qn_t2); dev_free(ma->qn_base); dev_free(ma->qn_dots);
   if (ma->qn_hdots) cudaFreeHost(ma->qn_hdots);
   dev_free(ma->rhs); dev_free(ma->a); dev_free(ma->dphi); dev_free(ma->dscal); dev_free(ma->bc_mask);
-  for (int i = 0; i < 2; ++i) { dev_free(ma->hist_x[i]); dev_free(ma->hist_b[i]); }
+  for (int i = 0; i < 8; ++i) { dev_free(ma->hist_x[i]); dev_free(ma->hist_b[i]); }
   if (ma->h_scal) cudaFreeHost(ma->h_scal);
   eqbc_free(ma);
   delete ma;
@@ -889,56 +889,101 @@ extern "C" int mv_ma_diagnostics(mv_ma* ma, int use_H_old, double* out) {
   return MV_OK;
 }
 
-// Initial guess of the Poisson solve K x = b from the two previous solves (x1, b1), (x2, b2) of the same mover:
-// the Galerkin (energy-optimal) combination x0 = a1 x1 + a2 x2, i.e. [xi.K xj] a = [xi.b] with K xj = bj known.
-// The right-hand side dt * (a - theta m_l) changes smoothly from one relaxation iteration to the next, so x0 is
-// typically two to three digits accurate; the solve itself and its stopping rule (rtol relative to b) are unchanged.
-enum { H_G11 = 8, H_G12 = 9, H_G22 = 10, H_F1 = 11, H_F2 = 12, H_A1 = 13, H_A2 = 14 };
+// Initial guess of the Poisson solve K x = b from the previous solves of the same mover: the Galerkin (energy-optimal)
+// combination over their span.  The history is kept as a K-ORTHONORMAL basis {(x_i, b_i = K x_i)}, x_i.b_j = delta_ij
+// (Gram-Schmidt in the energy inner product, which only needs the stored b_j: <x_i, y>_K = x_i.(K y) = b_i.y), so the
+// guess is x0 = sum_i (x_i.b) x_i -- no small system, no conditioning problem when consecutive solutions are nearly
+// parallel.  The right-hand side dt * (a - theta m_l) changes smoothly from one relaxation iteration to the next (a few
+// slowly decaying modes late in the run), so x0 is typically two to four digits accurate; the solve itself and its
+// stopping rule (rtol relative to b) are unchanged.  Depth: MV_POISSON_HISTORY (0 off, 1 = default depth, k >= 2 = k).
+#define MV_HIST_MAX 8
+#define MV_HIST_DEFAULT 4
+enum { H_C = 8, H_S0 = 8 + MV_HIST_MAX, H_S1 = 9 + MV_HIST_MAX, H_END = 10 + MV_HIST_MAX };
+static_assert((int)H_END <= (int)D_N, "history scalars must fit the device scalar block");
+struct HistPtrs {
+  const double* x[MV_HIST_MAX];
+  const double* b[MV_HIST_MAX];
+};
+// c_i = X_i . y for the m basis vectors (X = x or b side), s0 = z . y (optional)
+template <int M>
 __global__ void __launch_bounds__(MV_BLOCK)
-k_hist_dots(int64_t n, const double* __restrict__ x1, const double* __restrict__ b1, const double* __restrict__ x2,
-            const double* __restrict__ b2, const double* __restrict__ b, double* __restrict__ partials,
-            unsigned* __restrict__ counter, double* __restrict__ dscal) {
-  double acc[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+k_hist_dots(int64_t n, HistPtrs h, int side_b, const double* __restrict__ y, const double* __restrict__ z,
+            double* __restrict__ partials, unsigned* __restrict__ counter, double* __restrict__ dscal) {
+  double acc[M + 1];
+#pragma unroll
+  for (int i = 0; i <= M; ++i) acc[i] = 0.0;
   for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < n; v += (int64_t)gridDim.x * blockDim.x) {
-    const double p1 = x1[v], q1 = b1[v], bb = b[v];
-    acc[0] = fma(p1, q1, acc[0]);
-    acc[3] = fma(p1, bb, acc[3]);
-    if (x2) {
-      const double p2 = x2[v], q2 = b2[v];
-      acc[1] = fma(p1, q2, acc[1]);
-      acc[2] = fma(p2, q2, acc[2]);
-      acc[4] = fma(p2, bb, acc[4]);
-    }
+    const double yy = y[v];
+#pragma unroll
+    for (int i = 0; i < M; ++i) acc[i] = fma((side_b ? h.b[i] : h.x[i])[v], yy, acc[i]);
+    if (z) acc[M] = fma(z[v], yy, acc[M]);
   }
-  grid_reduce_sum<5>(acc, partials, counter, [&](double(&t)[5]) {
-    dscal[H_G11] = t[0]; dscal[H_G12] = t[1]; dscal[H_G22] = t[2]; dscal[H_F1] = t[3]; dscal[H_F2] = t[4];
+  grid_reduce_sum<M + 1>(acc, partials, counter, [&](double(&t)[M + 1]) {
+#pragma unroll
+    for (int i = 0; i < M; ++i) dscal[H_C + i] = t[i];
+    dscal[H_S0] = t[M];
   });
 }
-__global__ void k_hist_alpha(int two, double* __restrict__ dscal) {
-  const double g11 = dscal[H_G11], g12 = dscal[H_G12], g22 = dscal[H_G22], f1 = dscal[H_F1], f2 = dscal[H_F2];
-  double a1 = 0.0, a2 = 0.0;
-  const double det = g11 * g22 - g12 * g12;
-  if (two && g11 > 0.0 && g22 > 0.0 && det > 1e-8 * g11 * g22) {   // x1, x2 not (numerically) parallel in the energy norm
-    a1 = (f1 * g22 - f2 * g12) / det;
-    a2 = (f2 * g11 - f1 * g12) / det;
-  } else if (g11 > 0.0) {
-    a1 = f1 / g11;
-  }
-  if (!(a1 == a1) || !(a2 == a2)) { a1 = 0.0; a2 = 0.0; }
-  dscal[H_A1] = a1;
-  dscal[H_A2] = a2;
-}
+// x0 = sum_i c_i x_i
+template <int M>
 __global__ void __launch_bounds__(MV_BLOCK)
-k_hist_guess(int64_t n, const double* __restrict__ x1, const double* __restrict__ x2, const double* __restrict__ dscal,
-             double* __restrict__ x0) {
-  const double a1 = dscal[H_A1], a2 = dscal[H_A2];
-  for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < n; v += (int64_t)gridDim.x * blockDim.x)
-    x0[v] = x2 ? fma(a2, x2[v], a1 * x1[v]) : a1 * x1[v];
+k_hist_guess(int64_t n, HistPtrs h, const double* __restrict__ dscal, double* __restrict__ x0) {
+  double c[M > 0 ? M : 1];
+#pragma unroll
+  for (int i = 0; i < M; ++i) { c[i] = dscal[H_C + i]; if (!(c[i] == c[i])) c[i] = 0.0; }
+  for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < n; v += (int64_t)gridDim.x * blockDim.x) {
+    double a = 0.0;
+#pragma unroll
+    for (int i = 0; i < M; ++i) a = fma(c[i], h.x[i][v], a);
+    x0[v] = a;
+  }
+}
+// (xn, bn) = (x, b) - sum_i c_i (x_i, b_i) ; s1 = xn . bn
+template <int M>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_hist_orth(int64_t n, HistPtrs h, const double* __restrict__ x, const double* __restrict__ b, double* __restrict__ xn,
+            double* __restrict__ bn, double* __restrict__ partials, unsigned* __restrict__ counter, double* __restrict__ dscal) {
+  double c[M > 0 ? M : 1];
+#pragma unroll
+  for (int i = 0; i < M; ++i) c[i] = dscal[H_C + i];
+  double acc[1] = {0.0};
+  for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < n; v += (int64_t)gridDim.x * blockDim.x) {
+    double xv = x[v], bv = b[v];
+#pragma unroll
+    for (int i = 0; i < M; ++i) { xv = fma(-c[i], h.x[i][v], xv); bv = fma(-c[i], h.b[i][v], bv); }
+    xn[v] = xv;
+    bn[v] = bv;
+    acc[0] = fma(xv, bv, acc[0]);
+  }
+  grid_reduce_sum<1>(acc, partials, counter, [&](double(&t)[1]) { dscal[H_S1] = t[0]; });
+}
+// normalise the new pair in the energy norm; a direction that is (numerically) inside the span is stored as zero
+__global__ void __launch_bounds__(MV_BLOCK)
+k_hist_normalise(int64_t n, const double* __restrict__ dscal, double* __restrict__ xn, double* __restrict__ bn) {
+  const double s0 = dscal[H_S0], s1 = dscal[H_S1];
+  const double sc = (s1 > 0.0 && s0 > 0.0 && s1 > 1e-14 * s0) ? rsqrt(s1) : 0.0;
+  for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < n; v += (int64_t)gridDim.x * blockDim.x) {
+    xn[v] *= sc;
+    bn[v] *= sc;
+  }
 }
 
-static int g_poisson_history = -1;   // -1: read MV_POISSON_HISTORY (default on)
+#define HIST_DISPATCH(m, ...)                                              \
+  switch (m) {                                                             \
+    case 0: { constexpr int M = 0; __VA_ARGS__; } break;                   \
+    case 1: { constexpr int M = 1; __VA_ARGS__; } break;                   \
+    case 2: { constexpr int M = 2; __VA_ARGS__; } break;                   \
+    case 3: { constexpr int M = 3; __VA_ARGS__; } break;                   \
+    case 4: { constexpr int M = 4; __VA_ARGS__; } break;                   \
+    case 5: { constexpr int M = 5; __VA_ARGS__; } break;                   \
+    case 6: { constexpr int M = 6; __VA_ARGS__; } break;                   \
+    case 7: { constexpr int M = 7; __VA_ARGS__; } break;                   \
+    default: { constexpr int M = 8; __VA_ARGS__; } break;                  \
+  }
+
+static int g_poisson_history = -1;   // -1: read MV_POISSON_HISTORY (default on); otherwise the depth (0 = off)
 extern "C" int mv_set_poisson_history(int on) {
-  g_poisson_history = on ? 1 : 0;
+  g_poisson_history = on <= 0 ? 0 : (on == 1 ? MV_HIST_DEFAULT : (on > MV_HIST_MAX ? MV_HIST_MAX : on));
   return MV_OK;
 }
 
@@ -951,15 +996,16 @@ extern "C" int mv_ma_pseudotimestep(mv_ma* ma, double dt, int* iters) {
   const int64_t n = m->Vown;
   const int gv = grid_for(n);
   MV_L k_scale<<<gv, MV_BLOCK, 0, g_stream>>>(n, dt, ma->f[MV_F_RESIDUAL], ma->rhs);
-  if (g_poisson_history < 0) { const char* e = getenv("MV_POISSON_HISTORY"); g_poisson_history = e ? atoi(e) : 1; }
-  const int use_hist = g_poisson_history;
-  if (use_hist && ma->hist_n > 0) {
-    const bool two = ma->hist_n > 1;
-    MV_L k_hist_dots<<<gv, MV_BLOCK, 0, g_stream>>>(n, ma->hist_x[0], ma->hist_b[0], two ? ma->hist_x[1] : nullptr,
-                                               two ? ma->hist_b[1] : nullptr, ma->rhs, m->red.partials, m->red.counter, ma->dscal);
-    if (comm_active()) MV_CHECK(allreduce_sum_dev(ma->dscal + H_G11, 5));
-    MV_L k_hist_alpha<<<1, 1, 0, g_stream>>>(two ? 1 : 0, ma->dscal);
-    MV_L k_hist_guess<<<gv, MV_BLOCK, 0, g_stream>>>(n, ma->hist_x[0], two ? ma->hist_x[1] : nullptr, ma->dscal, ma->dphi);
+  if (g_poisson_history < 0) { const char* e = getenv("MV_POISSON_HISTORY"); mv_set_poisson_history(e ? atoi(e) : 1); }
+  const int depth = g_poisson_history;
+  HistPtrs hp;
+  const int mh = ma->hist_n < depth ? ma->hist_n : depth;   // basis vectors in use (the newest mh)
+  for (int i = 0; i < MV_HIST_MAX; ++i) { hp.x[i] = i < mh ? ma->hist_x[i] : nullptr; hp.b[i] = i < mh ? ma->hist_b[i] : nullptr; }
+  const bool dist = comm_active();
+  if (depth > 0 && mh > 0) {
+    HIST_DISPATCH(mh, MV_L k_hist_dots<M><<<gv, MV_BLOCK, 0, g_stream>>>(n, hp, 0, ma->rhs, nullptr, m->red.partials, m->red.counter, ma->dscal));
+    if (dist) MV_CHECK(allreduce_sum_dev(ma->dscal + H_C, mh));
+    HIST_DISPATCH(mh, MV_L k_hist_guess<M><<<gv, MV_BLOCK, 0, g_stream>>>(n, hp, ma->dscal, ma->dphi));
     MV_KERNEL_CHECK();
   } else {
     MV_CUDA(cudaMemsetAsync(ma->dphi, 0, m->V * sizeof(double), g_stream));
@@ -968,19 +1014,28 @@ extern "C" int mv_ma_pseudotimestep(mv_ma* ma, double dt, int* iters) {
                      nullptr));
   MV_L k_add<<<gv, MV_BLOCK, 0, g_stream>>>(n, ma->f[MV_F_PHI_OLD], ma->dphi, ma->f[MV_F_PHI]);
   MV_KERNEL_CHECK();
-  if (use_hist) {
-    // newest pair into slot 0 (the oldest buffers are recycled)
-    if (!ma->hist_x[1]) {
-      for (int i = 0; i < 2; ++i) {
+  if (depth > 0) {
+    // the new pair, K-orthonormalised against the basis, takes the place of the oldest one (slot depth-1 -> slot 0)
+    for (int i = 0; i < depth; ++i)
+      if (!ma->hist_x[i]) {
         MV_CHECK(dev_alloc(&ma->hist_x[i], n));
         MV_CHECK(dev_alloc(&ma->hist_b[i], n));
       }
-    }
-    double* tx = ma->hist_x[1]; ma->hist_x[1] = ma->hist_x[0]; ma->hist_x[0] = tx;
-    double* tb = ma->hist_b[1]; ma->hist_b[1] = ma->hist_b[0]; ma->hist_b[0] = tb;
-    MV_CUDA(cudaMemcpyAsync(ma->hist_x[0], ma->dphi, n * sizeof(double), cudaMemcpyDeviceToDevice, g_stream));
-    MV_CUDA(cudaMemcpyAsync(ma->hist_b[0], ma->rhs, n * sizeof(double), cudaMemcpyDeviceToDevice, g_stream));
-    if (ma->hist_n < 2) ++ma->hist_n;
+    const int keep = mh < depth - 1 ? mh : depth - 1;   // basis vectors that survive
+    for (int i = 0; i < MV_HIST_MAX; ++i) { if (i >= keep) { hp.x[i] = nullptr; hp.b[i] = nullptr; } }
+    double* xn = ma->hist_x[depth - 1];
+    double* bn = ma->hist_b[depth - 1];
+    // c_i = b_i . x_new = <x_i, x_new>_K ;  s0 = b . x_new   (b = the projected right-hand side up to its mean, and x_new has zero mean)
+    HIST_DISPATCH(keep, MV_L k_hist_dots<M><<<gv, MV_BLOCK, 0, g_stream>>>(n, hp, 1, ma->dphi, ma->rhs, m->red.partials, m->red.counter, ma->dscal));
+    if (dist) MV_CHECK(allreduce_sum_dev(ma->dscal + H_C, MV_HIST_MAX + 1));
+    HIST_DISPATCH(keep, MV_L k_hist_orth<M><<<gv, MV_BLOCK, 0, g_stream>>>(n, hp, ma->dphi, ma->rhs, xn, bn, m->red.partials, m->red.counter, ma->dscal));
+    if (dist) MV_CHECK(allreduce_sum_dev(ma->dscal + H_S1, 1));
+    MV_L k_hist_normalise<<<gv, MV_BLOCK, 0, g_stream>>>(n, ma->dscal, xn, bn);
+    MV_KERNEL_CHECK();
+    for (int i = depth - 1; i > 0; --i) { ma->hist_x[i] = ma->hist_x[i - 1]; ma->hist_b[i] = ma->hist_b[i - 1]; }
+    ma->hist_x[0] = xn;
+    ma->hist_b[0] = bn;
+    if (ma->hist_n < depth) ++ma->hist_n;
   }
   return MV_OK;
 }

@@ -400,7 +400,7 @@ __global__ void k_sp_post(double* __restrict__ scal, int* __restrict__ flags) {
   scal[SC(S_BETA, 0)] = rz > 0.0 ? rzn / rz : 0.0;
   scal[SC(S_RZ, 0)] = rzn;
   scal[SC(S_RZ, 1)] = rrn;
-  if (!(rzn == rzn)) flags[2] = 1;
+  if (!(rzn == rzn) || rzn < 0.0) flags[2] = 1;   // NaN, or a preconditioner that is not positive definite
   flags[1] += 1;
   const bool pre = rzn <= scal[SC(S_THR, 0)], euc = rrn <= scal[SC(S_THR, 1)];
   if (pre && flags[3] == 0) flags[3] = flags[1];
@@ -411,10 +411,13 @@ __global__ void k_sp_post(double* __restrict__ scal, int* __restrict__ flags) {
 // x += alpha p ; r -= alpha q (constrained dofs stay zero)
 __global__ void __launch_bounds__(MV_BLOCK)
 k_sp_update(int64_t n, int64_t ld, const double* __restrict__ p, const double* __restrict__ q, const uint16_t* __restrict__ mask,
-            double* __restrict__ x, double* __restrict__ r, const int* __restrict__ flags, const double* __restrict__ scal) {
+            double* __restrict__ x, double* __restrict__ r, int* __restrict__ flags, const double* __restrict__ scal) {
   if (flags[0]) return;
   const double pq = scal[SC(S_PQ, 0)], rz = scal[SC(S_RZ, 0)];
   const double alpha = pq > 0.0 ? rz / pq : 0.0;
+  // p.K p <= 0 or NaN with r != 0: the operator is not positive definite (degenerate edge, NaN coordinates) -- a breakdown,
+  // not a reason to iterate to maxit with alpha = 0
+  if (!(pq > 0.0) && rz > 0.0 && blockIdx.x == 0 && threadIdx.x == 0) flags[2] = 1;
   for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < n; v += (int64_t)gridDim.x * blockDim.x) {
     const unsigned mk = mask ? mask[v] : 0u;
     const double p0 = p[v], p1 = p[ld + v], q0 = __ldcs(&q[v]), q1 = __ldcs(&q[ld + v]);
@@ -519,6 +522,7 @@ static int spring_solve_amg(mv_mesh* m, const double* coords, const double* dinv
   MV_KERNEL_CHECK();
   int it = 0, batch = 4;
   w.h_flags[0] = 0;
+  if (maxit > 5000) maxit = 5000;   // mesh-independent convergence: thousands of multigrid-preconditioned iterations mean a broken operator
   while (true) {
     MV_CUDA(cudaMemcpyAsync(w.h_flags, w.flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, g_stream));
     MV_CUDA(cudaStreamSynchronize(g_stream));
@@ -546,6 +550,14 @@ static int spring_solve_amg(mv_mesh* m, const double* coords, const double* dinv
 #undef SPRING_SPMV
   const int done = w.h_flags[0], niter = w.h_flags[1], breakdown = w.h_flags[2];
   g_prof.pcg_iters[2] += niter;
+  if (getenv("MV_PCG_VERBOSE")) {
+    MV_CUDA(cudaMemcpyAsync(w.h_scal, w.scal, S_NSLOTS * 16 * sizeof(double), cudaMemcpyDeviceToHost, g_stream));
+    MV_CUDA(cudaStreamSynchronize(g_stream));
+    fprintf(stderr, "[mv spring] n %lld: %d iterations (preconditioned test met at %d), done %d, breakdown %d, hierarchies %s (age %d, levels %zu/%zu); "
+            "rz/thr %.3e rr/thr2 %.3e ref %.3e pq %.3e\n", (long long)n, niter, w.h_flags[3], done, breakdown, rebuild ? "rebuilt" : "reused",
+            m->spring_pc_age, px->lv.size(), py->lv.size(), w.h_scal[SC(S_RZ, 0)] / w.h_scal[SC(S_THR, 0)],
+            w.h_scal[SC(S_RZ, 1)] / w.h_scal[SC(S_THR, 1)], w.h_scal[SC(S_REF, 0)], w.h_scal[SC(S_PQ, 0)]);
+  }
   MV_CHECK(soa_to_aos(2, n, xs, ld, u));
   if (m->spring_pc_age == 0) m->spring_pc_its = niter;
   m->spring_pc_age += 1;

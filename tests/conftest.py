@@ -19,6 +19,19 @@ def _seed():
     np.random.seed(0)
 
 
+@pytest.fixture(autouse=True)
+def _restore_trace_printers():
+    """Several test modules silence the movers' trace lines by replacing the modules' ``_print``; tests that read the
+    lines through ``capsys`` must not depend on the order the files run in."""
+    import importlib
+
+    mods = [importlib.import_module("movement_b200." + name) for name in ("mover", "monge_ampere", "laplacian_smoothing", "spring")]
+    saved = [(m, m._print) for m in mods]
+    yield
+    for m, fn in saved:
+        m._print = fn
+
+
 def _has_gpu():
     try:
         import torch

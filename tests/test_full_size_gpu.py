@@ -79,8 +79,12 @@ def test_forced_movers_full_size(which, n):
     assert torch.equal(_dev(mesh), xi)                       # the caller's mesh is never touched (mover.py:49)
     del mover
     # demo forcing: one step at amplitude 1 and one at amplitude 2 -> linear in the data
-    # (the spring solve is a Jacobi-PCG with O(n) iterations at this size: one step, no second run)
-    m1 = _forced(mv, cls, mesh, 1.0, steps=2 if which == "laplacian" else 1)
+    # (the spring stiffness follows the moving mesh, so its solve is not linear in the data: no amplitude-2 run)
+    m1 = _forced(mv, cls, mesh, 1.0, steps=2 if which == "laplacian" else 5)
+    if which == "spring":
+        # block-diagonal multigrid preconditioner (mv_movers.cu): mesh-independent iteration counts, hierarchies reused
+        print("spring cg iterations", m1.cg_iterations)
+        assert DIV > 1 or max(m1.cg_iterations) <= 80, m1.cg_iterations
     d1 = _dev(m1.mesh) - xi
     scale = float(d1.abs().max())
     assert scale > 1e-3

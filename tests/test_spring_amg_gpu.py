@@ -66,7 +66,7 @@ def _oracle_forced(n, steps, dt=0.1, amplitude=0.2):
     return ref
 
 
-@pytest.mark.parametrize("n", [24, 48])
+@pytest.mark.parametrize("n", [32, 48])   # (<= 640 vertices: one level, no hierarchy to test)
 def test_spring_multigrid_path_matches_the_oracle(n):
     mv = _mv()
     steps = 4
