@@ -236,7 +236,12 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
 //   MIX_IT   TV = TX = float: one iteration on the correction, b = the single-precision residual, xin / xout the
 //            correction iterates (MODE == CHEB_FIRST: the previous iterate is zero; no sums in any mode);
 //            x64 != nullptr: the last iteration of a sweep, x64 += the new iterate
-enum { MIX_NONE = 0, MIX_RES = 1, MIX_IT = 2 };
+//   MIX_RES4 / MIX_IT4: the same two roles with the single-precision iterates PACKED per component group: CG = 3 components of
+//            a vertex + one pad in one float4 ([C/3][ld] float4), so that a neighbour's three values arrive with ONE 128-bit
+//            gather instead of three 32-bit ones.  ncu (round 2, 256^3) showed the SoA fp32 iteration issue-bound, not
+//            bandwidth-bound: 2.2 warp instructions per cycle and SM, 1750 per slice, 135 of them gathers -- 1.41 ms at
+//            2.8 TB/s of DRAM traffic where the fp64 kernel it replaced took 1.45 ms.
+enum { MIX_NONE = 0, MIX_RES = 1, MIX_IT = 2, MIX_RES4 = 3, MIX_IT4 = 4 };
 
 template <int C, int CG, int SPB, int MINB, int NSTAGE, bool VS, int MODE, bool LOCAL, typename TV = double, typename TX = double, int MIX = MIX_NONE>
 __global__ void __launch_bounds__(32 * (C / CG) * SPB, MINB)
@@ -248,8 +253,12 @@ k_cheb_tma(const int* __restrict__ sched, int64_t ngroups, int64_t nrows, const 
            double* __restrict__ scal, int maxw, float* __restrict__ f_r = nullptr, float* __restrict__ f_d = nullptr,
            double* __restrict__ x64 = nullptr) {
   constexpr int NG = C / CG;
-  if ((MODE != CHEB_FIRST || MIX == MIX_IT) && *flags) return;
-  constexpr int NS = MIX == MIX_IT ? 1 : (MODE == CHEB_FIRST ? 2 * CG : (MODE == CHEB_CHECK ? CG : 1));
+  constexpr bool IS_RES = MIX == MIX_RES || MIX == MIX_RES4, IS_IT = MIX == MIX_IT || MIX == MIX_IT4;
+  constexpr bool PK = MIX == MIX_RES4 || MIX == MIX_IT4;
+  static_assert(!PK || CG == 3, "packed iterates carry three components per float4");
+  static_assert(MIX != MIX_IT4 || sizeof(TX) == 4, "packed iterates are single precision");
+  if ((MODE != CHEB_FIRST || IS_IT) && *flags) return;
+  constexpr int NS = IS_IT ? 1 : (MODE == CHEB_FIRST ? 2 * CG : (MODE == CHEB_CHECK ? CG : 1));
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int slice_elems = maxw * MV_SLICE;
   // VS: the values are staged too; otherwise only the indices (the gathers depend on them, the values do not) and
@@ -262,10 +271,12 @@ k_cheb_tma(const int* __restrict__ sched, int64_t ngroups, int64_t nrows, const 
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int g = wid % NG, sl = wid / NG;
   const int64_t cb = (int64_t)g * CG * ld;
-  b += cb; xin += cb;
-  if (MIX != MIX_RES) xout += cb;
-  if (MIX == MIX_RES) { f_r += cb; f_d += cb; }
-  if (MIX == MIX_IT && x64) x64 += cb;
+  const int64_t cb4 = (int64_t)g * 4 * ld;   // packed iterates: group g starts at float 4 g ld
+  b += cb;
+  xin += MIX == MIX_IT4 ? cb4 : cb;
+  if (!IS_RES) xout += MIX == MIX_IT4 ? cb4 : cb;
+  if (IS_RES) { f_r += cb; f_d += PK ? cb4 : cb; }
+  if (IS_IT && x64) x64 += cb;
   const TX akx = (TX)ak, ckx = (TX)ck;
   if (threadIdx.x == 0) {
 #pragma unroll
@@ -316,9 +327,13 @@ k_cheb_tma(const int* __restrict__ sched, int64_t ngroups, int64_t nrows, const 
     // streamed operands first: they are in flight while the warp waits for the matrix tile
     TX bv[CG], xo[CG];
 #pragma unroll
-    for (int c = 0; c < CG; ++c) {
-      bv[c] = __ldcs(&b[c * ld + rr]);
-      xo[c] = (MODE == CHEB_FIRST || MIX == MIX_RES) ? (TX)0 : __ldcs(&xout[c * ld + rr]);
+    for (int c = 0; c < CG; ++c) bv[c] = __ldcs(&b[c * ld + rr]);
+    if (MIX == MIX_IT4) {
+      const float4 t = MODE == CHEB_FIRST ? make_float4(0.f, 0.f, 0.f, 0.f) : __ldcs(reinterpret_cast<const float4*>(xout) + rr);
+      xo[0] = (TX)t.x; xo[1 % CG] = (TX)t.y; xo[2 % CG] = (TX)t.z;
+    } else {
+#pragma unroll
+      for (int c = 0; c < CG; ++c) xo[c] = (MODE == CHEB_FIRST || IS_RES) ? (TX)0 : __ldcs(&xout[c * ld + rr]);
     }
     const TV di = __ldg(&dinv[rr]);
     const unsigned mk = mask ? (unsigned)__ldg(&mask[rr]) >> (g * CG) : 0u;
@@ -329,52 +344,88 @@ k_cheb_tma(const int* __restrict__ sched, int64_t ngroups, int64_t nrows, const 
     TX acc[CG];
 #pragma unroll
     for (int c = 0; c < CG; ++c) acc[c] = (TX)0;
-    constexpr int KB = CG >= 9 ? (sizeof(TX) == 4 ? 3 : 2) : (CG >= 3 ? (sizeof(TX) == 4 ? 8 : 5) : 8);
-    for (int k0 = 0; k0 < w; k0 += KB) {
-      int col[KB];
+    if (MIX == MIX_IT4) {
+      // one 128-bit gather per neighbour
+      constexpr int KB = MINB >= 4 ? 5 : 8;   // fewer registers per thread at higher occupancy targets
+      const float4* x4 = reinterpret_cast<const float4*>(xin);
+      for (int k0 = 0; k0 < w; k0 += KB) {
+        int col[KB];
 #pragma unroll
-      for (int j = 0; j < KB; ++j) col[j] = k0 + j < w ? cp[(k0 + j) * MV_SLICE] : (int)rr;
-      TX xv[KB][CG];
+        for (int j = 0; j < KB; ++j) col[j] = k0 + j < w ? cp[(k0 + j) * MV_SLICE] : (int)rr;
+        float4 xv[KB];
 #pragma unroll
-      for (int j = 0; j < KB; ++j) {
-        const TX* xp = xin + col[j];
+        for (int j = 0; j < KB; ++j) xv[j] = __ldg(x4 + col[j]);
 #pragma unroll
-        for (int c = 0; c < CG; ++c) xv[j][c] = __ldg(xp + c * ld);
+        for (int j = 0; j < KB; ++j) {
+          const TV a = k0 + j < w ? (VS ? vp[(k0 + j) * MV_SLICE] : __ldg(vp + (k0 + j) * MV_SLICE)) : (TV)0;
+          acc[0] = fma(a, (TX)xv[j].x, acc[0]);
+          acc[1 % CG] = fma(a, (TX)xv[j].y, acc[1 % CG]);
+          acc[2 % CG] = fma(a, (TX)xv[j].z, acc[2 % CG]);
+        }
       }
+    } else {
+      constexpr int KB = CG >= 9 ? (sizeof(TX) == 4 ? 3 : 2) : (CG >= 3 ? (sizeof(TX) == 4 ? 8 : 5) : 8);
+      for (int k0 = 0; k0 < w; k0 += KB) {
+        int col[KB];
 #pragma unroll
-      for (int j = 0; j < KB; ++j) {
-        const TV a = k0 + j < w ? (VS ? vp[(k0 + j) * MV_SLICE] : (NG > 1 ? __ldg(vp + (k0 + j) * MV_SLICE) : __ldcs(vp + (k0 + j) * MV_SLICE))) : (TV)0;
+        for (int j = 0; j < KB; ++j) col[j] = k0 + j < w ? cp[(k0 + j) * MV_SLICE] : (int)rr;
+        TX xv[KB][CG];
 #pragma unroll
-        for (int c = 0; c < CG; ++c) acc[c] = fma(a, xv[j][c], acc[c]);
+        for (int j = 0; j < KB; ++j) {
+          const TX* xp = xin + col[j];
+#pragma unroll
+          for (int c = 0; c < CG; ++c) xv[j][c] = __ldg(xp + c * ld);
+        }
+#pragma unroll
+        for (int j = 0; j < KB; ++j) {
+          const TV a = k0 + j < w ? (VS ? vp[(k0 + j) * MV_SLICE] : (NG > 1 ? __ldg(vp + (k0 + j) * MV_SLICE) : __ldcs(vp + (k0 + j) * MV_SLICE))) : (TV)0;
+#pragma unroll
+          for (int c = 0; c < CG; ++c) acc[c] = fma(a, xv[j][c], acc[c]);
+        }
       }
     }
     if (live) {
+      TX xkv[CG], outv[CG];
+      if (MIX == MIX_IT4) {
+        const float4 t = __ldg(reinterpret_cast<const float4*>(xin) + row);
+        xkv[0] = (TX)t.x; xkv[1 % CG] = (TX)t.y; xkv[2 % CG] = (TX)t.z;
+      } else if (!IS_RES) {
+#pragma unroll
+        for (int c = 0; c < CG; ++c) xkv[c] = __ldg(&xin[c * ld + row]);
+      }
 #pragma unroll
       for (int c = 0; c < CG; ++c) {
         const bool fix = (mk >> c) & 1u;
         const TX r = fix ? (TX)0 : bv[c] - acc[c];
         const TX z = di * r;
-        if (MIX == MIX_RES) {
+        if (IS_RES) {
           f_r[c * ld + row] = (float)r;
-          f_d[c * ld + row] = (float)(ckx * z);
-        } else if (MIX == MIX_IT) {
-          const TX xk = __ldg(&xin[c * ld + row]);
+          outv[c] = ckx * z;
+          if (!PK) f_d[c * ld + row] = (float)outv[c];
+        } else if (IS_IT) {
+          const TX xk = xkv[c];
           const TX xn = fix ? (TX)0 : xk + akx * (xk - xo[c]) + ckx * z;
-          xout[c * ld + row] = xn;
+          outv[c] = xn;
+          if (!PK) xout[c * ld + row] = xn;
           if (x64) x64[c * ld + row] += (double)xn;
         } else {
-          const TX xk = __ldg(&xin[c * ld + row]);
+          const TX xk = xkv[c];
           const TX xn = fix ? xk : xk + (MODE == CHEB_FIRST ? (TX)0 : akx * (xk - xo[c])) + ckx * z;
           xout[c * ld + row] = xn;
         }
-        if (MIX != MIX_IT) {
+        if (!IS_IT) {
           if (MODE != CHEB_PLAIN) sum[c] = fma((double)r, (double)z, sum[c]);
           if (MODE == CHEB_FIRST) sum[CG + c] = fix ? sum[CG + c] : fma((double)(bv[c] * di), (double)bv[c], sum[CG + c]);
         }
       }
+      if (PK) {
+        const float4 o = make_float4((float)outv[0], (float)outv[1 % CG], (float)outv[2 % CG], 0.f);
+        if (IS_RES) reinterpret_cast<float4*>(f_d)[row] = o;
+        else reinterpret_cast<float4*>(xout)[row] = o;
+      }
     }
   }
-  if (MODE == CHEB_PLAIN || MIX == MIX_IT) return;
+  if (MODE == CHEB_PLAIN || IS_IT) return;
   cheb_grid_reduce<C, CG, SPB, MODE, LOCAL, NS>(sum, k, rtol, atol, flags, partials, counter, scal);
 }
 
@@ -552,7 +603,7 @@ static int cheb_soa(mv_mesh* m, const double* val, const double* dinv, const dou
 // ======================================================================================================
 enum { MK_RES_FIRST = 0, MK_RES_CHECK = 1, MK_IT = 2, MK_IT_FIRST = 3 };
 
-template <int C, int CG, int SPB, int MINB, int KIND, bool LAST, bool LOCAL>
+template <int C, int CG, int SPB, int MINB, int KIND, bool LAST, bool LOCAL, bool PK = false>
 __global__ void __launch_bounds__(32 * (C / CG) * SPB, MINB)
 k_mcheb(const int* __restrict__ sched, int64_t ngroups, int64_t nrows, const int64_t* __restrict__ slice_ptr, const int* __restrict__ cols,
         const double* __restrict__ val64, const float* __restrict__ val32, const double* __restrict__ dinv64,
@@ -568,6 +619,8 @@ k_mcheb(const int* __restrict__ sched, int64_t ngroups, int64_t nrows, const int
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int g = wid % NG, sl = wid / NG;
   const int64_t cb = (int64_t)g * CG * ld;
+  const int64_t cb4 = (int64_t)g * 4 * ld;   // PK: the single-precision iterates are [C/3][ld] float4 (three components + pad)
+  static_assert(!PK || CG == 3, "packed iterates carry three components per float4");
   double sum[NS];
 #pragma unroll
   for (int c = 0; c < NS; ++c) sum[c] = 0.0;
@@ -611,26 +664,34 @@ k_mcheb(const int* __restrict__ sched, int64_t ngroups, int64_t nrows, const int
         }
       }
       if (live) {
+        float d1[CG];
 #pragma unroll
         for (int c = 0; c < CG; ++c) {
           const bool fix = (mk >> c) & 1u;
           const double r = fix ? 0.0 : bv[c] - acc[c];
           const double z = di * r;
           r32[cb + c * ld + row] = (float)r;
-          dout[cb + c * ld + row] = (float)(ck * z);
+          d1[c] = (float)(ck * z);
+          if (!PK) dout[cb + c * ld + row] = d1[c];
           sum[c] = fma(r, z, sum[c]);
           if (KIND == MK_RES_FIRST) sum[CG + c] = fix ? sum[CG + c] : fma(bv[c] * di, bv[c], sum[CG + c]);
         }
+        if (PK) reinterpret_cast<float4*>(dout + cb4)[row] = make_float4(d1[0], d1[1 % CG], d1[2 % CG], 0.f);
       }
     } else {
       // ---- fp32 Chebyshev iteration on the correction: d_{j+1} = d_j + a (d_j - d_{j-1}) + c D^-1 (r - M d_j)
       const float* vp = val32 + base + lane;
-      const float* dg = din + cb;
+      const float* dg = din + (PK ? cb4 : cb);
+      const float4* dg4 = reinterpret_cast<const float4*>(dg);
       float rv[CG], dp[CG];
 #pragma unroll
-      for (int c = 0; c < CG; ++c) {
-        rv[c] = __ldcs(&r32[cb + c * ld + rr]);
-        dp[c] = KIND == MK_IT_FIRST ? 0.0f : __ldcs(&dout[cb + c * ld + rr]);
+      for (int c = 0; c < CG; ++c) rv[c] = __ldcs(&r32[cb + c * ld + rr]);
+      if (PK) {
+        const float4 t = KIND == MK_IT_FIRST ? make_float4(0.f, 0.f, 0.f, 0.f) : __ldcs(reinterpret_cast<const float4*>(dout + cb4) + rr);
+        dp[0] = t.x; dp[1 % CG] = t.y; dp[2 % CG] = t.z;
+      } else {
+#pragma unroll
+        for (int c = 0; c < CG; ++c) dp[c] = KIND == MK_IT_FIRST ? 0.0f : __ldcs(&dout[cb + c * ld + rr]);
       }
       const float di = __ldg(&dinv32[rr]);
       float acc[CG];
@@ -646,23 +707,45 @@ k_mcheb(const int* __restrict__ sched, int64_t ngroups, int64_t nrows, const int
           col[j] = in ? (NG > 1 ? __ldg(cp + (k0 + j) * MV_SLICE) : __ldcs(cp + (k0 + j) * MV_SLICE)) : 0;
           a[j] = in ? (NG > 1 ? __ldg(vp + (k0 + j) * MV_SLICE) : __ldcs(vp + (k0 + j) * MV_SLICE)) : 0.0f;
         }
+        if (PK) {
+          float4 xv[KB];
 #pragma unroll
-        for (int j = 0; j < KB; ++j) {
-          const float* xp = dg + col[j];
+          for (int j = 0; j < KB; ++j) xv[j] = __ldg(dg4 + col[j]);   // one 128-bit gather per neighbour
 #pragma unroll
-          for (int c = 0; c < CG; ++c) acc[c] = fmaf(a[j], __ldg(xp + c * ld), acc[c]);
+          for (int j = 0; j < KB; ++j) {
+            acc[0] = fmaf(a[j], xv[j].x, acc[0]);
+            acc[1 % CG] = fmaf(a[j], xv[j].y, acc[1 % CG]);
+            acc[2 % CG] = fmaf(a[j], xv[j].z, acc[2 % CG]);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < KB; ++j) {
+            const float* xp = dg + col[j];
+#pragma unroll
+            for (int c = 0; c < CG; ++c) acc[c] = fmaf(a[j], __ldg(xp + c * ld), acc[c]);
+          }
         }
       }
       if (live) {
+        float dkv[CG], dnv[CG];
+        if (PK) {
+          const float4 t = __ldg(dg4 + row);
+          dkv[0] = t.x; dkv[1 % CG] = t.y; dkv[2 % CG] = t.z;
+        } else {
+#pragma unroll
+          for (int c = 0; c < CG; ++c) dkv[c] = __ldg(&dg[c * ld + row]);
+        }
 #pragma unroll
         for (int c = 0; c < CG; ++c) {
           const bool fix = (mk >> c) & 1u;
-          const float dk = __ldg(&dg[c * ld + row]);
+          const float dk = dkv[c];
           const float res = fix ? 0.0f : rv[c] - acc[c];
           const float dn = fix ? 0.0f : dk + akf * (dk - dp[c]) + ckf * (di * res);
-          dout[cb + c * ld + row] = dn;
+          dnv[c] = dn;
+          if (!PK) dout[cb + c * ld + row] = dn;
           if (LAST) x64[cb + c * ld + row] += (double)dn;
         }
+        if (PK) reinterpret_cast<float4*>(dout + cb4)[row] = make_float4(dnv[0], dnv[1 % CG], dnv[2 % CG], 0.f);
       }
     }
   }
@@ -683,8 +766,10 @@ static int ensure_mixed_buffers(mv_mesh* m, const double* val, const double* din
   const size_t maxc = (size_t)m->dim * m->dim;
   if (!w.f32[0]) {
     for (int i = 0; i < 3; ++i) {
-      MV_CHECK(dev_alloc(&w.f32[i], (size_t)m->V * maxc));
-      MV_CUDA(cudaMemsetAsync(w.f32[i], 0, (size_t)m->V * maxc * sizeof(float), g_stream));
+      // room for the packed layout of the iterates: ceil(maxc / 3) float4 per vertex
+      const size_t per_vertex = ((maxc + 2) / 3) * 4 > maxc ? ((maxc + 2) / 3) * 4 : maxc;
+      MV_CHECK(dev_alloc(&w.f32[i], (size_t)m->V * per_vertex));
+      MV_CUDA(cudaMemsetAsync(w.f32[i], 0, (size_t)m->V * per_vertex * sizeof(float), g_stream));
     }
   }
   if (w.f32_src != val) {     // single-precision copy of the operator the sweeps stream (one per mesh: the mass matrix)
@@ -698,7 +783,7 @@ static int ensure_mixed_buffers(mv_mesh* m, const double* val, const double* din
   return MV_OK;
 }
 
-template <int C, int CG, int SPB, int MINB>
+template <int C, int CG, int SPB, int MINB, bool PK = false>
 struct MChebLaunch {
   static int run(mv_mesh* m, int kind, bool last, bool local, const double* val, const double* dinv, const uint16_t* mask, const double* b,
                  double* x64, float* r32, const float* din, float* dout, int64_t ld, double ak, double ck, int k, double rtol, double atol) {
@@ -710,7 +795,7 @@ struct MChebLaunch {
     static int per_sm = 0;
     if (per_sm == 0) {
       int nb = 0;
-      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_mcheb<C, CG, SPB, MINB, MK_IT, false, true>, NT, 0) != cudaSuccess || nb < 1) nb = 1;
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_mcheb<C, CG, SPB, MINB, MK_IT, false, true, PK>, NT, 0) != cudaSuccess || nb < 1) nb = 1;
       per_sm = nb;
     }
     int64_t g = (int64_t)g_nsm * per_sm;
@@ -718,7 +803,7 @@ struct MChebLaunch {
     if (g > ngroups) g = ngroups;
     const int gr = (int)(g < 1 ? 1 : g);
 #define MCHEB_GO(KIND, LASTF, LOC)                                                                                                       \
-  MV_L k_mcheb<C, CG, SPB, MINB, KIND, LASTF, LOC><<<gr, NT, 0, g_stream>>>(p.sched, ngroups, p.nrows, p.slice_ptr, p.cols, val, w.valf, dinv,  \
+  MV_L k_mcheb<C, CG, SPB, MINB, KIND, LASTF, LOC, PK><<<gr, NT, 0, g_stream>>>(p.sched, ngroups, p.nrows, p.slice_ptr, p.cols, val, w.valf, dinv,  \
                                                                        w.dinvf, mask, b, x64, r32, din, dout, ld, ak, ck, k, rtol, atol,  \
                                                                        w.flags, m->red.partials, m->red.counter, w.scal)
     if (kind == MK_RES_FIRST) { if (local) MCHEB_GO(MK_RES_FIRST, false, true); else MCHEB_GO(MK_RES_FIRST, false, false); }
@@ -734,7 +819,8 @@ struct MChebLaunch {
 // the TMA-staged kernel in its two mixed-precision roles
 template <int C, int CG, int SPB, int MINB, int NST, int MIX>
 struct MixTmaLaunch {
-  using TV = typename std::conditional<MIX == MIX_IT, float, double>::type;
+  static constexpr bool IT = MIX == MIX_IT || MIX == MIX_IT4;
+  using TV = typename std::conditional<IT, float, double>::type;
   static bool fits(const mv_mesh* m) { return (size_t)NST * SPB * m->pat.maxw * MV_SLICE * (sizeof(TV) + sizeof(int)) <= 200 * 1024; }
   // MIX_RES: b, xin double, mode CHEB_FIRST / CHEB_CHECK;  MIX_IT: b = r32, xin / xout the float iterates, first: previous iterate zero
   static int run(mv_mesh* m, int mode, bool local, const uint16_t* mask, const void* b, const void* xin, void* xout, float* f_r, float* f_d,
@@ -752,7 +838,7 @@ struct MixTmaLaunch {
       if (smem > 48 * 1024) {
         MV_CUDA(cudaFuncSetAttribute(MIX_K(CHEB_PLAIN, true), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         MV_CUDA(cudaFuncSetAttribute(MIX_K(CHEB_FIRST, true), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        if (MIX == MIX_RES) {
+        if (!IT) {
           MV_CUDA(cudaFuncSetAttribute(MIX_K(CHEB_CHECK, true), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
           MV_CUDA(cudaFuncSetAttribute(MIX_K(CHEB_CHECK, false), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
           MV_CUDA(cudaFuncSetAttribute(MIX_K(CHEB_FIRST, false), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -767,13 +853,13 @@ struct MixTmaLaunch {
     if (g > MV_MAX_BLOCKS) g = MV_MAX_BLOCKS;
     if (g > ngroups) g = ngroups;
     const int gr = (int)(g < 1 ? 1 : g);
-    const TV* valt = MIX == MIX_IT ? reinterpret_cast<const TV*>(w.valf) : reinterpret_cast<const TV*>(val);
-    const TV* dinvt = MIX == MIX_IT ? reinterpret_cast<const TV*>(w.dinvf) : reinterpret_cast<const TV*>(dinv);
+    const TV* valt = IT ? reinterpret_cast<const TV*>(w.valf) : reinterpret_cast<const TV*>(val);
+    const TV* dinvt = IT ? reinterpret_cast<const TV*>(w.dinvf) : reinterpret_cast<const TV*>(dinv);
 #define MIX_GO(MODE, LOC)                                                                                                                \
   MV_L MIX_K(MODE, LOC)<<<gr, NT, smem, g_stream>>>(p.sched, ngroups, p.nrows, p.slice_ptr, p.cols, valt, dinvt, mask, static_cast<const TV*>(b), \
                                                     static_cast<const TV*>(xin), static_cast<TV*>(xout), ld, ak, ck, k, rtol, atol, w.flags, \
                                                     m->red.partials, m->red.counter, w.scal, p.maxw, f_r, f_d, x64)
-    if (MIX == MIX_IT) { if (mode == CHEB_FIRST) MIX_GO(CHEB_FIRST, true); else MIX_GO(CHEB_PLAIN, true); }
+    if (IT) { if (mode == CHEB_FIRST) MIX_GO(CHEB_FIRST, true); else MIX_GO(CHEB_PLAIN, true); }
     else if (mode == CHEB_FIRST) { if (local) MIX_GO(CHEB_FIRST, true); else MIX_GO(CHEB_FIRST, false); }
     else { if (local) MIX_GO(CHEB_CHECK, true); else MIX_GO(CHEB_CHECK, false); }
 #undef MIX_GO
@@ -810,6 +896,17 @@ static int cheb_mixed(mv_mesh* m, const double* val, const double* dinv, const d
   else MV_CUDA(cudaMemsetAsync(bs, 0, (size_t)ld * C * sizeof(double), g_stream));
   MV_CUDA(cudaMemsetAsync(w.flags, 0, 4 * sizeof(int), g_stream));
 
+  // packed single-precision iterates (three components + pad per float4, one 128-bit gather per neighbour): whenever the
+  // launch shapes carry three components per warp; on several GPUs only if the peer-memory halo exchange can carry them
+  constexpr bool CAN_PK = C % 3 == 0 && RCG == 3 && ICG == 3;
+  constexpr int NGRP = C / 3 > 0 ? C / 3 : 1;
+  // measured at 256^3 (round 2): C = 9 iteration 1.50 -> 1.28 ms packed; C = 3 0.58 -> 0.59 ms (already at 0.8 of the HBM
+  // peak, the pad only adds bytes), so three-component solves stay component-major unless MV_CHEB_PACK=2
+  int pack_env = C >= 9 ? 1 : 0;
+  { const char* e = getenv("MV_CHEB_PACK"); if (e) pack_env = atoi(e) == 2 ? 1 : (atoi(e) == 0 ? 0 : pack_env); }
+  const bool pk = CAN_PK && pack_env && (!dist || (m->halo.nn > 0 && 2 * NGRP <= m->halo.p2p_maxC) || m->halo.nn == 0);
+  constexpr int RES_MIX = CAN_PK ? MIX_RES4 : MIX_RES, IT_MIX = CAN_PK ? MIX_IT4 : MIX_IT;
+
   int cycle = 0, its32 = 0, passes = 0;
   bool done = false, breakdown = false;
   while (true) {
@@ -817,12 +914,20 @@ static int cheb_mixed(mv_mesh* m, const double* val, const double* dinv, const d
     if (dist) MV_CHECK(halo_exchange_soa(m->halo, n, C, X, ld));
     {
       const int pslot = prof_begin(C + 4);
-      if (RNST > 0 && MixTmaLaunch<C, RCG, RSPB, RMINB, RNST ? RNST : 2, MIX_RES>::fits(m))
-        MV_CHECK((MixTmaLaunch<C, RCG, RSPB, RMINB, RNST ? RNST : 2, MIX_RES>::run(m, cycle == 0 ? CHEB_FIRST : CHEB_CHECK, !dist, mask, bs, X, nullptr, r32, D[1],
-                                                                        nullptr, val, dinv, ld, 0.0, 1.0 / theta, cycle, rtol, atol)));
-      else
+      if (RNST > 0 && MixTmaLaunch<C, RCG, RSPB, RMINB, RNST ? RNST : 2, MIX_RES>::fits(m)) {
+        if (pk)
+          MV_CHECK((MixTmaLaunch<C, RCG, RSPB, RMINB, RNST ? RNST : 2, RES_MIX>::run(m, cycle == 0 ? CHEB_FIRST : CHEB_CHECK, !dist, mask, bs, X, nullptr, r32, D[1],
+                                                                          nullptr, val, dinv, ld, 0.0, 1.0 / theta, cycle, rtol, atol)));
+        else
+          MV_CHECK((MixTmaLaunch<C, RCG, RSPB, RMINB, RNST ? RNST : 2, MIX_RES>::run(m, cycle == 0 ? CHEB_FIRST : CHEB_CHECK, !dist, mask, bs, X, nullptr, r32, D[1],
+                                                                          nullptr, val, dinv, ld, 0.0, 1.0 / theta, cycle, rtol, atol)));
+      } else if (pk) {
+        MV_CHECK((MChebLaunch<C, RCG, RSPB, RMINB, CAN_PK>::run(m, cycle == 0 ? MK_RES_FIRST : MK_RES_CHECK, false, !dist, val, dinv, mask, bs, X, r32,
+                                                                nullptr, D[1], ld, 0.0, 1.0 / theta, cycle, rtol, atol)));
+      } else {
         MV_CHECK((MChebLaunch<C, RCG, RSPB, RMINB>::run(m, cycle == 0 ? MK_RES_FIRST : MK_RES_CHECK, false, !dist, val, dinv, mask, bs, X, r32,
                                                         nullptr, D[1], ld, 0.0, 1.0 / theta, cycle, rtol, atol)));
+      }
       prof_end(pslot);
     }
     ++passes;
@@ -855,14 +960,25 @@ static int cheb_mixed(mv_mesh* m, const double* val, const double* dinv, const d
       const double rk = 1.0 / (2.0 * sigma1 - rho);
       const double ak = rk * rho, ck = 2.0 * rk / delta;
       rho = rk;
-      if (dist) MV_CHECK(halo_exchange_soa_f32(m->halo, n, C, D[cur], ld));
+      if (dist) {
+        if (pk) { if (m->halo.nn > 0) MV_CHECK(p2p_halo_exchange_f32_packed4(m->halo, n, NGRP, D[cur], ld, nullptr)); }
+        else MV_CHECK(halo_exchange_soa_f32(m->halo, n, C, D[cur], ld));
+      }
       const int pslot = prof_begin(C);
-      if (INST > 0 && MixTmaLaunch<C, ICG, ISPB, IMINB, INST ? INST : 2, MIX_IT>::fits(m))
-        MV_CHECK((MixTmaLaunch<C, ICG, ISPB, IMINB, INST ? INST : 2, MIX_IT>::run(m, j == 1 ? CHEB_FIRST : CHEB_PLAIN, true, mask, r32, D[cur], D[cur ^ 1], nullptr,
-                                                                       nullptr, j == k - 1 ? X : nullptr, val, dinv, ld, ak, ck, cycle, rtol, atol)));
-      else
+      if (INST > 0 && MixTmaLaunch<C, ICG, ISPB, IMINB, INST ? INST : 2, MIX_IT>::fits(m)) {
+        if (pk)
+          MV_CHECK((MixTmaLaunch<C, ICG, ISPB, IMINB, INST ? INST : 2, IT_MIX>::run(m, j == 1 ? CHEB_FIRST : CHEB_PLAIN, true, mask, r32, D[cur], D[cur ^ 1], nullptr,
+                                                                         nullptr, j == k - 1 ? X : nullptr, val, dinv, ld, ak, ck, cycle, rtol, atol)));
+        else
+          MV_CHECK((MixTmaLaunch<C, ICG, ISPB, IMINB, INST ? INST : 2, MIX_IT>::run(m, j == 1 ? CHEB_FIRST : CHEB_PLAIN, true, mask, r32, D[cur], D[cur ^ 1], nullptr,
+                                                                         nullptr, j == k - 1 ? X : nullptr, val, dinv, ld, ak, ck, cycle, rtol, atol)));
+      } else if (pk) {
+        MV_CHECK((MChebLaunch<C, ICG, ISPB, IMINB, CAN_PK>::run(m, j == 1 ? MK_IT_FIRST : MK_IT, j == k - 1, true, val, dinv, mask, bs, X, r32, D[cur],
+                                                                D[cur ^ 1], ld, ak, ck, cycle, rtol, atol)));
+      } else {
         MV_CHECK((MChebLaunch<C, ICG, ISPB, IMINB>::run(m, j == 1 ? MK_IT_FIRST : MK_IT, j == k - 1, true, val, dinv, mask, bs, X, r32, D[cur],
                                                         D[cur ^ 1], ld, ak, ck, cycle, rtol, atol)));
+      }
       prof_end(pslot);
       cur ^= 1;
     }
@@ -923,6 +1039,14 @@ int cheb_mass_solve(mv_mesh* m, int ncomp, const double* val, const double* dinv
         if (var == 14) return cheb_mixed<9, 3, 4, 3, 2, 9, 8, 2, 2>(CHEB_ARGS);
         if (var == 15) return cheb_mixed<9, 3, 4, 3, 2, 3, 8, 2, 2>(CHEB_ARGS);
         if (var == 16) return cheb_mixed<9, 3, 4, 3, 2, 1, 2, 3, 2>(CHEB_ARGS);
+        if (var == 31) return cheb_mixed<9, 3, 4, 3, 2, 3, 4, 4, 2>(CHEB_ARGS);
+        if (var == 32) return cheb_mixed<9, 3, 4, 3, 2, 3, 8, 2, 2>(CHEB_ARGS);
+        if (var == 33) return cheb_mixed<9, 3, 4, 3, 2, 3, 2, 6, 2>(CHEB_ARGS);
+        if (var == 34) return cheb_mixed<9, 3, 4, 3, 2, 3, 4, 3, 0>(CHEB_ARGS);
+        if (var == 35) return cheb_mixed<9, 3, 4, 3, 2, 3, 2, 8, 2>(CHEB_ARGS);
+        if (var == 36) return cheb_mixed<9, 3, 4, 3, 2, 3, 4, 3, 3>(CHEB_ARGS);
+        if (var == 37) return cheb_mixed<9, 3, 4, 3, 2, 3, 8, 2, 0>(CHEB_ARGS);
+        if (var == 38) return cheb_mixed<9, 3, 4, 3, 2, 3, 4, 4, 0>(CHEB_ARGS);
         return cheb_mixed<9, 3, 4, 3, 2, 3, 4, 3, 2>(CHEB_ARGS);
     }
   }

@@ -280,8 +280,9 @@ struct mv_ma {
   double* a = nullptr;          // [V] assembled int psi m det(I+H)
   double* dphi = nullptr;       // [V]
   // the two previous Poisson solves (update, right-hand side): Galerkin initial guess of the next one
-  double* hist_x[8] = {nullptr};   // [V] K-orthonormal basis of the previous updates, newest first
-  double* hist_b[8] = {nullptr};   // [V] K x_i
+  double* hist_x[8] = {nullptr};   // [V] previous updates, newest first
+  double* hist_b[8] = {nullptr};   // [V] their right-hand sides (= K x_i up to a constant)
+  double* hist_G = nullptr;        // [8*8] Gram matrix x_i . b_j
   int hist_n = 0;
   double* mon_raw = nullptr;    // [V]
   double* dscal = nullptr;      // device scalars
@@ -352,6 +353,7 @@ size_t p2p_slot_bytes();
 int p2p_halo_exchange(const Halo& h, int64_t nown, int C, double* vec, int64_t ld, bool soa, const int* done);
 int p2p_halo_exchange_f32(const Halo& h, int64_t nown, int C, float* vec, int64_t ld, const int* done);
 int halo_exchange_soa_f32(const Halo& h, int64_t nown, int C, float* vec, int64_t ld);
+int p2p_halo_exchange_f32_packed4(const Halo& h, int64_t nown, int groups, float* vec, int64_t ld, const int* done);
 bool p2p_allreduce_fits(int n);
 int p2p_allreduce(double* d, int n, int op, const int* done);
 int p2p_check_status();

@@ -606,6 +606,7 @@ extern "C" void mv_ma_destroy(mv_ma* ma) {
   if (ma->qn_hdots) cudaFreeHost(ma->qn_hdots);
   dev_free(ma->rhs); dev_free(ma->a); dev_free(ma->dphi); dev_free(ma->dscal); dev_free(ma->bc_mask);
   for (int i = 0; i < 8; ++i) { dev_free(ma->hist_x[i]); dev_free(ma->hist_b[i]); }
+  dev_free(ma->hist_G);
   if (ma->h_scal) cudaFreeHost(ma->h_scal);
   eqbc_free(ma);
   delete ma;
@@ -890,21 +891,22 @@ extern "C" int mv_ma_diagnostics(mv_ma* ma, int use_H_old, double* out) {
 }
 
 // Initial guess of the Poisson solve K x = b from the previous solves of the same mover: the Galerkin (energy-optimal)
-// combination over their span.  The history is kept as a K-ORTHONORMAL basis {(x_i, b_i = K x_i)}, x_i.b_j = delta_ij
-// (Gram-Schmidt in the energy inner product, which only needs the stored b_j: <x_i, y>_K = x_i.(K y) = b_i.y), so the
-// guess is x0 = sum_i (x_i.b) x_i -- no small system, no conditioning problem when consecutive solutions are nearly
-// parallel.  The right-hand side dt * (a - theta m_l) changes smoothly from one relaxation iteration to the next (a few
-// slowly decaying modes late in the run), so x0 is typically two to four digits accurate; the solve itself and its
-// stopping rule (rtol relative to b) are unchanged.  Depth: MV_POISSON_HISTORY (0 off, 1 = default depth, k >= 2 = k).
+// combination x0 = sum_i a_i x_i over the last m solutions, G a = f with G_ij = x_i.K x_j = x_i.b_j (the right-hand sides
+// b_j are kept, so no matrix pass is needed) and f_i = x_i.b.  G is kept on the device and only its newest row is computed
+// when a pair is added (m fused dot products); a solve costs m more for f and one combination pass.  The small system is
+// solved by Cholesky in the order newest -> oldest and truncated at the first pivot that is (numerically) zero, i.e. when
+// an older solution adds nothing to the span.  The right-hand side dt * (a - theta m_l) changes smoothly from one relaxation
+// iteration to the next, so x0 is typically two to three digits accurate; the solve itself and its stopping rule (rtol
+// relative to b) are unchanged.  Depth: MV_POISSON_HISTORY (0 off, 1 = default depth, k >= 2 = k).
 #define MV_HIST_MAX 8
-#define MV_HIST_DEFAULT 4
-enum { H_C = 8, H_S0 = 8 + MV_HIST_MAX, H_S1 = 9 + MV_HIST_MAX, H_END = 10 + MV_HIST_MAX };
+#define MV_HIST_DEFAULT 3
+enum { H_C = 8, H_S0 = 8 + MV_HIST_MAX, H_END = 9 + MV_HIST_MAX };
 static_assert((int)H_END <= (int)D_N, "history scalars must fit the device scalar block");
 struct HistPtrs {
   const double* x[MV_HIST_MAX];
   const double* b[MV_HIST_MAX];
 };
-// c_i = X_i . y for the m basis vectors (X = x or b side), s0 = z . y (optional)
+// c_i = X_i . y for the m stored vectors (X = x or b side), s0 = z . y (optional)
 template <int M>
 __global__ void __launch_bounds__(MV_BLOCK)
 k_hist_dots(int64_t n, HistPtrs h, int side_b, const double* __restrict__ y, const double* __restrict__ z,
@@ -924,13 +926,44 @@ k_hist_dots(int64_t n, HistPtrs h, int side_b, const double* __restrict__ y, con
     dscal[H_S0] = t[M];
   });
 }
-// x0 = sum_i c_i x_i
+// G a = f (m x m, newest first) by Cholesky, truncated at the first negligible pivot; a -> dscal[H_C..]
+__global__ void k_hist_solve(int m, const double* __restrict__ G, double* __restrict__ dscal) {
+  double Lm[MV_HIST_MAX][MV_HIST_MAX], y[MV_HIST_MAX], a[MV_HIST_MAX];
+  int mm = 0;
+  for (int j = 0; j < m; ++j) {
+    double d = G[j * MV_HIST_MAX + j];
+    for (int k = 0; k < j; ++k) d -= Lm[j][k] * Lm[j][k];
+    if (!(d > 1e-10 * G[j * MV_HIST_MAX + j]) || !(G[j * MV_HIST_MAX + j] > 0.0)) break;
+    Lm[j][j] = sqrt(d);
+    for (int i = j + 1; i < m; ++i) {
+      double t = G[i * MV_HIST_MAX + j];
+      for (int k = 0; k < j; ++k) t -= Lm[i][k] * Lm[j][k];
+      Lm[i][j] = t / Lm[j][j];
+    }
+    mm = j + 1;
+  }
+  for (int i = 0; i < mm; ++i) {
+    double t = dscal[H_C + i];
+    for (int k = 0; k < i; ++k) t -= Lm[i][k] * y[k];
+    y[i] = t / Lm[i][i];
+  }
+  for (int i = mm - 1; i >= 0; --i) {
+    double t = y[i];
+    for (int k = i + 1; k < mm; ++k) t -= Lm[k][i] * a[k];
+    a[i] = t / Lm[i][i];
+  }
+  for (int i = 0; i < MV_HIST_MAX; ++i) {
+    const double v = i < mm ? a[i] : 0.0;
+    dscal[H_C + i] = v == v ? v : 0.0;
+  }
+}
+// x0 = sum_i a_i x_i
 template <int M>
 __global__ void __launch_bounds__(MV_BLOCK)
 k_hist_guess(int64_t n, HistPtrs h, const double* __restrict__ dscal, double* __restrict__ x0) {
   double c[M > 0 ? M : 1];
 #pragma unroll
-  for (int i = 0; i < M; ++i) { c[i] = dscal[H_C + i]; if (!(c[i] == c[i])) c[i] = 0.0; }
+  for (int i = 0; i < M; ++i) c[i] = dscal[H_C + i];
   for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < n; v += (int64_t)gridDim.x * blockDim.x) {
     double a = 0.0;
 #pragma unroll
@@ -938,34 +971,12 @@ k_hist_guess(int64_t n, HistPtrs h, const double* __restrict__ dscal, double* __
     x0[v] = a;
   }
 }
-// (xn, bn) = (x, b) - sum_i c_i (x_i, b_i) ; s1 = xn . bn
-template <int M>
-__global__ void __launch_bounds__(MV_BLOCK)
-k_hist_orth(int64_t n, HistPtrs h, const double* __restrict__ x, const double* __restrict__ b, double* __restrict__ xn,
-            double* __restrict__ bn, double* __restrict__ partials, unsigned* __restrict__ counter, double* __restrict__ dscal) {
-  double c[M > 0 ? M : 1];
-#pragma unroll
-  for (int i = 0; i < M; ++i) c[i] = dscal[H_C + i];
-  double acc[1] = {0.0};
-  for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < n; v += (int64_t)gridDim.x * blockDim.x) {
-    double xv = x[v], bv = b[v];
-#pragma unroll
-    for (int i = 0; i < M; ++i) { xv = fma(-c[i], h.x[i][v], xv); bv = fma(-c[i], h.b[i][v], bv); }
-    xn[v] = xv;
-    bn[v] = bv;
-    acc[0] = fma(xv, bv, acc[0]);
-  }
-  grid_reduce_sum<1>(acc, partials, counter, [&](double(&t)[1]) { dscal[H_S1] = t[0]; });
-}
-// normalise the new pair in the energy norm; a direction that is (numerically) inside the span is stored as zero
-__global__ void __launch_bounds__(MV_BLOCK)
-k_hist_normalise(int64_t n, const double* __restrict__ dscal, double* __restrict__ xn, double* __restrict__ bn) {
-  const double s0 = dscal[H_S0], s1 = dscal[H_S1];
-  const double sc = (s1 > 0.0 && s0 > 0.0 && s1 > 1e-14 * s0) ? rsqrt(s1) : 0.0;
-  for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < n; v += (int64_t)gridDim.x * blockDim.x) {
-    xn[v] *= sc;
-    bn[v] *= sc;
-  }
+// the pair that was just stored becomes index 0: shift G by one and insert its row (dscal[H_S0] = x0.b0, dscal[H_C + i] = x0.b_{i+1})
+__global__ void k_hist_push(int keep, double* __restrict__ G, const double* __restrict__ dscal) {
+  for (int i = keep; i >= 1; --i)
+    for (int j = keep; j >= 1; --j) G[i * MV_HIST_MAX + j] = G[(i - 1) * MV_HIST_MAX + (j - 1)];
+  G[0] = dscal[H_S0];
+  for (int i = 1; i <= keep; ++i) G[i] = G[i * MV_HIST_MAX] = dscal[H_C + i - 1];
 }
 
 #define HIST_DISPATCH(m, ...)                                              \
@@ -999,12 +1010,17 @@ extern "C" int mv_ma_pseudotimestep(mv_ma* ma, double dt, int* iters) {
   if (g_poisson_history < 0) { const char* e = getenv("MV_POISSON_HISTORY"); mv_set_poisson_history(e ? atoi(e) : 1); }
   const int depth = g_poisson_history;
   HistPtrs hp;
-  const int mh = ma->hist_n < depth ? ma->hist_n : depth;   // basis vectors in use (the newest mh)
+  const int mh = ma->hist_n < depth ? ma->hist_n : depth;   // stored pairs in use (the newest mh)
   for (int i = 0; i < MV_HIST_MAX; ++i) { hp.x[i] = i < mh ? ma->hist_x[i] : nullptr; hp.b[i] = i < mh ? ma->hist_b[i] : nullptr; }
   const bool dist = comm_active();
+  if (depth > 0 && !ma->hist_G) {
+    MV_CHECK(dev_alloc(&ma->hist_G, MV_HIST_MAX * MV_HIST_MAX));
+    MV_CUDA(cudaMemsetAsync(ma->hist_G, 0, MV_HIST_MAX * MV_HIST_MAX * sizeof(double), g_stream));
+  }
   if (depth > 0 && mh > 0) {
     HIST_DISPATCH(mh, MV_L k_hist_dots<M><<<gv, MV_BLOCK, 0, g_stream>>>(n, hp, 0, ma->rhs, nullptr, m->red.partials, m->red.counter, ma->dscal));
     if (dist) MV_CHECK(allreduce_sum_dev(ma->dscal + H_C, mh));
+    MV_L k_hist_solve<<<1, 1, 0, g_stream>>>(mh, ma->hist_G, ma->dscal);
     HIST_DISPATCH(mh, MV_L k_hist_guess<M><<<gv, MV_BLOCK, 0, g_stream>>>(n, hp, ma->dscal, ma->dphi));
     MV_KERNEL_CHECK();
   } else {
@@ -1015,26 +1031,26 @@ extern "C" int mv_ma_pseudotimestep(mv_ma* ma, double dt, int* iters) {
   MV_L k_add<<<gv, MV_BLOCK, 0, g_stream>>>(n, ma->f[MV_F_PHI_OLD], ma->dphi, ma->f[MV_F_PHI]);
   MV_KERNEL_CHECK();
   if (depth > 0) {
-    // the new pair, K-orthonormalised against the basis, takes the place of the oldest one (slot depth-1 -> slot 0)
+    // the new pair takes the place of the oldest one (slot depth-1 -> slot 0); its row of G from the stored right-hand sides
     for (int i = 0; i < depth; ++i)
       if (!ma->hist_x[i]) {
         MV_CHECK(dev_alloc(&ma->hist_x[i], n));
         MV_CHECK(dev_alloc(&ma->hist_b[i], n));
       }
-    const int keep = mh < depth - 1 ? mh : depth - 1;   // basis vectors that survive
+    const int keep = mh < depth - 1 ? mh : depth - 1;   // older pairs that stay
     for (int i = 0; i < MV_HIST_MAX; ++i) { if (i >= keep) { hp.x[i] = nullptr; hp.b[i] = nullptr; } }
-    double* xn = ma->hist_x[depth - 1];
-    double* bn = ma->hist_b[depth - 1];
-    // c_i = b_i . x_new = <x_i, x_new>_K ;  s0 = b . x_new   (b = the projected right-hand side up to its mean, and x_new has zero mean)
+    // x_new . b_i (i kept) and x_new . b_new; x_new has zero mean, so the mean of the right-hand sides drops out
     HIST_DISPATCH(keep, MV_L k_hist_dots<M><<<gv, MV_BLOCK, 0, g_stream>>>(n, hp, 1, ma->dphi, ma->rhs, m->red.partials, m->red.counter, ma->dscal));
     if (dist) MV_CHECK(allreduce_sum_dev(ma->dscal + H_C, MV_HIST_MAX + 1));
-    HIST_DISPATCH(keep, MV_L k_hist_orth<M><<<gv, MV_BLOCK, 0, g_stream>>>(n, hp, ma->dphi, ma->rhs, xn, bn, m->red.partials, m->red.counter, ma->dscal));
-    if (dist) MV_CHECK(allreduce_sum_dev(ma->dscal + H_S1, 1));
-    MV_L k_hist_normalise<<<gv, MV_BLOCK, 0, g_stream>>>(n, ma->dscal, xn, bn);
-    MV_KERNEL_CHECK();
+    MV_L k_hist_push<<<1, 1, 0, g_stream>>>(keep, ma->hist_G, ma->dscal);
+    double* xn = ma->hist_x[depth - 1];
+    double* bn = ma->hist_b[depth - 1];
     for (int i = depth - 1; i > 0; --i) { ma->hist_x[i] = ma->hist_x[i - 1]; ma->hist_b[i] = ma->hist_b[i - 1]; }
     ma->hist_x[0] = xn;
     ma->hist_b[0] = bn;
+    MV_CUDA(cudaMemcpyAsync(xn, ma->dphi, n * sizeof(double), cudaMemcpyDeviceToDevice, g_stream));
+    MV_CUDA(cudaMemcpyAsync(bn, ma->rhs, n * sizeof(double), cudaMemcpyDeviceToDevice, g_stream));
+    MV_KERNEL_CHECK();
     if (ma->hist_n < depth) ++ma->hist_n;
   }
   return MV_OK;

@@ -76,7 +76,8 @@ struct HaloArgs {
 };
 
 // vec: component-major [C][ld] (SOA) or interleaved [ld][C]; owned rows [0, nown), ghosts after.
-template <bool SOA, typename T>
+// LAYOUT 2: packed groups of four, [C/4][ld][4] (the float4 iterates of the mixed-precision Chebyshev sweeps, mv_cheb.cu)
+template <int LAYOUT, typename T>
 __global__ void __launch_bounds__(MV_BLOCK)
 k_p2p_halo(HaloArgs h, int me, int C, const int* __restrict__ send_idx, T* __restrict__ vec, int64_t ld, int64_t nown,
            unsigned char* __restrict__ mywin, P2PWindowLayout lay, unsigned long long* __restrict__ seq,
@@ -96,7 +97,7 @@ k_p2p_halo(HaloArgs h, int me, int C, const int* __restrict__ send_idx, T* __res
     for (int64_t i = tid; i < tot; i += nth) {
       const int64_t c = i / ns, t = i - c * ns;
       const int64_t v = __ldg(&idx[t]);
-      dst[i] = SOA ? vec[c * ld + v] : vec[v * C + c];
+      dst[i] = LAYOUT == 1 ? vec[c * ld + v] : (LAYOUT == 0 ? vec[v * C + c] : vec[((c >> 2) * ld + v) * 4 + (c & 3)]);
     }
   }
   // 2. the last CTA to finish its stores releases the flags
@@ -129,8 +130,9 @@ k_p2p_halo(HaloArgs h, int me, int C, const int* __restrict__ send_idx, T* __res
     for (int64_t i = tid; i < tot; i += nth) {
       const int64_t c = i / nr, t = i - c * nr;
       const T val = __ldcv(&src[i]);      // written by the peer: never from a stale cache line
-      if (SOA) vec[c * ld + g0 + t] = val;
-      else vec[(g0 + t) * C + c] = val;
+      if (LAYOUT == 1) vec[c * ld + g0 + t] = val;
+      else if (LAYOUT == 0) vec[(g0 + t) * C + c] = val;
+      else vec[((c >> 2) * ld + g0 + t) * 4 + (c & 3)] = val;
     }
     __syncthreads();
   }
@@ -271,7 +273,7 @@ void p2p_finalize() {
 size_t p2p_slot_bytes() { return g_p2p.on ? g_p2p.lay.slot_bytes : 0; }
 
 template <typename T>
-static int p2p_halo_exchange_t(const Halo& h, int64_t nown, int C, T* vec, int64_t ld, bool soa, const int* done) {
+static int p2p_halo_exchange_t(const Halo& h, int64_t nown, int C, T* vec, int64_t ld, int layout, const int* done) {
   P2P& p = g_p2p;
   HaloArgs a;
   a.nn = h.nn;
@@ -288,20 +290,26 @@ static int p2p_halo_exchange_t(const Halo& h, int64_t nown, int C, T* vec, int64
   const int cap = g_nsm > 0 ? g_nsm * 2 : 128;
   if (grid > cap) grid = cap;
   if (grid < 1) grid = 1;
-  if (soa)
-    MV_L k_p2p_halo<true, T><<<grid, MV_BLOCK, 0, g_stream>>>(a, p.rank, C, h.send_idx, vec, ld, nown, p.win, p.lay, p.seq, p.ticket, p.status, done);
+  if (layout == 1)
+    MV_L k_p2p_halo<1, T><<<grid, MV_BLOCK, 0, g_stream>>>(a, p.rank, C, h.send_idx, vec, ld, nown, p.win, p.lay, p.seq, p.ticket, p.status, done);
+  else if (layout == 0)
+    MV_L k_p2p_halo<0, T><<<grid, MV_BLOCK, 0, g_stream>>>(a, p.rank, C, h.send_idx, vec, ld, nown, p.win, p.lay, p.seq, p.ticket, p.status, done);
   else
-    MV_L k_p2p_halo<false, T><<<grid, MV_BLOCK, 0, g_stream>>>(a, p.rank, C, h.send_idx, vec, ld, nown, p.win, p.lay, p.seq, p.ticket, p.status, done);
+    MV_L k_p2p_halo<2, T><<<grid, MV_BLOCK, 0, g_stream>>>(a, p.rank, C, h.send_idx, vec, ld, nown, p.win, p.lay, p.seq, p.ticket, p.status, done);
   MV_KERNEL_CHECK();
   ++p.n_halo;
   return MV_OK;
 }
 
 int p2p_halo_exchange(const Halo& h, int64_t nown, int C, double* vec, int64_t ld, bool soa, const int* done) {
-  return p2p_halo_exchange_t<double>(h, nown, C, vec, ld, soa, done);
+  return p2p_halo_exchange_t<double>(h, nown, C, vec, ld, soa ? 1 : 0, done);
 }
 int p2p_halo_exchange_f32(const Halo& h, int64_t nown, int C, float* vec, int64_t ld, const int* done) {
-  return p2p_halo_exchange_t<float>(h, nown, C, vec, ld, true, done);
+  return p2p_halo_exchange_t<float>(h, nown, C, vec, ld, 1, done);
+}
+// packed float4 groups: C = 4 * groups values per vertex, [groups][ld][4]
+int p2p_halo_exchange_f32_packed4(const Halo& h, int64_t nown, int groups, float* vec, int64_t ld, const int* done) {
+  return p2p_halo_exchange_t<float>(h, nown, 4 * groups, vec, ld, 2, done);
 }
 
 int p2p_allreduce(double* d, int n, int op, const int* done) {

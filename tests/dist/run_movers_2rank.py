@@ -82,10 +82,14 @@ def main():
     mv.mover._print = mv.laplacian_smoothing._print = mv.spring._print = mv.monge_ampere._print = lambda *a, **k: None
     e_lap = forced("laplacian", 12, 4)
     e_spr = forced("spring", 10, 4)
+    # the same with the assembled blocks + block-diagonal multigrid preconditioner (default from 4096 vertices on)
+    os.environ["MV_SPRING_AMG_MIN"] = "16"
+    e_spr_mg = forced("spring", 40, 3)
+    os.environ.pop("MV_SPRING_AMG_MIN")
     nit, ref_nit, e_qn = quasi_newton(20)
-    ok = e_lap < 1e-10 and e_spr < 1e-10 and abs(nit - ref_nit) <= 1 and e_qn < 1e-10
+    ok = e_lap < 1e-10 and e_spr < 1e-10 and e_spr_mg < 1e-10 and abs(nit - ref_nit) <= 1 and e_qn < 1e-10
     if rank == 0:
-        print(f"laplacian {e_lap:.3e}  spring {e_spr:.3e}  quasi-newton its {nit} vs {ref_nit}, x {e_qn:.3e}")
+        print(f"laplacian {e_lap:.3e}  spring {e_spr:.3e}  spring(multigrid) {e_spr_mg:.3e}  quasi-newton its {nit} vs {ref_nit}, x {e_qn:.3e}")
         print("DIST-MOVERS-OK" if ok else "DIST-MOVERS-FAIL", flush=True)
     parallel.finalize()
     sys.exit(0 if ok else 1)
