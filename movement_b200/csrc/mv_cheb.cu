@@ -1047,7 +1047,19 @@ int cheb_mass_solve(mv_mesh* m, int ncomp, const double* val, const double* dinv
         if (var == 36) return cheb_mixed<9, 3, 4, 3, 2, 3, 4, 3, 3>(CHEB_ARGS);
         if (var == 37) return cheb_mixed<9, 3, 4, 3, 2, 3, 8, 2, 0>(CHEB_ARGS);
         if (var == 38) return cheb_mixed<9, 3, 4, 3, 2, 3, 4, 4, 0>(CHEB_ARGS);
-        return cheb_mixed<9, 3, 4, 3, 2, 3, 4, 3, 2>(CHEB_ARGS);
+        if (var == 39) return cheb_mixed<9, 3, 4, 3, 2, 3, 1, 12, 2>(CHEB_ARGS);
+        if (var == 40) return cheb_mixed<9, 3, 4, 3, 2, 3, 2, 7, 2>(CHEB_ARGS);
+        if (var == 41) return cheb_mixed<9, 3, 4, 3, 2, 3, 2, 6, 3>(CHEB_ARGS);
+        if (var == 42) return cheb_mixed<9, 3, 4, 3, 2, 3, 1, 10, 2>(CHEB_ARGS);
+        if (var == 43) return cheb_mixed<9, 3, 4, 3, 2, 3, 2, 5, 2>(CHEB_ARGS);
+        if (var == 44) return cheb_mixed<9, 3, 2, 6, 2, 3, 2, 6, 2>(CHEB_ARGS);
+        if (var == 45) return cheb_mixed<9, 3, 2, 5, 2, 3, 2, 6, 2>(CHEB_ARGS);
+        if (var == 46) return cheb_mixed<9, 3, 1, 10, 2, 3, 1, 12, 2>(CHEB_ARGS);
+        // measured at 256^3, cold start to 1e-12 (33 matrix passes), packed iterates: iteration shape <3,4,3,2> (12 warps per CTA,
+        // 3 CTAs/SM) 43.5 ms per solve, barrier stall 3.9 per issue (ncu); <3,2,6,2> (6 warps per CTA, 6 CTAs/SM) 39.1;
+        // <3,1,10..12,2> 39.0; plain loads instead of the TMA stage 54-70 (profiles/r2_cheb9_variants.txt)
+        if (var == 30) return cheb_mixed<9, 3, 4, 3, 2, 3, 4, 3, 2>(CHEB_ARGS);
+        return cheb_mixed<9, 3, 4, 3, 2, 3, 2, 6, 2>(CHEB_ARGS);
     }
   }
   switch (ncomp) {

@@ -77,7 +77,7 @@ void prof_drain();           // stream must be synchronised
 // phases (ingest, multigrid hierarchy) allocate and drop gigabytes of temporaries, and with cudaMalloc/cudaFree
 // every free synchronised the device and every second mover paid the driver for the same pages again (multigrid
 // set-up 260 ms for the first mover of a process, 680 ms for the next one, round 1).  The pool keeps up to
-// MV_POOL_KEEP_GB (default 32) of freed memory for reuse.
+// MV_POOL_KEEP_GB (default: half of the device memory) of freed memory for reuse.
 int pool_init();
 template <typename T>
 int dev_alloc(T** p, size_t n) {
@@ -284,6 +284,10 @@ struct mv_ma {
   double* hist_b[8] = {nullptr};   // [V] their right-hand sides (= K x_i up to a constant)
   double* hist_G = nullptr;        // [8*8] Gram matrix x_i . b_j
   int hist_n = 0;
+  // right-hand side of the next L2 projection, produced by the Hessian right-hand-side kernel inside mv_ma_relax_move
+  double* l2_rhs = nullptr;     // [V*d]
+  const double* l2_rhs_phi = nullptr;   // the phi buffer it was computed from
+  bool l2_rhs_valid = false, fuse_l2_rhs = false;
   double* mon_raw = nullptr;    // [V]
   double* dscal = nullptr;      // device scalars
   double* h_scal = nullptr;     // pinned
@@ -367,7 +371,7 @@ int allreduce_volstats_dev(double* dout);  // [0] sum, [1] max, [2] min
 int volume_stats_device(mv_mesh* m, const double* x, const double* mon, const double* vol0, double* volume,
                         double* dout, int64_t global_cells);
 int l2_rhs_dev(mv_mesh* m, const double* phi, double* b);
-int hess_rhs_dev(mv_mesh* m, const double* phi, double* c);
+int hess_rhs_dev(mv_mesh* m, const double* phi, double* c, double* l2_out = nullptr);
 int assemble_a_dev(mv_mesh* m, const double* mon, const double* H, double* a, double* dscal);
 int jac_A_dev(mv_mesh* m, const double* mon, const double* H, const double* dH, double sign, double* out);
 bool comm_active();

@@ -110,13 +110,17 @@ __global__ void __launch_bounds__(MV_BLOCK)
 k_hess_rhs(const double* __restrict__ xi, const int* __restrict__ cells, int dg, const int* __restrict__ v2c_ptr,
            const int* __restrict__ v2c, const int* __restrict__ v2f_ptr, const int* __restrict__ v2f,
            const int* __restrict__ bf_cell, const double* __restrict__ bf_normal, const double* __restrict__ bf_area,
-           int64_t nrows, const double* __restrict__ phi, double* __restrict__ out) {
+           int64_t nrows, const double* __restrict__ phi, double* __restrict__ out, double* __restrict__ l2_out) {
+  // l2_out != nullptr: also the right-hand side of the NEXT L2 projection of grad(phi) (k_l2_rhs, same phi, same cell
+  // geometry and cell gradients -- the same operations in the same order, so the same bits)
   for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < nrows; v += (int64_t)gridDim.x * blockDim.x) {
-    double acc[D][D];
+    double acc[D][D], acc1[D];
 #pragma unroll
-    for (int a = 0; a < D; ++a)
+    for (int a = 0; a < D; ++a) {
+      acc1[a] = 0.0;
 #pragma unroll
       for (int b = 0; b < D; ++b) acc[a][b] = 0.0;
+    }
     const int tb = __ldg(&v2c_ptr[v]), te = __ldg(&v2c_ptr[v + 1]);
     for (int t = tb; t < te; ++t) {
       const int entry = __ldg(&v2c[t]);
@@ -143,6 +147,9 @@ k_hess_rhs(const double* __restrict__ xi, const int* __restrict__ cells, int dg,
       for (int a = 0; a < D; ++a)
 #pragma unroll
         for (int b = 0; b < D; ++b) acc[a][b] -= g.vol * gl[b] * gk[a];
+      const double wgt = g.vol / (D + 1);
+#pragma unroll
+      for (int a = 0; a < D; ++a) acc1[a] = fma(wgt, gk[a], acc1[a]);
     }
     const int fb = __ldg(&v2f_ptr[v]), fe = __ldg(&v2f_ptr[v + 1]);
     for (int t = fb; t < fe; ++t) {
@@ -175,6 +182,10 @@ k_hess_rhs(const double* __restrict__ xi, const int* __restrict__ cells, int dg,
     for (int a = 0; a < D; ++a)
 #pragma unroll
       for (int b = 0; b < D; ++b) out[v * D * D + a * D + b] = acc[a][b];
+    if (l2_out) {
+#pragma unroll
+      for (int a = 0; a < D; ++a) l2_out[v * D + a] = acc1[a];
+    }
   }
 }
 
@@ -607,6 +618,7 @@ extern "C" void mv_ma_destroy(mv_ma* ma) {
   dev_free(ma->rhs); dev_free(ma->a); dev_free(ma->dphi); dev_free(ma->dscal); dev_free(ma->bc_mask);
   for (int i = 0; i < 8; ++i) { dev_free(ma->hist_x[i]); dev_free(ma->hist_b[i]); }
   dev_free(ma->hist_G);
+  dev_free(ma->l2_rhs);
   if (ma->h_scal) cudaFreeHost(ma->h_scal);
   eqbc_free(ma);
   delete ma;
@@ -749,10 +761,10 @@ int l2_rhs_dev(mv_mesh* m, const double* phi, double* b) {
   MV_KERNEL_CHECK();
   return MV_OK;
 }
-int hess_rhs_dev(mv_mesh* m, const double* phi, double* c) {
+int hess_rhs_dev(mv_mesh* m, const double* phi, double* c, double* l2_out) {
   const int grid = grid_for(m->Vown);
   MV_DISPATCH_DIM(m->dim, MV_L k_hess_rhs<DIM><<<grid, MV_BLOCK, 0, g_stream>>>(m->xi, m->cells, m->dg, m->v2c_ptr, m->v2c, m->v2f_ptr, m->v2f,
-                                                                           m->bf_cell, m->bf_normal, m->bf_area, m->Vown, phi, c));
+                                                                           m->bf_cell, m->bf_normal, m->bf_area, m->Vown, phi, c, l2_out));
   MV_KERNEL_CHECK();
   return MV_OK;
 }
@@ -811,9 +823,13 @@ extern "C" int mv_ma_l2_project(mv_ma* ma, int* iters) {
   MA_REQUIRE(ma, MV_F_GRAD_PHI);
   mv_mesh* m = ma->mesh;
   if (comm_active()) MV_CHECK(halo_exchange(m, 1, ma->f[MV_F_PHI_OLD]));
-  MV_CHECK(l2_rhs_dev(m, ma->f[MV_F_PHI_OLD], ma->rhs));
+  // inside mv_ma_relax_move the right-hand side came with the previous iteration's Hessian right-hand side (same phi)
+  const double* rhs = ma->rhs;
+  if (ma->l2_rhs_valid && ma->l2_rhs_phi == ma->f[MV_F_PHI_OLD]) rhs = ma->l2_rhs;
+  else MV_CHECK(l2_rhs_dev(m, ma->f[MV_F_PHI_OLD], ma->rhs));
+  ma->l2_rhs_valid = false;
   MV_CHECK(eqbc_apply(ma, ma->f[MV_F_PHI_OLD], ma->f[MV_F_GRAD_PHI]));   // EquationBC segments: boundary solve first, its values are data
-  MV_CHECK(pcg_solve(m, MV_OP_MASS, m->dim, ma->rhs, ma->f[MV_F_GRAD_PHI], ma->have_bc ? ma->bc_mask : nullptr, ma->rtol,
+  MV_CHECK(pcg_solve(m, MV_OP_MASS, m->dim, rhs, ma->f[MV_F_GRAD_PHI], ma->have_bc ? ma->bc_mask : nullptr, ma->rtol,
                      ma->atol, ma->maxit_mass, 0, iters, nullptr));
   if (comm_active()) MV_CHECK(halo_exchange(m, m->dim, ma->f[MV_F_GRAD_PHI]));
   return MV_OK;
@@ -1062,7 +1078,13 @@ extern "C" int mv_ma_equidistribute(mv_ma* ma, int* iters) {
   MA_REQUIRE(ma, MV_F_H);
   mv_mesh* m = ma->mesh;
   if (comm_active()) MV_CHECK(halo_exchange(m, 1, ma->f[MV_F_PHI]));
-  MV_CHECK(hess_rhs_dev(m, ma->f[MV_F_PHI], ma->rhs));
+  double* l2_out = nullptr;
+  if (ma->fuse_l2_rhs) {
+    if (!ma->l2_rhs) MV_CHECK(dev_alloc(&ma->l2_rhs, (size_t)m->V * m->dim));
+    l2_out = ma->l2_rhs;
+  }
+  MV_CHECK(hess_rhs_dev(m, ma->f[MV_F_PHI], ma->rhs, l2_out));
+  ma->l2_rhs_phi = l2_out ? ma->f[MV_F_PHI] : nullptr;
   MV_CHECK(pcg_solve(m, MV_OP_MASS, m->dim * m->dim, ma->rhs, ma->f[MV_F_H], nullptr, ma->rtol, ma->atol, ma->maxit_mass, 0,
                      iters, nullptr));
   return MV_OK;
@@ -1125,6 +1147,10 @@ extern "C" int mv_ma_relax_move(mv_ma* ma, double dt, int i0, int nmax, int maxi
   double* const user_H_old = ma->f[MV_F_H_OLD];
   int status = 3, i = i0, st = MV_OK, done = 0;
   bool advanced = false;
+  static int fuse_env = -1;
+  if (fuse_env < 0) { const char* e = getenv("MV_FUSE_L2_RHS"); fuse_env = e ? atoi(e) : 1; }
+  ma->fuse_l2_rhs = fuse_env != 0;
+  ma->l2_rhs_valid = false;
   for (int k = 0; k < nmax && i < maxiter; ++k, ++i) {
     int it[3] = {0, 0, 0};
     double out[6];
@@ -1148,8 +1174,11 @@ extern "C" int mv_ma_relax_move(mv_ma* ma, double dt, int i0, int nmax, int maxi
     double* t = ma->f[MV_F_PHI]; ma->f[MV_F_PHI] = ma->f[MV_F_PHI_OLD]; ma->f[MV_F_PHI_OLD] = t;
     t = ma->f[MV_F_H]; ma->f[MV_F_H] = ma->f[MV_F_H_OLD]; ma->f[MV_F_H_OLD] = t;
     advanced = true;
+    ma->l2_rhs_valid = ma->fuse_l2_rhs && ma->l2_rhs_phi == ma->f[MV_F_PHI_OLD];   // the buffer the Hessian pass read is phi_old now
     if (cg_iters) for (int q = 0; q < 3; ++q) cg_iters[k * 3 + q] = it[q];
   }
+  ma->fuse_l2_rhs = false;      // between calls the caller may change phi: the next call starts from k_l2_rhs again
+  ma->l2_rhs_valid = false;
   if (status == 3 && st == MV_OK) --i;   // chunk exhausted: i is the last completed iteration
   // hand the fields back: the newest iterate sits in f[*_OLD] after an advance; both user buffers get it
   const double* newest_phi = ma->f[MV_F_PHI_OLD];
