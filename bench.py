@@ -667,6 +667,12 @@ def run_forced(args, kind):
     nnzv = dm.nnz / dm.Vown
     if kind == "laplacian":
         per_it = (12 * nnzv + 4 + 104 * 2)       # B_cg(2), SURVEY 8d
+    elif Vg >= 4096:
+        # assembled spring blocks + block-diagonal multigrid: SpMV over Kxx, Kxy, Kyy (28 B per non-zero + vectors),
+        # update / r.z / direction on [2][V] vectors, and one V-cycle per diagonal block (two fp32-valued level-0 passes, P and R,
+        # ~30 % more on the coarse levels)
+        vcycle = 1.3 * (2 * (8 * nnzv + 36) + 100)
+        per_it = (28 * nnzv + 38) + 176 + 2 * vcycle
     else:
         per_it = (4 * nnzv + 16 + 32) + 2 * 88   # matrix-free spring SpMV + the vector kernels of a 2-component CG iteration
     step_bytes = float(np.mean(its)) * per_it * Vg
