@@ -968,6 +968,8 @@ int amg_build_values(mv_mesh* m, int op, const double* val, const uint16_t* mask
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   cudaEventRecord(e0, g_stream);
   Amg* a = new Amg();
+  static unsigned long long next_uid = 1;
+  a->uid = next_uid++;
   a->op = op;
   a->singular = singular;
   BuildParams bp;

@@ -150,6 +150,12 @@ struct PcgWork {
   double* h_scal = nullptr; // pinned host mirror
   // mixed-precision Chebyshev (mv_cheb.cu): residual and two correction iterates in single, [V*MV_MAX_COMP] each,
   // single-precision copy of the operator values / inverse diagonal the sweeps stream
+  // CUDA graph of ONE multigrid-preconditioned CG iteration (mv_pcg_soa.cu): captured once per (operator, hierarchy,
+  // buffers) and replayed, so the ~40 small launches of an iteration cost one
+  void* graph_exec = nullptr;          // cudaGraphExec_t
+  unsigned long long graph_key[12] = {0};
+  long long graph_launches = 0;        // kernels inside the graph (launch accounting)
+  bool graph_failed = false;           // capture / instantiation failed once: plain launches from then on
   float* f32[3] = {nullptr, nullptr, nullptr};
   float* valf = nullptr;
   float* dinvf = nullptr;
@@ -209,6 +215,7 @@ struct Amg {
   int z_C = 0;
   double* cglob = nullptr;        // multi-GPU coarse solve: [2][C][nc] gathered right-hand side / scratch
   double setup_ms = 0.0;
+  unsigned long long uid = 0;     // unique per built hierarchy (a rebuilt one may reuse the address)
   ~Amg();
 };
 

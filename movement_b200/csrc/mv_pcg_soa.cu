@@ -16,6 +16,8 @@
 // r.D^-1 r, beta, convergence flag) -> k_dir_soa (p = D^-1 r + b p); with the multigrid
 // preconditioner the update carries no reduction and z = V-cycle(r) follows (mv_amg_cycle.cu).
 // Scalars stay on the device; reductions are deterministic (mv_internal.cuh).
+#include <string.h>
+
 #include "mv_internal.cuh"
 
 namespace mv {
@@ -522,15 +524,10 @@ int pcg_soa(mv_mesh* m, const double* val, const double* dinv, const double* rhs
 
   int it = 0, batch = pc ? 4 : 8;
   w.h_flags[0] = 0;
-  while (true) {
-    MV_CUDA(cudaMemcpyAsync(w.h_flags, w.flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, g_stream));
-    MV_CUDA(cudaStreamSynchronize(g_stream));
-    if (g_prof.used) prof_drain();
-    if (w.h_flags[0] || it >= maxit) break;
-    const int nb = batch < maxit - it ? batch : maxit - it;
-    for (int k = 0; k < nb; ++k) {
+  // One iteration as a sequence of launches; `timed` brackets the SpMV with the profiling events (not inside a graph).
+  auto iteration = [&](bool timed) -> int {
       if (dist) MV_CHECK(halo_exchange_soa(m->halo, n, C, w.p, ld));
-      const int pslot = prof_begin(C);
+      const int pslot = timed ? prof_begin(C) : -1;
       MV_CHECK(spmv_soa_launch<C>(m, val, w.p, w.q, ld, true));
       prof_end(pslot);
       if (dist) MV_CHECK(allreduce_sum_dev(w.scal + SC(S_PQ, 0), C));
@@ -559,6 +556,75 @@ int pcg_soa(mv_mesh* m, const double* val, const double* dinv, const double* rhs
                                                                      m->red.counter, w.scal);
         }
         MV_L k_dir_soa<C><<<gv, MV_BLOCK, 0, g_stream>>>(n, ld, w.r, dinv, w.p, w.flags, w.scal);
+      }
+      return MV_OK;
+  };
+  // CUDA graph of the multigrid-preconditioned iteration: ~25 launches at one GPU, ~45 with the peer-memory exchanges on
+  // several, most of them a few microseconds long on the coarse levels -- replayed as one graph launch.  All arguments
+  // are device pointers / device-resident scalars that do not change between iterations or solves, so the graph is
+  // captured once per (operator, hierarchy, buffers).  The first batch of a solve stays un-graphed while the profiling
+  // events are on (bench.py's per-launch SpMV timing).  MV_PCG_GRAPH=0 switches it off.
+  static int graph_env = -1;
+  if (graph_env < 0) { const char* e = getenv("MV_PCG_GRAPH"); graph_env = e ? atoi(e) : 1; }
+  const bool want_graph = pc != nullptr && graph_env != 0 && !w.graph_failed;
+  unsigned long long key[12] = {(unsigned long long)C, pc ? pc->uid : 0ull, (unsigned long long)(uintptr_t)val, (unsigned long long)(uintptr_t)dinv,
+                                (unsigned long long)(uintptr_t)mask, (unsigned long long)(uintptr_t)xs, (unsigned long long)n,
+                                (unsigned long long)ld, dist ? 1ull : 0ull, (unsigned long long)(uintptr_t)w.r,
+                                (unsigned long long)(uintptr_t)(pc ? pc->z : nullptr), (unsigned long long)(uintptr_t)g_stream};
+  auto ensure_graph = [&]() -> bool {
+    if (w.graph_exec && memcmp(key, w.graph_key, sizeof(key)) == 0) return true;
+    if (w.graph_exec) { cudaGraphExecDestroy((cudaGraphExec_t)w.graph_exec); w.graph_exec = nullptr; }
+    const long long l0 = g_launches;
+    // the library's stream is normally torch's current stream, i.e. the legacy default stream, which cannot be captured:
+    // capture on a private stream (every launch site uses the global g_stream), replay on the caller's
+    static cudaStream_t cap_stream = nullptr;
+    if (!cap_stream && cudaStreamCreateWithFlags(&cap_stream, cudaStreamNonBlocking) != cudaSuccess) {
+      cudaGetLastError(); w.graph_failed = true; return false;
+    }
+    cudaStream_t user_stream = g_stream;
+    g_stream = cap_stream;
+    cudaError_t cb = cudaStreamBeginCapture(g_stream, cudaStreamCaptureModeThreadLocal);
+    if (cb != cudaSuccess) {
+      g_stream = user_stream;
+      if (getenv("MV_PCG_VERBOSE")) fprintf(stderr, "[mv pcg] graph capture not started: %s\n", cudaGetErrorString(cb));
+      cudaGetLastError(); w.graph_failed = true; return false;
+    }
+    const int st = iteration(false);
+    cudaGraph_t graph = nullptr;
+    const cudaError_t ce = cudaStreamEndCapture(g_stream, &graph);
+    g_stream = user_stream;
+    w.graph_launches = g_launches - l0;
+    g_launches = l0;                       // nothing ran yet
+    cudaGraphExec_t exec = nullptr;
+    cudaError_t ci = cudaSuccess;
+    if (st != MV_OK || ce != cudaSuccess || !graph || (ci = cudaGraphInstantiate(&exec, graph, 0)) != cudaSuccess) {
+      if (getenv("MV_PCG_VERBOSE"))
+        fprintf(stderr, "[mv pcg] graph capture failed: iteration status %d, end capture '%s', instantiate '%s'\n", st, cudaGetErrorString(ce),
+                cudaGetErrorString(ci));
+      cudaGetLastError();
+      if (graph) cudaGraphDestroy(graph);
+      w.graph_failed = true;
+      return false;
+    }
+    if (getenv("MV_PCG_VERBOSE")) fprintf(stderr, "[mv pcg] iteration graph captured: %lld kernel launches\n", w.graph_launches);
+    cudaGraphDestroy(graph);
+    w.graph_exec = exec;
+    memcpy(w.graph_key, key, sizeof(key));
+    return true;
+  };
+  while (true) {
+    MV_CUDA(cudaMemcpyAsync(w.h_flags, w.flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, g_stream));
+    MV_CUDA(cudaStreamSynchronize(g_stream));
+    if (g_prof.used) prof_drain();
+    if (w.h_flags[0] || it >= maxit) break;
+    const int nb = batch < maxit - it ? batch : maxit - it;
+    const bool graphed = want_graph && !(g_prof.on && it == 0) && ensure_graph();
+    for (int k = 0; k < nb; ++k) {
+      if (graphed) {
+        MV_CUDA(cudaGraphLaunch((cudaGraphExec_t)w.graph_exec, g_stream));
+        g_launches += w.graph_launches;
+      } else {
+        MV_CHECK(iteration(true));
       }
     }
     MV_KERNEL_CHECK();
