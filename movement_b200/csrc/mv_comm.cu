@@ -369,6 +369,8 @@ extern "C" int mv_comm_info(int64_t* info) {
 }
 
 extern "C" int mv_comm_finalize(void) {
+  cudaStreamSynchronize(g_stream);
+  pcg_graph_release_all();   // graphs with NCCL nodes first: ncclCommDestroy waits for them
   p2p_finalize();
   if (g_comm) {
     cudaStreamSynchronize(g_stream);

@@ -514,7 +514,7 @@ extern "C" void mv_mesh_destroy(mv_mesh* m) {
   dev_free(m->pcg.r); dev_free(m->pcg.p); dev_free(m->pcg.q); dev_free(m->pcg.xs); dev_free(m->pcg.scal); dev_free(m->pcg.flags);
   for (int i = 0; i < 3; ++i) dev_free(m->pcg.f32[i]);
   dev_free(m->pcg.valf); dev_free(m->pcg.dinvf);
-  if (m->pcg.graph_exec) cudaGraphExecDestroy((cudaGraphExec_t)m->pcg.graph_exec);
+  mv::pcg_graph_release(m->pcg);
   if (m->pcg.h_flags) cudaFreeHost(m->pcg.h_flags);
   if (m->pcg.h_scal) cudaFreeHost(m->pcg.h_scal);
   dev_free(m->halo.send_idx); dev_free(m->halo.send_buf);

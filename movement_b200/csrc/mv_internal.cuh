@@ -338,6 +338,8 @@ int spring_apply_dev(mv_mesh* m, const double* coords, const uint16_t* mask, con
 int pcg_solve_spring(mv_mesh* m, const double* coords, const double* dinv_dof, const double* rhs, double* x, const uint16_t* mask,
                      double rtol, double atol, int maxit, int* iters);
 int ensure_pcg_workspace(mv_mesh* m);
+void pcg_graph_release(PcgWork& w);   // captured iteration graph of a mesh (mv_pcg_soa.cu)
+void pcg_graph_release_all();         // before the communicator goes away
 int exclusive_scan_i32(const int* in, int* out, int64_t n);
 
 // host-side entry points shared across translation units

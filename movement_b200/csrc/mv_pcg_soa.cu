@@ -22,6 +22,26 @@
 
 namespace mv {
 
+// Graphs that hold NCCL nodes must be gone before the communicator is destroyed (ncclCommDestroy waits for them: a mover
+// still alive at mv_comm_finalize hung the 8-GPU converged run at exit, round 2), so every captured graph is registered.
+static std::vector<PcgWork*> g_graph_owners;
+void pcg_graph_release(PcgWork& w) {
+  if (w.graph_exec) {
+    cudaGraphExecDestroy((cudaGraphExec_t)w.graph_exec);
+    w.graph_exec = nullptr;
+  }
+  for (size_t i = 0; i < g_graph_owners.size(); ++i)
+    if (g_graph_owners[i] == &w) { g_graph_owners.erase(g_graph_owners.begin() + i); break; }
+}
+void pcg_graph_release_all() {
+  for (PcgWork* w : g_graph_owners)
+    if (w->graph_exec) {
+      cudaGraphExecDestroy((cudaGraphExec_t)w->graph_exec);
+      w->graph_exec = nullptr;
+    }
+  g_graph_owners.clear();
+}
+
 #define VERTEX_LOOP(v, n) for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < (n); v += (int64_t)gridDim.x * blockDim.x)
 
 template <int C>
@@ -573,7 +593,7 @@ int pcg_soa(mv_mesh* m, const double* val, const double* dinv, const double* rhs
                                 (unsigned long long)(uintptr_t)(pc ? pc->z : nullptr), (unsigned long long)(uintptr_t)g_stream};
   auto ensure_graph = [&]() -> bool {
     if (w.graph_exec && memcmp(key, w.graph_key, sizeof(key)) == 0) return true;
-    if (w.graph_exec) { cudaGraphExecDestroy((cudaGraphExec_t)w.graph_exec); w.graph_exec = nullptr; }
+    pcg_graph_release(w);
     const long long l0 = g_launches;
     // the library's stream is normally torch's current stream, i.e. the legacy default stream, which cannot be captured:
     // capture on a private stream (every launch site uses the global g_stream), replay on the caller's
@@ -609,6 +629,7 @@ int pcg_soa(mv_mesh* m, const double* val, const double* dinv, const double* rhs
     if (getenv("MV_PCG_VERBOSE")) fprintf(stderr, "[mv pcg] iteration graph captured: %lld kernel launches\n", w.graph_launches);
     cudaGraphDestroy(graph);
     w.graph_exec = exec;
+    g_graph_owners.push_back(&w);
     memcpy(w.graph_key, key, sizeof(key));
     return true;
   };

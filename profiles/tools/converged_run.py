@@ -3,7 +3,7 @@
 mover.move()) on UnitCubeMesh(n,n,n), 1 GPU or partitioned under torchrun.
 
   python profiles/tools/converged_run.py --n 256 --out gpurun_out/converged_n256_N1.json [--record rec.npz]
-  python -m torch.distributed.run --nproc-per-node 8 ... profiles/tools/converged_run.py --n 256 --compare rec.npz
+  python -m torch.distributed.run --nproc-per-node 8 ... profiles/tools/converged_run.py --size 256 --compare rec.npz
 
 Prints / stores: iteration count, final residual, residual trace, tangled cells of the PHYSICAL mesh at convergence,
 wall time of move(), converged vertex-iterations/s, inner iteration totals, checksums of the moved coordinates; with
@@ -22,7 +22,7 @@ sys.path.insert(0, ROOT)
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--n", type=int, default=256)
+    ap.add_argument("--n", "--size", dest="n", type=int, default=256, help="--size under torchrun (its parser finds --n ambiguous)")
     ap.add_argument("--dim", type=int, default=3)
     ap.add_argument("--rtol", type=float, default=1e-8)
     ap.add_argument("--maxiter", type=int, default=1000)
