@@ -230,8 +230,9 @@ int mv_ma_eval_monitor(mv_ma* ma, const double* coords, double* m_out);
 int mv_ma_diagnostics(mv_ma* ma, int use_H_old, double* out);
 /* replaces: monge_ampere.py:419-449 + :535 -- K dphi = dt * residual, phi = phi_old+dphi */
 int mv_ma_pseudotimestep(mv_ma* ma, double pseudo_dt, int* iters);
-/* Initial guess of the Poisson solve: 1 (default) = Galerkin combination of the mover's two previous solves,
- * 0 = zero, as a KSP without KSPSetInitialGuessNonzero starts (monge_ampere.py:441-448).  Process-wide.      */
+/* Initial guess of the Poisson solve: 0 = zero, as a KSP without KSPSetInitialGuessNonzero starts
+ * (monge_ampere.py:441-448); 1 (default) = Galerkin combination of the mover's previous solves at the default depth (3);
+ * k >= 2 = depth k (at most 8).  Process-wide; the solve and its stopping rule are the same for every setting.    */
 int mv_set_poisson_history(int on);
 /* replaces: monge_ampere.py:451-485 + :536 -- M H = -int div(tau).grad(phi) + bdry      */
 int mv_ma_equidistribute(mv_ma* ma, int* iters);
