@@ -46,15 +46,65 @@ class LocalPart:
     send_ptr: np.ndarray = field(default_factory=lambda: np.zeros(1, np.int64))
     send_idx: np.ndarray = field(default_factory=lambda: np.zeros(0, np.int32))   # local owned vertices to send
     recv_ptr: np.ndarray = field(default_factory=lambda: np.zeros(1, np.int64))   # ghost segments, relative to n_owned
+    method: str = "block"         # "block": owned vertices are global_vertex[:n_owned] = a contiguous range; "rcb": any set
 
 
 def owner_of(gv, starts):
     return np.searchsorted(starts, gv, side="right") - 1
 
 
-def partition_mesh(coords, cells, bfacets, btags, rank, size, starts=None):
+def rcb_order(coords, size):
+    """Recursive coordinate bisection of the vertices into ``size`` parts of (almost) equal counts: the vertex set is cut
+    perpendicular to its longest extent, proportionally to the number of parts on either side, until every set is one
+    part.  Returns ``(perm, starts)``: part r consists of the vertices ``perm[starts[r]:starts[r+1]]`` (old numbers, ascending
+    inside a part so that the generator's locality survives).  Deterministic (ties are broken by vertex number), so every
+    rank computes the same decomposition without communication.  This is the general-mesh alternative to the
+    contiguous index blocks, which are slabs only for meshes numbered plane by plane."""
+    coords = np.asarray(coords, dtype=np.float64)
+    V = coords.shape[0]
+    parts = []
+
+    def split(idx, p):
+        if p == 1:
+            parts.append(np.sort(idx))
+            return
+        p1 = p // 2
+        k = (idx.size * p1) // p
+        x = coords[idx]
+        axis = int(np.argmax(x.max(axis=0) - x.min(axis=0))) if idx.size else 0
+        order = np.lexsort((idx, x[:, axis]))
+        split(idx[order[:k]], p1)
+        split(idx[order[k:]], p - p1)
+
+    split(np.arange(V, dtype=np.int64), int(size))
+    starts = np.concatenate([[0], np.cumsum([q.size for q in parts])]).astype(np.int64)
+    return np.concatenate(parts) if parts else np.zeros(0, np.int64), starts
+
+
+def partition_mesh(coords, cells, bfacets, btags, rank, size, starts=None, method=None):
     """Extract rank ``rank``'s part of a global mesh.  Deterministic; every rank can compute
-    every other rank's part, which is how the send lists are derived without communication."""
+    every other rank's part, which is how the send lists are derived without communication.
+
+    ``method``: ``"block"`` (default) -- contiguous blocks of the global vertex numbers; ``"rcb"`` -- recursive coordinate
+    bisection (``rcb_order``) for meshes whose numbering carries no locality: the mesh is renumbered part by part, cut into
+    those blocks, and ``global_vertex`` / ``global_cell`` of the result refer to the CALLER's numbering again.  The default
+    can be switched with the environment variable ``MV_PARTITION``."""
+    import os
+
+    method = method or os.environ.get("MV_PARTITION", "block")
+    if method == "rcb" and starts is None and size > 1:
+        coords = np.asarray(coords)
+        cells = np.asarray(cells)
+        perm, rstarts = rcb_order(coords, size)
+        inv = np.empty(coords.shape[0], dtype=np.int64)
+        inv[perm] = np.arange(coords.shape[0])
+        bf = np.asarray(bfacets)
+        lp = partition_mesh(coords[perm], inv[cells], inv[bf] if bf.size else bf, btags, rank, size, starts=rstarts, method="block")
+        lp.global_vertex = perm[lp.global_vertex]
+        lp.method = "rcb"
+        return lp
+    if method not in ("block", "rcb"):
+        raise ValueError(f"unknown partition method {method!r} (block, rcb)")
     coords = np.asarray(coords)
     cells = np.asarray(cells)
     V = coords.shape[0]

@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 from movement_b200.mesh import cube_arrays, square_arrays
-from movement_b200.partition import block_ranges, partition_mesh
+from movement_b200.partition import block_ranges, partition_mesh, rcb_order
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
@@ -42,6 +42,63 @@ def test_partition_covers_mesh_and_halo_plan_is_consistent(arrays, size):
             recv = Q.global_vertex[Q.n_owned_vertices + Q.recv_ptr[kk]: Q.n_owned_vertices + Q.recv_ptr[kk + 1]]
             assert np.array_equal(sent, recv)
         assert p.n_owned_vertices + p.recv_ptr[-1] == p.coords.shape[0]
+
+
+def _shuffled(arrays, seed=0):
+    """The same mesh with a vertex numbering that carries no locality."""
+    c, ce, bf, bt = arrays
+    rng = np.random.default_rng(seed)
+    new_of_old = rng.permutation(c.shape[0])
+    old_of_new = np.argsort(new_of_old)
+    return c[old_of_new], new_of_old[ce].astype(ce.dtype), new_of_old[bf].astype(bf.dtype), bt
+
+
+@pytest.mark.parametrize("arrays", [cube_arrays(6, 5, 7), square_arrays(12, 9)])
+@pytest.mark.parametrize("size", [2, 3, 5, 8])
+def test_rcb_partition_of_an_unordered_mesh(arrays, size):
+    """Recursive coordinate bisection (general meshes): same invariants as the block partition, in the caller's
+    numbering, and far fewer ghosts than index blocks of a numbering without locality."""
+    c, ce, bf, bt = _shuffled(arrays)
+    V = c.shape[0]
+    perm, starts = rcb_order(c, size)
+    assert np.array_equal(np.sort(perm), np.arange(V)) and starts[0] == 0 and starts[-1] == V
+    assert np.diff(starts).max() - np.diff(starts).min() <= 1 + size          # balanced
+    parts = [partition_mesh(c, ce, bf, bt, r, size, method="rcb") for r in range(size)]
+    owned = np.concatenate([p.global_vertex[: p.n_owned_vertices] for p in parts])
+    assert np.array_equal(np.sort(owned), np.arange(V))                       # every vertex owned exactly once
+    owned_cells = np.concatenate([p.global_cell[: p.n_owned_cells] for p in parts])
+    assert np.array_equal(np.sort(owned_cells), np.arange(ce.shape[0]))       # every cell owned exactly once
+    for p in parts:
+        assert p.method == "rcb"
+        mine = np.zeros(V, bool)
+        mine[p.global_vertex[: p.n_owned_vertices]] = True
+        assert np.array_equal(p.global_vertex[: p.n_owned_vertices], perm[starts[p.rank]:starts[p.rank + 1]])
+        touch = mine[ce].any(axis=1)
+        assert touch.sum() == p.cells.shape[0]                                # every cell touching an owned vertex is local
+        assert np.array_equal(p.global_vertex[p.cells], ce[p.global_cell])
+        assert np.array_equal(p.coords, c[p.global_vertex])
+        assert mine[bf].any(axis=1).sum() == p.bfacets.shape[0]
+        for k, q in enumerate(p.neighbours):
+            sent = p.global_vertex[p.send_idx[p.send_ptr[k]:p.send_ptr[k + 1]]]
+            Q = parts[q]
+            kk = list(Q.neighbours).index(p.rank)
+            recv = Q.global_vertex[Q.n_owned_vertices + Q.recv_ptr[kk]: Q.n_owned_vertices + Q.recv_ptr[kk + 1]]
+            assert np.array_equal(sent, recv)
+        assert p.n_owned_vertices + p.recv_ptr[-1] == p.coords.shape[0]
+    ghosts_rcb = sum(int(p.recv_ptr[-1]) for p in parts)
+    ghosts_block = sum(int(partition_mesh(c, ce, bf, bt, r, size).recv_ptr[-1]) for r in range(size))
+    assert ghosts_rcb < ghosts_block                                          # index blocks of a shuffled numbering: almost everything is a ghost
+    # on the generator's own numbering the parts are boxes: compact extents
+    c0 = arrays[0]
+    perm0, starts0 = rcb_order(c0, size)
+    for r in range(size):
+        x = c0[perm0[starts0[r]:starts0[r + 1]]]
+        assert np.prod(x.max(axis=0) - x.min(axis=0) + 1e-12) <= 1.0 / size * 3.5
+
+
+def test_unknown_partition_method():
+    with pytest.raises(ValueError, match="unknown partition method"):
+        partition_mesh(*square_arrays(3, 3), 0, 2, method="metis")
 
 
 def test_block_ranges():
@@ -84,12 +141,13 @@ print("GLOO-OK")
 '''
 
 
-def test_world_size_2_gloo(tmp_path):
+@pytest.mark.parametrize("method", ["block", "rcb"])
+def test_world_size_2_gloo(tmp_path, method):
     script = tmp_path / "worker.py"
     script.write_text(_WORKER)
-    env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="", MV_PARTITION=method)
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
-                          "--master-addr", "127.0.0.1", "--master-port", "29533", str(script), ROOT],
+                          "--master-addr", "127.0.0.1", "--master-port", "29533" if method == "block" else "29535", str(script), ROOT],
                          capture_output=True, text=True, timeout=300, env=env)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
     assert out.stdout.count("GLOO-OK") == 2
