@@ -358,7 +358,8 @@ def run_relaxation(args, dim):
             fused = cheb and c != 1
             if fused and mixed:
                 alg = 8.0 * dm.nnz + (4.0 + 4.0 + 16.0 * c + (2.0 if (c == dim and have_mask) else 0.0)) * dm.Vown
-                kern = "k_cheb_tma<float>" if c == 9 else "k_mcheb (fp32 iteration)"
+                kern = ("k_cheb_tma<...,float,float,MIX_IT4> (fp32 Chebyshev iteration, TMA-staged stream, packed float4 iterates)" if c == 9
+                        else "k_mcheb (fp32 Chebyshev iteration)")
             else:
                 per_row = (4.0 + 8.0 + 32.0 * c + (2.0 if (c == dim and have_mask) else 0.0)) if fused else (4.0 + 16.0 * c)
                 alg = 12.0 * dm.nnz + per_row * dm.Vown
@@ -508,8 +509,9 @@ def run_relaxation(args, dim):
                 "config": {"workload": workload_name(n, dim), "n": n, "vertices": Vglobal, "cells": Cglobal,
                            "parallelism": f"vertex-owner slab partition x{world}" if world > 1 else "single GPU",
                            "l2": "inputs larger than L2 (matrix stream %.1f GB per SpMV)" % (12.0 * dm.nnz / 1e9),
-                           "mass_solver": "fused Chebyshev (Wathen interval), measured stop at rtol 1e-12" if cheb else "Jacobi-PCG",
-                           "poisson_solver": f"PCG + smoothed-aggregation multigrid, {amg['levels']} levels, rows {amg['rows']}" if amg else "Jacobi-PCG",
+                           "mass_solver": ("fused Chebyshev (Wathen interval), " + ("mixed precision: fp64 residual passes with the measured stopping test at rtol 1e-12, fp32 sweeps on the correction" if mixed else "all fp64, measured stop at rtol 1e-12")) if cheb else "Jacobi-PCG",
+                           "poisson_solver": (f"PCG (CUDA-graph iteration) + smoothed-aggregation multigrid, {amg['levels']} levels, rows {amg['rows']}, "
+                                              "Galerkin initial guess from the last 3 solves") if amg else "Jacobi-PCG",
                            "inner_iterations_per_step(l2,poisson,hessian)": [float(x) for x in cg.mean(axis=0)],
                            "residual_after_timed_steps": float(trace[-1, 1])},
                 "roofline": roofline,
