@@ -876,6 +876,34 @@ class MAOperators:
         return volx * m[self.cells].mean(axis=1) / vol0
 
 
+def galerkin_guess(xs, bs, b, tol=1e-10):
+    """Initial guess of K x = b from earlier solutions xs[i] with right-hand sides bs[i] = K xs[i] (newest first): the
+    energy-optimal combination sum_i a_i xs[i], G a = f with G_ij = xs[i].bs[j], f_i = xs[i].b, by a Cholesky factorisation
+    in the given order that stops at the first negligible pivot (restatement of k_hist_solve / mv_ma_pseudotimestep in
+    movement_b200/csrc/mv_ma.cu, which prepares the KSP solve of movement/monge_ampere.py:441-448; the reference itself
+    starts every solve from zero).  Returns (x0, number of vectors used)."""
+    m = len(xs)
+    if m == 0:
+        return np.zeros_like(b), 0
+    G = np.array([[float(np.dot(xs[i], bs[j])) for j in range(m)] for i in range(m)])
+    f = np.array([float(np.dot(xs[i], b)) for i in range(m)])
+    L = np.zeros((m, m))
+    mm = 0
+    for j in range(m):
+        d = G[j, j] - float(np.dot(L[j, :j], L[j, :j]))
+        if not (G[j, j] > 0.0 and d > tol * G[j, j]):
+            break
+        L[j, j] = np.sqrt(d)
+        for i in range(j + 1, m):
+            L[i, j] = (G[i, j] - float(np.dot(L[i, :j], L[j, :j]))) / L[j, j]
+        mm = j + 1
+    if mm == 0:
+        return np.zeros_like(b), 0
+    y = np.linalg.solve(L[:mm, :mm], f[:mm])
+    a = np.linalg.solve(L[:mm, :mm].T, y)
+    return sum(a[i] * xs[i] for i in range(mm)), mm
+
+
 class OracleRelaxation:
     """movement/monge_ampere.py:345-540 with exact inner solves."""
 
