@@ -691,10 +691,22 @@ extern "C" int mv_spring_move(mv_mesh* m, double* coords, const double* forcing,
   double vg = (double)n;
   if (comm_active()) MV_CHECK(allreduce_host(&vg, 1, 0));
   int st;
-  if (m->pc_kind == MV_PC_AMG && vg >= (double)g_spring_min_rows)
+  if (m->pc_kind == MV_PC_AMG && vg >= (double)g_spring_min_rows) {
     st = spring_solve_amg(m, coords, dinv, sf.as<double>(), u, sm.as<uint16_t>(), rtol, atol, maxit, iters);
-  else
+    if (st == MV_ERR_NOT_CONVERGED && !g_spring_last_setup) {
+      // a REUSED preconditioner failed (breakdown or the iteration cap): the mesh may have moved too far from the
+      // configuration it was built on -- rebuild the hierarchies on the current operator and solve once more from the
+      // same initial guess (the status is the same on every rank: it derives from allreduced scalars)
+      for (int c = 0; c < 2; ++c)
+        if (m->spring_pc[c]) { delete m->spring_pc[c]; m->spring_pc[c] = nullptr; }
+      MV_CUDA(cudaMemcpyAsync(u, sf.dev, m->V * 2 * sizeof(double), cudaMemcpyDeviceToDevice, g_stream));
+      MV_L k_zero_free<2><<<grid_for(n * 2), MV_BLOCK, 0, g_stream>>>(n, sm.as<uint16_t>(), u);
+      MV_KERNEL_CHECK();
+      st = spring_solve_amg(m, coords, dinv, sf.as<double>(), u, sm.as<uint16_t>(), rtol, atol, maxit, iters);
+    }
+  } else {
     st = pcg_solve_spring(m, coords, dinv, sf.as<double>(), u, sm.as<uint16_t>(), rtol, atol, maxit, iters);
+  }
   if (st != MV_OK) return st;
   double* dout = m->pcg.scal + SC(S_SUM, 8);
   MV_L k_axpy_norm<<<grid_for(n * 2), MV_BLOCK, 0, g_stream>>>(n * 2, dt, u, coords, displacement, m->red.partials, m->red.counter,
