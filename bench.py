@@ -255,19 +255,27 @@ class Ctx:
         return list(mx), list(cnt)
 
 
-def host_mesh(cx, arrays_fn):
-    """The caller's input: (pinned) host arrays of this rank's part, with the time it took to make them."""
+def host_mesh(cx, arrays_fn, part_fn=None):
+    """The caller's input: (pinned) host arrays of this rank's part, with the time it took to make them.  On several GPUs
+    the generated meshes are created slab by slab (mesh.cube_part / square_part: identical to cutting the global mesh,
+    tests/test_partition.py) unless MV_PARTITION selects another partitioner."""
     t0 = time.perf_counter()
-    arrays = arrays_fn()
-    t1 = time.perf_counter()
     lp = None
-    Vg, Cg = arrays[0].shape[0], arrays[1].shape[0]
-    if cx.world > 1:
-        from movement_b200.partition import partition_mesh
-
-        lp = partition_mesh(*arrays, cx.rank, cx.world)
+    if cx.world > 1 and part_fn is not None and os.environ.get("MV_PARTITION", "block") == "block":
+        lp = part_fn(cx.rank, cx.world)
+        t1 = t2 = time.perf_counter()
         arrays = (lp.coords, lp.cells, lp.bfacets, lp.btags)
-    t2 = time.perf_counter()
+        Vg, Cg = lp.global_num_vertices, lp.global_num_cells
+    else:
+        arrays = arrays_fn()
+        t1 = time.perf_counter()
+        Vg, Cg = arrays[0].shape[0], arrays[1].shape[0]
+        if cx.world > 1:
+            from movement_b200.partition import partition_mesh
+
+            lp = partition_mesh(*arrays, cx.rank, cx.world)
+            arrays = (lp.coords, lp.cells, lp.bfacets, lp.btags)
+        t2 = time.perf_counter()
     host, keep = cx.pinned(arrays)
     return host, keep, lp, Vg, Cg, {"mesh_generation_s": t1 - t0, "partition_s": t2 - t1, "pin_s": time.perf_counter() - t2}
 
@@ -301,7 +309,7 @@ def move_k(mover, k):
 def run_relaxation(args, dim):
     cx = Ctx(args)
     np, torch, mv, L, lib = cx.np, cx.torch, cx.mv, cx.L, cx.lib
-    from movement_b200.mesh import Mesh, cube_arrays, square_arrays
+    from movement_b200.mesh import Mesh, cube_arrays, cube_part, square_arrays, square_part
 
     rank, world = cx.rank, cx.world
     cheb = args.mass_solver == "chebyshev"
@@ -309,7 +317,8 @@ def run_relaxation(args, dim):
     n = args.n or (256 if dim == 3 else 8192)
     mv.monge_ampere.MongeAmpereMover_Base.inner_rtol = args.inner_rtol
     monitor = mv.sinatan3_hessian_monitor() if dim == 3 else mv.helmholtz_hessian_monitor()
-    host, keep, lp, Vglobal, Cglobal, prep = host_mesh(cx, (lambda: cube_arrays(n, n, n)) if dim == 3 else (lambda: square_arrays(n, n)))
+    host, keep, lp, Vglobal, Cglobal, prep = host_mesh(cx, (lambda: cube_arrays(n, n, n)) if dim == 3 else (lambda: square_arrays(n, n)),
+                                                       (lambda r, s: cube_part(n, n, n, r, s)) if dim == 3 else (lambda r, s: square_part(n, n, r, s)))
     h2d_bytes = sum(int(a.nbytes) for a in host)
 
     def make_mover(maxiter=10 ** 6):

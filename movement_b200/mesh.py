@@ -13,6 +13,8 @@ plus a Firedrake-like ``.dat.data`` host view.
 """
 from __future__ import annotations
 
+import os
+
 import numpy as np
 import torch
 
@@ -381,32 +383,134 @@ def cube_arrays(nx, ny, nz):
     return coords, cells, np.concatenate(bf).astype(np.int32), np.concatenate(bt).astype(np.int32)
 
 
-def _maybe_distribute(arrays, distribute):
+def cube_part(nx, ny, nz, rank, size):
+    """Rank ``rank``'s part of ``cube_arrays(nx, ny, nz)`` under the block partition, generated WITHOUT the global mesh:
+    only the hexahedron layers that can touch an owned vertex (vertex numbers run x fastest, z slowest, so an index block is
+    a z-slab) are created, in the global order, and cut by the same routine as a global mesh (``partition._cut_block``).
+    The result is identical, array by array, to ``partition_mesh(*cube_arrays(nx, ny, nz), rank, size)``
+    (tests/test_partition.py); at 256^3 on 8 ranks each rank touches 1/7 of the 100 M cells instead of all of them."""
+    from .partition import _cut_block, block_ranges
+
+    xs, ys, zs = (np.linspace(0.0, 1.0, n + 1) for n in (nx, ny, nz))
+    sx, sy, sz = 1, nx + 1, (nx + 1) * (ny + 1)
+    V = sz * (nz + 1)
+    starts = block_ranges(V, size)
+    lo, hi = int(starts[rank]), int(starts[rank + 1])
+    klo, khi = lo // sz, (max(hi, lo + 1) - 1) // sz          # z-layers of the owned vertices
+    k0, k1 = max(klo - 1, 0), min(khi, nz - 1)                 # hexahedron layers that touch them
+    kk, jj, ii = np.meshgrid(np.arange(k0, k1 + 1, dtype=np.int64), np.arange(ny, dtype=np.int64),
+                             np.arange(nx, dtype=np.int64), indexing="ij")
+    v0 = (kk * sz + jj * sy + ii).ravel()
+    off = np.array([0, sx, sy, sx + sy, sz, sx + sz, sy + sz, sx + sy + sz], dtype=np.int64)
+    cells = np.empty((v0.size, 6, 4), dtype=np.int32)
+    for t in range(6):
+        for l in range(4):
+            cells[:, t, l] = v0 + off[_KUHN[t, l]]
+    cells = cells.reshape(-1, 4)
+    cell_gid = np.int64(k0) * ny * nx * 6 + np.arange(cells.shape[0], dtype=np.int64)
+
+    def quad_faces(a, b, c, d):
+        return np.concatenate([np.stack([a, b, d], axis=1), np.stack([a, c, d], axis=1)])
+
+    def grid(r1, r2):
+        p, q = np.meshgrid(r1, r2, indexing="ij")
+        return p.ravel(), q.ravel()
+
+    kr = np.arange(k0, k1 + 1, dtype=np.int64)
+    bf, bt = [], []
+    j, k = grid(np.arange(ny, dtype=np.int64), kr)
+    for tag, i0 in ((1, 0), (2, nx)):
+        a = k * sz + j * sy + i0
+        bf.append(quad_faces(a, a + sy, a + sz, a + sy + sz)); bt.append(np.full(2 * a.size, tag))
+    i, k = grid(np.arange(nx, dtype=np.int64), kr)
+    for tag, j0 in ((3, 0), (4, ny)):
+        a = k * sz + j0 * sy + i
+        bf.append(quad_faces(a, a + sx, a + sz, a + sx + sz)); bt.append(np.full(2 * a.size, tag))
+    i, j = grid(np.arange(nx, dtype=np.int64), np.arange(ny, dtype=np.int64))
+    for tag, kp, wanted in ((5, 0, klo == 0), (6, nz, khi == nz)):
+        if wanted:
+            a = kp * sz + j * sy + i
+            bf.append(quad_faces(a, a + sx, a + sy, a + sx + sy)); bt.append(np.full(2 * a.size, tag))
+
+    def coords_of(gv):
+        gv = np.asarray(gv, dtype=np.int64)
+        return np.stack([xs[gv % sy], ys[(gv // sy) % (ny + 1)], zs[gv // sz]], axis=1)
+
+    return _cut_block(coords_of, 3, V, cells, cell_gid, 6 * nx * ny * nz, np.concatenate(bf).astype(np.int32),
+                      np.concatenate(bt).astype(np.int32), rank, size, starts)
+
+
+def square_part(nx, ny, rank, size, Lx=1.0, Ly=1.0):
+    """The same for ``square_arrays`` (vertex numbers run y fastest: an index block is an x-slab)."""
+    from .partition import _cut_block, block_ranges
+
+    xs = np.linspace(0.0, Lx, nx + 1)
+    ys = np.linspace(0.0, Ly, ny + 1)
+    sy = ny + 1
+    V = (nx + 1) * sy
+    starts = block_ranges(V, size)
+    lo, hi = int(starts[rank]), int(starts[rank + 1])
+    ilo, ihi = lo // sy, (max(hi, lo + 1) - 1) // sy
+    i0, i1 = max(ilo - 1, 0), min(ihi, nx - 1)
+    ii, jj = np.meshgrid(np.arange(i0, i1 + 1, dtype=np.int64), np.arange(ny, dtype=np.int64), indexing="ij")
+    q0 = (ii * sy + jj).ravel()
+    q1, q3 = q0 + 1, q0 + sy
+    q2 = q3 + 1
+    cells = np.empty((2 * q0.size, 3), dtype=np.int32)
+    cells[0::2, 0], cells[0::2, 1], cells[0::2, 2] = q0, q1, q3
+    cells[1::2, 0], cells[1::2, 1], cells[1::2, 2] = q1, q2, q3
+    cell_gid = np.int64(i0) * ny * 2 + np.arange(cells.shape[0], dtype=np.int64)
+    j = np.arange(ny, dtype=np.int64)
+    i = np.arange(i0, i1 + 1, dtype=np.int64)
+    bf, bt = [], []
+    if ilo == 0:
+        bf.append(np.stack([j, j + 1], axis=1)); bt.append(np.full(ny, 1))
+    if ihi == nx:
+        bf.append(np.stack([nx * sy + j, nx * sy + j + 1], axis=1)); bt.append(np.full(ny, 2))
+    bf.append(np.stack([i * sy, (i + 1) * sy], axis=1)); bt.append(np.full(i.size, 3))
+    bf.append(np.stack([i * sy + ny, (i + 1) * sy + ny], axis=1)); bt.append(np.full(i.size, 4))
+
+    def coords_of(gv):
+        gv = np.asarray(gv, dtype=np.int64)
+        return np.stack([xs[gv // sy], ys[gv % sy]], axis=1)
+
+    return _cut_block(coords_of, 2, V, cells, cell_gid, 2 * nx * ny, np.concatenate(bf).astype(np.int32),
+                      np.concatenate(bt).astype(np.int32), rank, size, starts)
+
+
+def _maybe_distribute(arrays, distribute, part_fn=None):
     from . import parallel
 
-    coords, cells, bf, bt = arrays
     if distribute is None:
         distribute = parallel.is_active()
+    if callable(arrays) and not (distribute and part_fn is not None and os.environ.get("MV_PARTITION", "block") == "block"):
+        arrays = arrays()
     if not distribute:
+        coords, cells, bf, bt = arrays
         return Mesh(coords, cells, bf, bt)
     from .partition import partition_mesh
 
-    lp = partition_mesh(coords, cells, bf, bt, parallel.rank(), parallel.size())
+    if callable(arrays):      # generated mesh, block partition: this rank's slab only, never the global mesh
+        lp = part_fn(parallel.rank(), parallel.size())
+    else:
+        coords, cells, bf, bt = arrays
+        lp = partition_mesh(coords, cells, bf, bt, parallel.rank(), parallel.size())
     return Mesh(lp.coords, lp.cells, lp.bfacets, lp.btags, part=lp)
 
 
 def UnitSquareMesh(nx, ny=None, distribute=None):
-    return _maybe_distribute(square_arrays(nx, nx if ny is None else ny), distribute)
+    ny = nx if ny is None else ny
+    return _maybe_distribute(lambda: square_arrays(nx, ny), distribute, lambda r, s: square_part(nx, ny, r, s))
 
 
 def RectangleMesh(nx, ny, Lx, Ly, distribute=None):
-    return _maybe_distribute(square_arrays(nx, ny, Lx, Ly), distribute)
+    return _maybe_distribute(lambda: square_arrays(nx, ny, Lx, Ly), distribute, lambda r, s: square_part(nx, ny, r, s, Lx, Ly))
 
 
 def UnitCubeMesh(nx, ny=None, nz=None, distribute=None):
     ny = nx if ny is None else ny
     nz = nx if nz is None else nz
-    return _maybe_distribute(cube_arrays(nx, ny, nz), distribute)
+    return _maybe_distribute(lambda: cube_arrays(nx, ny, nz), distribute, lambda r, s: cube_part(nx, ny, nz, r, s))
 
 
 def UnitTriangleMesh():

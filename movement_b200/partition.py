@@ -109,14 +109,19 @@ def partition_mesh(coords, cells, bfacets, btags, rank, size, starts=None, metho
     cells = np.asarray(cells)
     V = coords.shape[0]
     starts = block_ranges(V, size) if starts is None else np.asarray(starts, dtype=np.int64)
+    return _cut_block(lambda gv: coords[gv].copy(), coords.shape[1], V, cells, None, int(cells.shape[0]), bfacets, btags,
+                      rank, size, starts)
+
+
+def _cut_block(coords_of, dim, V, cells, cell_gid, num_global_cells, bfacets, btags, rank, size, starts):
+    """The block partition proper.  ``cells`` / ``bfacets`` may be CANDIDATE subsets of the global arrays (any superset of
+    the entities that touch an owned vertex, in global order; ``cell_gid`` = their global cell numbers, None = they are the
+    global arrays), ``coords_of(global ids)`` returns coordinates -- so a generated mesh never has to exist as a whole
+    (``cube_part`` / ``square_part`` below)."""
+    cells = np.asarray(cells)
     lo, hi = int(starts[rank]), int(starts[rank + 1])
-
-    def local_cells(r):
-        l, h = int(starts[r]), int(starts[r + 1])
-        touch = ((cells >= l) & (cells < h)).any(axis=1)
-        return np.nonzero(touch)[0]
-
-    cidx = local_cells(rank)
+    touch = ((cells >= lo) & (cells < hi)).any(axis=1)
+    cidx = np.nonzero(touch)[0]
     cmin = cells[cidx].min(axis=1)
     own_c = (cmin >= lo) & (cmin < hi)
     # cells whose smallest vertex is owned first; both groups keep global order
@@ -134,14 +139,14 @@ def partition_mesh(coords, cells, bfacets, btags, rank, size, starts=None, metho
     lcells = g2l[cells[cidx]].astype(np.int32)
     # boundary facets with at least one owned vertex (the owned vertex's boundary term needs them);
     # their other vertices are in the 1-ring by construction
-    bfacets = np.asarray(bfacets).reshape(-1, max(coords.shape[1], 1))
+    bfacets = np.asarray(bfacets).reshape(-1, max(dim, 1))
     if bfacets.shape[0]:
         ftouch = ((bfacets >= lo) & (bfacets < hi)).any(axis=1)
         lbf = g2l[bfacets[ftouch]].astype(np.int32)
         lbt = np.asarray(btags)[ftouch].astype(np.int32)
         assert (lbf >= 0).all()
     else:
-        lbf, lbt = np.zeros((0, coords.shape[1]), np.int32), np.zeros(0, np.int32)
+        lbf, lbt = np.zeros((0, dim), np.int32), np.zeros(0, np.int32)
     # halo plan: receive segments
     neigh = np.unique(gown).astype(np.int32)
     recv_ptr = np.concatenate([[0], np.cumsum([(gown == r).sum() for r in neigh])]).astype(np.int64)
@@ -156,7 +161,8 @@ def partition_mesh(coords, cells, bfacets, btags, rank, size, starts=None, metho
         send_lists.append((mine - lo).astype(np.int32))
     send_ptr = np.concatenate([[0], np.cumsum([len(s) for s in send_lists])]).astype(np.int64)
     send_idx = np.concatenate(send_lists).astype(np.int32) if send_lists else np.zeros(0, np.int32)
-    return LocalPart(rank=rank, size=size, coords=coords[gvert].copy(), cells=lcells, bfacets=lbf, btags=lbt,
+    global_cell = cidx.astype(np.int64) if cell_gid is None else np.asarray(cell_gid, dtype=np.int64)[cidx]
+    return LocalPart(rank=rank, size=size, coords=coords_of(gvert), cells=lcells, bfacets=lbf, btags=lbt,
                      n_owned_vertices=hi - lo, n_owned_cells=n_owned_cells, global_vertex=gvert,
-                     global_cell=cidx.astype(np.int64), global_num_vertices=V, global_num_cells=int(cells.shape[0]),
+                     global_cell=global_cell, global_num_vertices=V, global_num_cells=int(num_global_cells),
                      vertex_starts=starts, neighbours=neigh, send_ptr=send_ptr, send_idx=send_idx, recv_ptr=recv_ptr)

@@ -96,6 +96,43 @@ def test_rcb_partition_of_an_unordered_mesh(arrays, size):
         assert np.prod(x.max(axis=0) - x.min(axis=0) + 1e-12) <= 1.0 / size * 3.5
 
 
+_FIELDS = ("coords", "cells", "bfacets", "btags", "global_vertex", "global_cell", "vertex_starts", "neighbours", "send_ptr",
+           "send_idx", "recv_ptr")
+
+
+@pytest.mark.parametrize("shape,size", [((5, 4, 6), 1), ((5, 4, 6), 2), ((5, 4, 6), 3), ((5, 4, 6), 7), ((3, 3, 2), 8),
+                                        ((8, 8, 8), 8), ((2, 2, 12), 5), ((16, 16, 16), 4)])
+def test_cube_slab_generated_without_the_global_mesh_equals_the_cut_of_the_global_mesh(shape, size):
+    """`cube_part` creates only the hexahedron layers around a rank's vertex block; every array of the result must equal
+    what `partition_mesh` extracts from the whole mesh (bench.py and UnitCubeMesh use it on several GPUs)."""
+    from movement_b200.mesh import cube_part
+
+    arrays = cube_arrays(*shape)
+    for rank in range(size):
+        ref = partition_mesh(*arrays, rank, size)
+        got = cube_part(*shape, rank, size)
+        for f in _FIELDS:
+            a, b = getattr(ref, f), getattr(got, f)
+            assert a.dtype == b.dtype and a.shape == b.shape and np.array_equal(a, b), (f, rank)
+        for f in ("n_owned_vertices", "n_owned_cells", "global_num_vertices", "global_num_cells", "rank", "size"):
+            assert getattr(ref, f) == getattr(got, f), (f, rank)
+
+
+@pytest.mark.parametrize("shape,size", [((7, 9), 1), ((7, 9), 2), ((7, 9), 3), ((7, 9), 8), ((3, 20), 4), ((32, 32), 5)])
+def test_square_slab_generated_without_the_global_mesh_equals_the_cut_of_the_global_mesh(shape, size):
+    from movement_b200.mesh import square_part
+
+    for L in ((1.0, 1.0), (2.0, 0.5)):
+        arrays = square_arrays(*shape, *L)
+        for rank in range(size):
+            ref = partition_mesh(*arrays, rank, size)
+            got = square_part(*shape, rank, size, *L)
+            for f in _FIELDS:
+                a, b = getattr(ref, f), getattr(got, f)
+                assert a.dtype == b.dtype and a.shape == b.shape and np.array_equal(a, b), (f, rank)
+            assert (ref.n_owned_vertices, ref.n_owned_cells, ref.global_num_cells) == (got.n_owned_vertices, got.n_owned_cells, got.global_num_cells)
+
+
 def test_unknown_partition_method():
     with pytest.raises(ValueError, match="unknown partition method"):
         partition_mesh(*square_arrays(3, 3), 0, 2, method="metis")
