@@ -279,6 +279,28 @@ int mv_ma_assemble_a(mv_mesh* m, const double* mon, const double* H, double* a);
  * (replaces: laplacian_smoothing.py:119, spring.py:274, mover.py:199-217)
  * stats[0..3] = max, min, mean, coefficient of variation                              */
 int mv_cell_volumes(mv_mesh* m, const double* coords, double* volume, double* stats);
+/* The same diagnostic for callers that cannot allocate device memory.  (No counterpart in the reference: this entry
+ * exists because of how the library is deployed, not because of a reference call site.)
+ * Who that is: a rank whose neighbour's peer-memory kernel is spinning on a flag -- cudaMalloc / cudaFree synchronise
+ * the device and would wait on that kernel; a process whose HBM is already owned by torch's caching allocator or by a
+ * full-size mover, where a diagnostic must not be the call that runs out of memory; a monitoring thread that may not
+ * block on the driver's allocator.  mv_cell_volumes needs an mv_mesh (whose creation allocates) and takes result slots
+ * from cudaMallocAsync per call; this variant needs no handle and calls no cudaMalloc, cudaMallocAsync, cudaFree or
+ * any routine that allocates.  Its scratch is one file-scope __device__ array of ~768 KB (csrc/mv_static.cu) that
+ * every GPU loading the library holds until the process exits.
+ *   dim 1..3; cells [C,dim+1] int32 and coords [*,dim] fp64 (P1 coordinates, not the DG layout of periodic meshes) are
+ *   DEVICE pointers and so is the output volume [C]; host pointers are refused with MV_ERR_BADARG because staging
+ *   them would allocate.  stats is a HOST array of 4: max, min, mean, coefficient of variation, over the C cells
+ *   given (no reduction over ranks).  C > 134 217 728 (2^27: 32768 CTAs of 4096 cells, the size of the scratch) is
+ *   refused with MV_ERR_UNSUPPORTED and a message naming the limit.
+ * The first call on each device looks up the device address of the scratch (cudaGetSymbolAddress, with that device
+ * current), which also makes the driver load the module there: make that first call before any stream capture
+ * begins.  All calls on a GPU share the one scratch, which keeps the previous call's partial results; the single word
+ * that must start at zero (the last-block ticket) is cleared at the start of every call.  Two calls that overlap on
+ * the GPU (different streams, different threads) race on it: serialise them.  Work goes to the mv_set_stream stream;
+ * the call returns after synchronising it.  Sums are folded in a fixed order that does not depend on the SM count.  */
+int mv_cell_volumes_static(int dim, int64_t C, const double* coords, const int32_t* cells, double* volume,
+                           double* stats);
 
 /* ---- Laplacian smoothing (replaces: laplacian_smoothing.py:64-77 + :109-117)
  * Solves K v = 0 per component with v prescribed where mask bit is set (values already in

@@ -80,6 +80,7 @@ SIGNATURES = {
     "mv_ma_hess_rhs": (_i, [_vp, _vp, _vp]),
     "mv_ma_assemble_a": (_i, [_vp, _vp, _vp, _vp]),
     "mv_cell_volumes": (_i, [_vp, _vp, _vp, _pd]),
+    "mv_cell_volumes_static": (_i, [_i, _i64, _vp, _vp, _vp, _pd]),
     "mv_laplace_move": (_i, [_vp, _vp, _vp, _d, _vp, _d, _d, _i, _pi, _pd]),
     "mv_spring_edge_count": (_i, [_vp, _pi64]),
     "mv_spring_edge_geometry": (_i, [_vp, _vp, _vp, _vp, _vp, _vp]),

@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libmovement_b200.so")
-SOURCES = ["mv_core.cu", "mv_ingest.cu", "mv_pcg.cu", "mv_pcg_soa.cu", "mv_cheb.cu", "mv_sched.cu", "mv_ma.cu", "mv_movers.cu", "mv_comm.cu", "mv_p2p.cu", "mv_amg.cu", "mv_amg_dist.cu", "mv_amg_cycle.cu", "mv_qn.cu", "mv_eqbc.cu", "mv_recovery.cu"]
+SOURCES = ["mv_core.cu", "mv_ingest.cu", "mv_pcg.cu", "mv_pcg_soa.cu", "mv_cheb.cu", "mv_sched.cu", "mv_ma.cu", "mv_movers.cu", "mv_comm.cu", "mv_p2p.cu", "mv_amg.cu", "mv_amg_dist.cu", "mv_amg_cycle.cu", "mv_qn.cu", "mv_eqbc.cu", "mv_recovery.cu", "mv_static.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
