@@ -40,21 +40,35 @@ def boundary_facet_geometry(coords, cells, bfacets):
     """Vectorised: adjacent cell, outward unit normal and measure of every boundary facet."""
     V, d = coords.shape
     d1 = d + 1
-    assert float(V) ** d < 9e18, "facet keys would overflow int64"
     faces = np.concatenate([np.delete(cells, loc, axis=1) for loc in range(d1)]).astype(np.int64)
     fcell = np.tile(np.arange(cells.shape[0]), d1)
     fopp = np.concatenate([cells[:, loc] for loc in range(d1)])
+    # Match every boundary facet with the cell facet that has the same (sorted) vertices.  Only facets made of boundary
+    # vertices can match, and the boundary vertices are renumbered 0..nb-1 first: the key ((v0*nb)+v1)*nb+v2 then needs
+    # nb^d < 2^63 instead of V^d (V^3 overflowed int64 above 126^3 cells; nb = 6n^2+2 stays far below at any size a
+    # host can hold).
+    bf = bfacets.astype(np.int64)
+    bverts = np.unique(bf)
+    nb = int(bverts.size)
+    assert float(nb) ** d < 9e18, "facet keys would overflow int64"
+    renum = np.full(V, -1, dtype=np.int64)
+    renum[bverts] = np.arange(nb)
+    rf = renum[faces]
+    cand = np.flatnonzero((rf >= 0).all(axis=1))
 
     def key(f):
         f = np.sort(f, axis=1)
         k = f[:, 0].copy()
         for a in range(1, d):
-            k = k * V + f[:, a]
+            k = k * nb + f[:, a]
         return k
 
-    fk = key(faces)
+    fk = key(rf[cand])
     order = np.argsort(fk, kind="stable")
-    pos = order[np.searchsorted(fk[order], key(bfacets.astype(np.int64)))]
+    bk = key(renum[bf])
+    at = np.searchsorted(fk[order], bk)
+    assert at.max(initial=0) < fk.size and np.array_equal(fk[order][at], bk), "a boundary facet belongs to no cell"
+    pos = cand[order[at]]
     cell, opp = fcell[pos], fopp[pos]
     fx = coords[bfacets]
     if d == 2:
