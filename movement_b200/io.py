@@ -4,6 +4,10 @@
 ``VTKFile("out.pvd").write(f, g, time=t)`` writes one ``out_<k>.vtu`` (XML UnstructuredGrid, ASCII) per call with the
 current coordinates of the functions' mesh and the functions as point (P1) or cell (P0) data, and keeps ``out.pvd``
 (the time-series index) up to date.  Host-side and small: fields are read through ``Function.dat.data_ro``.
+
+On a partitioned mesh (``movement_b200.parallel`` active) every rank writes its own piece ``out_<k>_<rank>.vtu`` holding
+the cells it OWNS (ghost cells would be drawn twice) with the local vertices they use, and rank 0 alone writes the
+``.pvd``, one ``<DataSet part="rank">`` per piece -- what Firedrake's parallel VTK output amounts to for a reader.
 """
 from __future__ import annotations
 
@@ -45,7 +49,15 @@ class VTKFile:
         xyz[:, :d] = np.asarray(mesh.coordinates.dat.data_ro).reshape(mesh.num_vertices(), d)
         cells = np.asarray(mesh.cells)
         k = len(self._entries)
-        path = f"{self._base}_{k}.vtu"
+        part = getattr(mesh, "part", None)
+        rank, nparts = 0, 1
+        if part is not None:
+            from . import parallel
+
+            rank, nparts = parallel.rank(), parallel.size()
+            cells = cells[:mesh.n_owned_cells]        # owned cells come first in the local numbering
+        ncell_out = cells.shape[0]
+        path = f"{self._base}_{k}_{rank}.vtu" if part is not None else f"{self._base}_{k}.vtu"
         with open(path, "w", encoding="utf-8") as f:
             f.write('<?xml version="1.0"?>\n<VTKFile type="UnstructuredGrid" version="0.1" byte_order="LittleEndian">\n')
             f.write(f'<UnstructuredGrid>\n<Piece NumberOfPoints="{xyz.shape[0]}" NumberOfCells="{cells.shape[0]}">\n<Points>\n')
@@ -72,12 +84,16 @@ class VTKFile:
             f.write("</PointData>\n<CellData>\n")
             for g in cell:
                 self._array(f, g.name or "function",
-                            np.asarray(g.dat.data_ro), 1)
+                            np.asarray(g.dat.data_ro)[:ncell_out], 1)
             f.write("</CellData>\n</Piece>\n</UnstructuredGrid>\n</VTKFile>\n")
-        self._entries.append((float(k) if time is None else float(time), os.path.basename(path)))
-        with open(self.filename, "w", encoding="utf-8") as f:
-            f.write('<?xml version="1.0"?>\n<VTKFile type="Collection" version="0.1" byte_order="LittleEndian">\n<Collection>\n')
-            for t, name in self._entries:
-                f.write(f'<DataSet timestep="{t:.17g}" part="0" file="{name}"/>\n')
-            f.write("</Collection>\n</VTKFile>\n")
+        base = os.path.basename(self._base)
+        names = [f"{base}_{k}_{r}.vtu" for r in range(nparts)] if part is not None else [os.path.basename(path)]
+        self._entries.append((float(k) if time is None else float(time), names))
+        if rank == 0:                                  # the other ranks' piece names are known without asking them
+            with open(self.filename, "w", encoding="utf-8") as f:
+                f.write('<?xml version="1.0"?>\n<VTKFile type="Collection" version="0.1" byte_order="LittleEndian">\n<Collection>\n')
+                for t, pieces in self._entries:
+                    for r, name in enumerate(pieces):
+                        f.write(f'<DataSet timestep="{t:.17g}" part="{r}" file="{name}"/>\n')
+                f.write("</Collection>\n</VTKFile>\n")
         return path

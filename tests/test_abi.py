@@ -117,3 +117,35 @@ def test_vtk_output_and_profiling_events(tmp_path):
     for cls, name in ((mv.MongeAmpereMover_Relaxation, "move"), (mv.MongeAmpereMover_QuasiNewton, "move"), (mv.LaplacianSmoother, "move"),
                       (mv.SpringMover_Lineal, "move"), (mv.MeshTanglingChecker, "check")):
         assert hasattr(getattr(cls, name), "__wrapped__")
+
+
+def test_vtk_output_of_a_partitioned_mesh_is_one_piece_per_rank(tmp_path, monkeypatch):
+    """every rank used to write the same out_<k>.vtu with its ghosts.  Now: out_<k>_<rank>.vtu with the owned
+    cells only, the .pvd (rank 0) lists all pieces; the pieces together hold every cell of the global mesh once."""
+    import xml.etree.ElementTree as ET
+
+    import movement_b200 as mv
+    from movement_b200 import parallel
+    from movement_b200.mesh import Mesh, square_arrays
+    from movement_b200.partition import partition_mesh
+
+    arrays = square_arrays(6, 5)
+    total, ghosts = 0, 0
+    for rank in (1, 0):                       # rank 0 last: it writes the index
+        monkeypatch.setattr(parallel, "_state", {"active": True, "rank": rank, "size": 2})
+        lp = partition_mesh(*arrays, rank, 2)
+        mesh = Mesh(lp.coords, lp.cells, lp.bfacets, lp.btags, part=lp, device="cpu")
+        vol = mv.Function(mesh.function_space("P0"), name="volume")
+        vol.dat.data[:] = np.arange(mesh.num_cells())
+        out = mv.VTKFile(str(tmp_path / "run.pvd"))
+        path = out.write(mesh.coordinates, vol, time=0.25)
+        assert path.endswith(f"run_0_{rank}.vtu")
+        piece = ET.parse(path).getroot().find("UnstructuredGrid").find("Piece")
+        assert int(piece.get("NumberOfCells")) == mesh.n_owned_cells <= mesh.num_cells()
+        ghosts += mesh.num_cells() - mesh.n_owned_cells
+        cd = np.array(piece.find("CellData").find("DataArray").text.split(), dtype=float)
+        assert np.array_equal(cd, np.arange(mesh.n_owned_cells))
+        total += mesh.n_owned_cells
+    assert total == arrays[1].shape[0] and ghosts > 0
+    sets = ET.parse(tmp_path / "run.pvd").getroot().find("Collection").findall("DataSet")
+    assert [(s.get("part"), s.get("file")) for s in sets] == [("0", "run_0_0.vtu"), ("1", "run_0_1.vtu")]
