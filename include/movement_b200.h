@@ -344,6 +344,10 @@ int mv_comm_info(int64_t* info);
  * neighbour via send_ptr) and the contiguous ghost range received from it.             */
 int mv_mesh_set_halo(mv_mesh* m, int n_neighbours, const int32_t* neighbour_ranks,
                      const int64_t* send_ptr, const int32_t* send_idx, const int64_t* recv_ptr);
+/* vec [V,ncomp] interleaved: ghost rows receive their owners' values.  With the peer-memory path active the call
+ * synchronises the stream and returns MV_ERR_COMM if a wait on a neighbour timed out (MV_P2P_TIMEOUT_S seconds, default
+ * 600, 0 = never): the ghosts of THIS call are then void; the status is reported once and the next exchange pairs up
+ * again as soon as the neighbour is back.                                                                       */
 int mv_halo_exchange(mv_mesh* m, int ncomp, double* vec);
 /* global numbers of the local cells [C] (host or device): the '+' cell of an interior edge (spring.py:113-127) is its
  * lowest-numbered incident cell in the GLOBAL numbering, which the local order (owned cells first) does not preserve */

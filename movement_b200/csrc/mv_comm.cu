@@ -407,7 +407,10 @@ extern "C" int mv_mesh_set_halo(mv_mesh* m, int nn, const int32_t* ranks, const 
 
 extern "C" int mv_halo_exchange(mv_mesh* m, int ncomp, double* vec) {
   if (!m || !vec) return MV_ERR_BADARG;
-  return halo_exchange(m, ncomp, vec);
+  MV_CHECK(halo_exchange(m, ncomp, vec));
+  // the public entry hands the ghosts to the host side: a peer-memory wait that timed out must not pass as data
+  if (comm_active() && p2p_active()) MV_CHECK(p2p_check_status());
+  return MV_OK;
 }
 
 extern "C" int mv_allreduce_sum(double* device_scalars, int n) { return allreduce_sum_dev(device_scalars, n); }

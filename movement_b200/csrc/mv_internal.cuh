@@ -298,6 +298,8 @@ struct mv_ma {
   double* mon_raw = nullptr;    // [V]
   double* dscal = nullptr;      // device scalars
   double* h_scal = nullptr;     // pinned
+  double gconst[3] = {0, 0, 0};  // allreduced constants of the mesh (cells, total volume, sum m_l^2); valid when gconst_ok
+  bool gconst_ok = false;
   int mon_kind = MV_MON_USER;
   double mon_params[8] = {0};
   double rtol = 1e-12, atol = 1e-50;

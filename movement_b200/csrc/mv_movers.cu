@@ -703,6 +703,7 @@ extern "C" int mv_spring_move(mv_mesh* m, double* coords, const double* forcing,
       MV_L k_zero_free<2><<<grid_for(n * 2), MV_BLOCK, 0, g_stream>>>(n, sm.as<uint16_t>(), u);
       MV_KERNEL_CHECK();
       st = spring_solve_amg(m, coords, dinv, sf.as<double>(), u, sm.as<uint16_t>(), rtol, atol, maxit, iters);
+      if (st == MV_OK) set_error("%s", "");   // the first attempt's message must not outlive a successful retry
     }
   } else {
     st = pcg_solve_spring(m, coords, dinv, sf.as<double>(), u, sm.as<uint16_t>(), rtol, atol, maxit, iters);

@@ -21,17 +21,22 @@
 // kernels themselves, so the exchange needs no host bookkeeping between launches.
 // Allreduce of n <= P2P_RED_MAX doubles (k_p2p_allreduce): one CTA stores its values into every peer's mailbox,
 // releases, acquires all peers' flags and combines the contributions in rank order -- bitwise identical on every rank.
-// Spin loops are bounded; a timeout raises a sticky device status that the next host poll turns into MV_ERR_COMM.
+// Spin loops are bounded by wall time (%globaltimer): MV_P2P_TIMEOUT_S seconds, default 600, 0 = wait for ever like NCCL
+// does.  A wait that times out (a neighbour stalled in host code for that long: hierarchy rebuild, a slow monitor
+// callback, a debugger) raises a device status that the next host poll reports ONCE as MV_ERR_COMM and clears: the
+// numbers of that solve are void, but the sequence counters advance at send time, so once the neighbour is back the
+// following exchanges pair up again and the communicator stays usable.
 #include "mv_internal.cuh"
 
 namespace mv {
 
 #define P2P_MAX_RANKS 16
 #define P2P_RED_MAX 64
-#define P2P_SPIN_MAX (1u << 26)   // ~1 us per poll: about a minute before a wait is declared dead
+#define P2P_TIMEOUT_DEFAULT_S 600.0
 
 struct P2PWindowLayout {
   size_t off_halo_flag, off_red_flag, off_red, off_slots, slot_bytes, total;
+  unsigned long long timeout_ns;   // 0: no time-out (rides along because every kernel receives the layout by value)
 };
 
 struct P2P {
@@ -59,13 +64,20 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
   asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 // wait until *p >= want; false on timeout
-__device__ __forceinline__ bool spin_until(const unsigned long long* p, unsigned long long want) {
-  for (unsigned it = 0; it < P2P_SPIN_MAX; ++it) {
+__device__ __forceinline__ bool spin_until(const unsigned long long* p, unsigned long long want, unsigned long long timeout_ns) {
+  if (ld_acquire_sys(p) >= want) return true;
+  const unsigned long long t0 = global_ns();
+  for (unsigned it = 1;; ++it) {
     if (ld_acquire_sys(p) >= want) return true;
     __nanosleep(20);
+    if (timeout_ns && (it & 1023u) == 0 && global_ns() - t0 > timeout_ns) return false;
   }
-  return false;
 }
 
 struct HaloArgs {
@@ -119,7 +131,7 @@ k_p2p_halo(HaloArgs h, int me, int C, const int* __restrict__ send_idx, T* __res
     const int64_t nr = h.recv_ptr[k + 1] - h.recv_ptr[k];
     const unsigned long long* flag = reinterpret_cast<const unsigned long long*>(mywin + lay.off_halo_flag) + h.ranks[k];
     __shared__ bool s_ok;
-    if (threadIdx.x == 0) s_ok = spin_until(flag, s_seq[k]);
+    if (threadIdx.x == 0) s_ok = spin_until(flag, s_seq[k], lay.timeout_ns);
     __syncthreads();
     if (!s_ok) {
       if (threadIdx.x == 0) *status = 1;
@@ -164,7 +176,7 @@ k_p2p_allreduce(RedArgs a, int me, int nranks, int n, int op, double* __restrict
   if (t == 0) s_ok = true;
   __syncthreads();
   if (t < nranks) {
-    if (!spin_until(reinterpret_cast<const unsigned long long*>(mywin + lay.off_red_flag) + t, s)) s_ok = false;
+    if (!spin_until(reinterpret_cast<const unsigned long long*>(mywin + lay.off_red_flag) + t, s, lay.timeout_ns)) s_ok = false;
   }
   __syncthreads();
   if (!s_ok) {
@@ -195,6 +207,9 @@ static P2PWindowLayout make_layout(int nranks, size_t window_bytes) {
   l.off_slots = off;
   l.slot_bytes = ((window_bytes - off) / ((size_t)2 * nranks)) & ~(size_t)255;
   l.total = off + l.slot_bytes * 2 * nranks;
+  const char* e = getenv("MV_P2P_TIMEOUT_S");
+  const double sec = e ? atof(e) : P2P_TIMEOUT_DEFAULT_S;
+  l.timeout_ns = sec > 0.0 ? (unsigned long long)(sec * 1e9) : 0ull;
   return l;
 }
 
@@ -285,9 +300,20 @@ static int p2p_halo_exchange_t(const Halo& h, int64_t nown, int C, T* vec, int64
     work += (ns > nr ? ns : nr) * C;
   }
   for (int k = 0; k <= h.nn; ++k) { a.send_ptr[k] = h.send_ptr[k]; a.recv_ptr[k] = h.recv_ptr[k]; }
-  // every CTA must be able to become resident while earlier ones spin: stay within one wave
+  // every CTA must be able to become resident while earlier ones spin: stay within one wave, as the occupancy
+  // calculator sees it for this instantiation (and never more than two CTAs per SM: room for a co-resident kernel)
   int grid = (int)((work + MV_BLOCK * 4 - 1) / (MV_BLOCK * 4));
-  const int cap = g_nsm > 0 ? g_nsm * 2 : 128;
+  static int per_sm[3][2] = {{0, 0}, {0, 0}, {0, 0}};
+  int& occ = per_sm[layout][sizeof(T) == 8 ? 1 : 0];
+  if (occ == 0) {
+    int nb = 0;
+    cudaError_t qe = layout == 1 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_p2p_halo<1, T>, MV_BLOCK, 0)
+                   : layout == 0 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_p2p_halo<0, T>, MV_BLOCK, 0)
+                                 : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_p2p_halo<2, T>, MV_BLOCK, 0);
+    if (qe != cudaSuccess) { cudaGetLastError(); nb = 1; }
+    occ = nb < 1 ? 1 : (nb > 2 ? 2 : nb);
+  }
+  const int cap = (g_nsm > 0 ? g_nsm : 64) * occ;
   if (grid > cap) grid = cap;
   if (grid < 1) grid = 1;
   if (layout == 1)
@@ -331,7 +357,10 @@ int p2p_check_status() {
   MV_CUDA(cudaMemcpyAsync(p.h_status, p.status, sizeof(int), cudaMemcpyDeviceToHost, g_stream));
   MV_CUDA(cudaStreamSynchronize(g_stream));
   if (*p.h_status) {
-    set_error("peer-memory collective timed out waiting for a neighbour (rank %d)", p.rank);
+    set_error("peer-memory collective timed out waiting for a neighbour (rank %d; MV_P2P_TIMEOUT_S = %.0f s); the results of "
+              "this call are void, the communicator stays usable", p.rank, (double)p.lay.timeout_ns * 1e-9);
+    *p.h_status = 0;
+    MV_CUDA(cudaMemsetAsync(p.status, 0, sizeof(int), g_stream));   // reported once, not for ever
     return MV_ERR_COMM;
   }
   return MV_OK;

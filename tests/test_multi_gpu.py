@@ -45,3 +45,15 @@ def test_two_rank_laplacian_spring_quasi_newton_match_oracle():
                           os.path.join(ROOT, "tests", "dist", "run_movers_2rank.py")],
                          capture_output=True, text=True, timeout=900)
     assert out.returncode == 0 and "DIST-MOVERS-OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
+
+
+def test_two_rank_peer_memory_timeout_is_reported_once_and_recovered_from():
+    """A neighbour that is late by more than MV_P2P_TIMEOUT_S fails ONE exchange with MV_ERR_COMM on the waiting rank;
+    the next exchanges succeed (csrc/mv_p2p.cu: wall-clock time-out, status cleared when reported)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29523",
+                          os.path.join(ROOT, "tests", "dist", "run_p2p_timeout_2rank.py")],
+                         capture_output=True, text=True, timeout=600, env=dict(os.environ, MV_P2P_TIMEOUT_S="2"))
+    assert out.returncode == 0 and "DIST-P2P-TIMEOUT-OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
