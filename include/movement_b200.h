@@ -195,6 +195,16 @@ int mv_amg_level_get(mv_mesh* m, int op, int level, int which, int64_t* size, in
  * Ghost entries of u are refreshed first on a partitioned mesh (hence non-const).                                 */
 int mv_recover_gradient_l2(mv_mesh* m, double* u, double* g, double rtol, int maxit, int* iters);
 int mv_clement_gradient(mv_mesh* m, int ncomp, double* u, double* out);
+/* replaces: movement/monitor.py:191-201, `Function(fs).project(self.solution)` -- the solution carried onto the mesh the
+ * monitor is asked for (a mover's moved copy).  Firedrake projects through a supermesh (third-party, unpinned); restated
+ * as the Galerkin L2 projection M_t u_t = int psi_i^t u_s with the (d+1)-point degree-2 rule on every target cell and
+ * u_s evaluated by point location in the source mesh (walk through face neighbours from the same-numbered cell): the
+ * identity when both meshes coincide, exact for globally linear fields, second order otherwise.  `src` / `tgt`: the two
+ * meshes as ingested (their xi coordinates), same dimension and domain, P1 coordinates, one GPU.  u_src [V_src], u_tgt
+ * [V_tgt] device pointers.  n_outside (optional): quadrature points the walk could not place inside a source cell
+ * (domains that differ); they take the linear extension of the last cell visited.                                    */
+int mv_project_p1(mv_mesh* src, const double* u_src, mv_mesh* tgt, double* u_tgt, double rtol, int maxit, int* iters,
+                  int64_t* n_outside);
 
 /* ---- Monge-Ampere pieces ---------------------------------------------------------- */
 int mv_ma_create(mv_mesh* m, mv_ma** out);

@@ -56,6 +56,7 @@ SIGNATURES = {
     "mv_ma_bind": (_i, [_vp, _i, _vp]),
     "mv_recover_gradient_l2": (_i, [_vp, _vp, _vp, _d, _i, _vp]),
     "mv_clement_gradient": (_i, [_vp, _i, _vp, _vp]),
+    "mv_project_p1": (_i, [_vp, _vp, _vp, _vp, _d, _i, _pi, _pi64]),
     "mv_ma_set_boundary": (_i, [_vp, _i, _vp]),
     "mv_ma_set_boundary_ex": (_i, [_vp, _i, _vp, _i, _vp, _vp]),
     "mv_ma_get_bcmask": (_i, [_vp, _vp]),

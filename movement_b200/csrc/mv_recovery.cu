@@ -51,6 +51,153 @@ k_clement_gradient(const double* __restrict__ xi, const int* __restrict__ cells,
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Projection of a P1 field between two meshes of the same domain (replaces: movement/monitor.py:191-201,
+// `Function(fs).project(self.solution)`, Firedrake's supermesh projection -- third-party, unpinned).  Restated as the
+// Galerkin L2 projection  M_t u_t = b,  b_i = int psi_i^t u_s dx,  with the integral taken by the (d+1)-point rule of
+// degree 2 on every TARGET cell (points with one barycentric coordinate A_D and the others B_D, equal weights): exact
+// when u_s is linear on the target cell -- so projecting onto the same mesh is the identity -- and second-order
+// accurate where a target cell straddles source cells.  u_s(x_q) needs the source cell that contains x_q: a straight
+// walk through face neighbours (found through the vertex->cell lists) that starts in the source cell with the target
+// cell's number -- for a mover's moved copy of the solution's mesh that is a few steps.
+// ---------------------------------------------------------------------------------------------------------------
+template <int D> struct QuadRule;
+template <> struct QuadRule<1> { static constexpr double A = 0.7886751345948129, B = 0.2113248654051871; };
+template <> struct QuadRule<2> { static constexpr double A = 2.0 / 3.0, B = 1.0 / 6.0; };
+template <> struct QuadRule<3> { static constexpr double A = 0.5854101966249685, B = 0.1381966011250105; };
+
+#define MV_WALK_MAX_STEPS (1 << 20)
+#define MV_WALK_TOL 1.0e-12
+
+// neighbour of cell c across the face opposite local vertex j (-1: boundary face)
+template <int D>
+__device__ __forceinline__ int64_t face_neighbour(const int* __restrict__ cells, const int* __restrict__ v2c_ptr,
+                                                  const int* __restrict__ v2c, int64_t c, const int (&cv)[D + 1], int j) {
+  const int f0 = cv[(j + 1) % (D + 1)];
+  for (int t = __ldg(&v2c_ptr[f0]), te = __ldg(&v2c_ptr[f0 + 1]); t < te; ++t) {
+    const int64_t c2 = __ldg(&v2c[t]) / (D + 1);
+    if (c2 == c) continue;
+    int cw[D + 1];
+    load_cell<D>(cells, c2, cw);
+    bool all = true;
+#pragma unroll
+    for (int k = 0; k <= D; ++k) {
+      if (k == j) continue;
+      bool found = false;
+#pragma unroll
+      for (int l = 0; l <= D; ++l) found = found || (cw[l] == cv[k]);
+      all = all && found;
+    }
+    if (all) return c2;
+  }
+  return -1;
+}
+
+// one thread per quadrature point of the target mesh: uq[c*(D+1)+q] = u_s(x_q); *outside counts the points the walk
+// could not place inside a source cell (left the domain through a boundary face, or ran out of steps): those take the
+// linear extension of the last cell visited
+template <int D>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_project_sample(const double* __restrict__ xt, const int* __restrict__ cells_t, int64_t Ct, const double* __restrict__ xs,
+                 const int* __restrict__ cells_s, int64_t Cs, const int* __restrict__ v2c_ptr, const int* __restrict__ v2c,
+                 const double* __restrict__ us, double* __restrict__ uq, unsigned long long* __restrict__ outside) {
+  const int64_t n = Ct * (D + 1);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t ct = i / (D + 1);
+    const int q = (int)(i - ct * (D + 1));
+    int cv[D + 1];
+    double xc[D + 1][D], p[D];
+    load_cell<D>(cells_t, ct, cv);
+    load_cell_coords<D>(xt, cv, xc);
+#pragma unroll
+    for (int a = 0; a < D; ++a) {
+      double t = 0.0;
+#pragma unroll
+      for (int j = 0; j <= D; ++j) t += (j == q ? QuadRule<D>::A : QuadRule<D>::B) * xc[j][a];
+      p[a] = t;
+    }
+    int64_t c = ct < Cs ? ct : 0;
+    double lam[D + 1];
+    bool inside = false;
+    for (int step = 0; step < MV_WALK_MAX_STEPS; ++step) {
+      CellGeom<D> g;
+      load_cell<D>(cells_s, c, cv);
+      load_cell_coords<D>(xs, cv, xc);
+      cell_geom(xc, g);
+      lam[0] = 1.0;
+#pragma unroll
+      for (int j = 1; j <= D; ++j) {
+        double l = 0.0;
+#pragma unroll
+        for (int a = 0; a < D; ++a) l += g.g[j][a] * (p[a] - xc[0][a]);
+        lam[j] = l;
+        lam[0] -= l;
+      }
+      // leave through the face with the most negative coordinate that has a neighbour behind it
+      bool tried[D + 1];
+#pragma unroll
+      for (int j = 0; j <= D; ++j) tried[j] = false;
+      int64_t next = -1;
+      bool any_negative = false;
+      for (int round = 0; round <= D && next < 0; ++round) {
+        int jm = -1;
+        double lm = -MV_WALK_TOL;
+#pragma unroll
+        for (int j = 0; j <= D; ++j)
+          if (!tried[j] && lam[j] < lm) { lm = lam[j]; jm = j; }
+        if (jm < 0) break;
+        any_negative = true;
+        tried[jm] = true;
+        next = face_neighbour<D>(cells_s, v2c_ptr, v2c, c, cv, jm);
+      }
+      if (!any_negative) { inside = true; break; }
+      if (next < 0) break;   // only boundary faces in the way
+      c = next;
+    }
+    if (!inside) atomicAdd(outside, 1ull);
+    double val = 0.0;
+#pragma unroll
+    for (int j = 0; j <= D; ++j) val += lam[j] * __ldg(&us[cv[j]]);
+    uq[i] = val;
+  }
+}
+
+// b_i = sum_{K ni i} |K| / (d+1) sum_q lambda_i(x_q) u_q  -- gathered per target vertex (no atomics, fixed order)
+template <int D>
+__global__ void __launch_bounds__(MV_BLOCK)
+k_project_rhs(const double* __restrict__ xt, const int* __restrict__ cells_t, const int* __restrict__ v2c_ptr,
+              const int* __restrict__ v2c, int64_t nrows, const double* __restrict__ uq, double* __restrict__ b) {
+  for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < nrows; v += (int64_t)gridDim.x * blockDim.x) {
+    double acc = 0.0;
+    for (int t = __ldg(&v2c_ptr[v]), te = __ldg(&v2c_ptr[v + 1]); t < te; ++t) {
+      const int e = __ldg(&v2c[t]);
+      const int64_t cell = e / (D + 1);
+      const int loc = e - (int)cell * (D + 1);
+      int cv[D + 1];
+      double xc[D + 1][D];
+      CellGeom<D> g;
+      load_cell<D>(cells_t, cell, cv);
+      load_cell_coords<D>(xt, cv, xc);
+      cell_geom(xc, g);
+      double sq = 0.0;
+#pragma unroll
+      for (int q = 0; q <= D; ++q) sq += (q == loc ? QuadRule<D>::A : QuadRule<D>::B) * __ldg(&uq[cell * (D + 1) + q]);
+      acc += g.vol * (1.0 / (D + 1)) * sq;
+    }
+    b[v] = acc;
+  }
+}
+
+template <int D>
+static int project_t(mv_mesh* src, const double* us, mv_mesh* tgt, double* uq, double* b, unsigned long long* d_out) {
+  MV_L k_project_sample<D><<<grid_for(tgt->C * (D + 1)), MV_BLOCK, 0, g_stream>>>(tgt->xi, tgt->cells, tgt->C, src->xi, src->cells, src->C,
+                                                                            src->v2c_ptr, src->v2c, us, uq, d_out);
+  MV_KERNEL_CHECK();
+  MV_L k_project_rhs<D><<<grid_for(tgt->V), MV_BLOCK, 0, g_stream>>>(tgt->xi, tgt->cells, tgt->v2c_ptr, tgt->v2c, tgt->V, uq, b);
+  MV_KERNEL_CHECK();
+  return MV_OK;
+}
+
 template <int D>
 static int clement_t(mv_mesh* m, int ncomp, const double* u, double* out) {
   const int grid = grid_for(m->Vown);
@@ -95,4 +242,41 @@ extern "C" int mv_recover_gradient_l2(mv_mesh* m, double* u, double* g, double r
   MV_CHECK(pcg_solve(m, MV_OP_MASS, m->dim, m->tmp_vec, g, nullptr, rtol, 1e-300, maxit, 0, iters, nullptr));
   if (comm_active()) MV_CHECK(halo_exchange(m, m->dim, g));
   return MV_OK;
+}
+
+extern "C" int mv_project_p1(mv_mesh* src, const double* u_src, mv_mesh* tgt, double* u_tgt, double rtol, int maxit, int* iters,
+                             int64_t* n_outside) {
+  if (!src || !tgt || !u_src || !u_tgt) return MV_ERR_BADARG;
+  if (!is_device_ptr(u_src) || !is_device_ptr(u_tgt)) {
+    set_error("mv_project_p1: device pointers required");
+    return MV_ERR_BADARG;
+  }
+  if (src->dim != tgt->dim || src->dg || tgt->dg) {
+    set_error("mv_project_p1: both meshes must have the same dimension and P1 (not periodic DG) coordinates");
+    return MV_ERR_UNSUPPORTED;
+  }
+  if (comm_active()) {
+    set_error("mv_project_p1: a quadrature point may lie in another rank's part of the source mesh; not supported on a partitioned mesh");
+    return MV_ERR_UNSUPPORTED;
+  }
+  double *uq = nullptr, *b = nullptr;
+  unsigned long long* d_out = nullptr;
+  MV_CHECK(dev_alloc(&uq, (size_t)tgt->C * (tgt->dim + 1)));
+  MV_CHECK(dev_alloc(&b, (size_t)tgt->V));
+  MV_CHECK(dev_alloc(&d_out, 1));
+  MV_CUDA(cudaMemsetAsync(d_out, 0, sizeof(unsigned long long), g_stream));
+  int st = MV_OK;
+  MV_DISPATCH_DIM(tgt->dim, st = project_t<DIM>(src, u_src, tgt, uq, b, d_out));
+  if (st == MV_OK) {
+    cudaMemsetAsync(u_tgt, 0, (size_t)tgt->V * sizeof(double), g_stream);
+    st = pcg_solve(tgt, MV_OP_MASS, 1, b, u_tgt, nullptr, rtol, 1e-300, maxit, 0, iters, nullptr);
+  }
+  unsigned long long h = 0;
+  cudaMemcpyAsync(&h, d_out, sizeof(h), cudaMemcpyDeviceToHost, g_stream);
+  cudaStreamSynchronize(g_stream);
+  if (n_outside) *n_outside = (int64_t)h;
+  dev_free(uq);
+  dev_free(b);
+  dev_free(d_out);
+  return st;
 }

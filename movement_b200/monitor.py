@@ -92,9 +92,10 @@ class SolutionBasedMonitorBuilder(MonitorBuilder, metaclass=abc.ABCMeta):
     """Abstract base class for monitor factories based on solution data (movement/monitor.py:174-201).
 
     The recovery operators run on the device (csrc/mv_recovery.cu) on the mesh the monitor is asked for.
-    ``projection`` is the identity when that mesh has the coordinates of the solution's mesh (the case of every test of
-    the reference, test/test_monitor.py); projecting between meshes with different coordinates is Firedrake's
-    supermesh projection, which this package does not have: NotImplementedError."""
+    ``projection`` carries the solution onto that mesh: the identity when it has the coordinates of the solution's mesh
+    (every test of the reference, test/test_monitor.py), otherwise -- a mover asking for the monitor on its moved copy --
+    the Galerkin L2 projection of ``mv_project_p1`` (degree-2 quadrature on the target cells, point location in the
+    source mesh).  Firedrake does this through a supermesh; nothing in the reference tree pins that operator."""
 
     recovery_rtol = 1.0e-12
 
@@ -107,23 +108,41 @@ class SolutionBasedMonitorBuilder(MonitorBuilder, metaclass=abc.ABCMeta):
         self.solution = solution
         self._dm = None
         self._dm_key = None
+        self._dm_src = None
+        self.projection_outside = 0     # quadrature points of the last projection that fell outside the source mesh
 
     def projection(self, mesh):
         """movement/monitor.py:191-201."""
+        import ctypes as C
+
         import torch
 
+        from . import parallel
+        from .core import device_mesh_from, use_current_stream
         from .mesh import Function
 
         src = self.solution.space.mesh
         same = mesh is src or (mesh.cells is src.cells or (mesh.cells.shape == src.cells.shape and bool((mesh.cells == src.cells).all())))
-        if not same or not torch.equal(mesh.coordinates.tensor, src.coordinates.tensor):
+        if same and torch.equal(mesh.coordinates.tensor, src.coordinates.tensor):
+            out = Function(mesh.function_space(self.solution.space.kind))
+            out.assign(self.solution)
+            return out
+        if self.solution.space.kind != "P1":
+            raise NotImplementedError(f"{type(self).__name__}.projection between meshes: only P1 solutions")
+        if parallel.is_active() or getattr(mesh, "periodic", False) or getattr(src, "periodic", False):
             raise NotImplementedError(
-                f"{type(self).__name__}.projection: the solution lives on a mesh with other coordinates; the reference "
-                "projects between the two meshes (Firedrake supermesh projection, movement/monitor.py:200-201), "
-                "which is not available here.  Re-evaluate the solution on the moved mesh in a torch callable instead.")
-        out = Function(mesh.function_space(self.solution.space.kind))
-        out.assign(self.solution)
-        return out
+                f"{type(self).__name__}.projection between meshes with different coordinates is not available on partitioned "
+                "or periodic meshes (mv_project_p1 locates points in the whole source mesh on one GPU)")
+        if self._dm_src is None:
+            self._dm_src = device_mesh_from(src)     # the solution's mesh does not move
+        tgt = self._device_mesh(mesh)
+        out = Function(mesh.function_space("P1"))
+        it, nout = C.c_int(0), C.c_int64(0)
+        use_current_stream()
+        L.check(L.load().mv_project_p1(self._dm_src.handle, L.ptr(self.solution.tensor), tgt.handle, L.ptr(out.tensor),
+                                       self.recovery_rtol, 1000, C.byref(it), C.byref(nout)))
+        self.projection_outside = int(nout.value)
+        return out.written()
 
     def _device_mesh(self, mesh):
         """Operators of `mesh` at its current coordinates (ingested again only when the coordinates changed)."""

@@ -367,6 +367,58 @@ def recover_hessian_clement(mesh, u):
     return g, clement_gradient(mesh, g)
 
 
+_PROJ_RULE = {1: (0.7886751345948129, 0.2113248654051871), 2: (2.0 / 3.0, 1.0 / 6.0), 3: (0.5854101966249685, 0.1381966011250105)}
+
+
+def p1_evaluate(mesh, u, points, chunk=256):
+    """u_h(p) for every row of `points`: brute force over all cells -- the cell whose smallest barycentric coordinate is
+    largest contains the point (P1 fields are continuous, so ties do not matter).  Returns (values, smallest coordinate)."""
+    x = mesh.coords[mesh.cells]                                   # [C, d+1, d]
+    _, grads = cell_geometry(mesh.coords, mesh.cells)
+    vals = np.empty(points.shape[0])
+    lmin = np.empty(points.shape[0])
+    for s0 in range(0, points.shape[0], chunk):
+        p = points[s0:s0 + chunk]
+        lam = np.einsum("cja,pca->pcj", grads, p[:, None, :] - x[None, :, 0, :])     # psi_j(p) - delta_j0
+        lam[:, :, 0] += 1.0
+        worst = lam.min(axis=2)
+        best = worst.argmax(axis=1)
+        rows = np.arange(p.shape[0])
+        vals[s0:s0 + chunk] = np.einsum("pj,pj->p", lam[rows, best], u[mesh.cells[best]])
+        lmin[s0:s0 + chunk] = worst[rows, best]
+    return vals, lmin
+
+
+def project_p1(src, u, tgt):
+    """movement/monitor.py:191-201, `Function(fs).project(self.solution)` from the solution's mesh `src` onto `tgt` (same
+    domain): Firedrake's supermesh projection is third-party and unpinned here; RESTATED as the Galerkin L2 projection
+    M_t u_t = b, b_i = int psi_i^t u_s, the integral by the (d+1)-point degree-2 rule on every target cell (one
+    barycentric coordinate A, the others B, equal weights).  Identity for coinciding meshes, exact for linear u."""
+    d = tgt.dim
+    A, B = _PROJ_RULE[d]
+    W = np.full((d + 1, d + 1), B) + (A - B) * np.eye(d + 1)     # W[q, j] = lambda_j(x_q)
+    xq = np.einsum("qj,cja->cqa", W, tgt.coords[tgt.cells])
+    uq = p1_evaluate(src, u, xq.reshape(-1, d))[0].reshape(-1, d + 1)
+    vol, _ = cell_geometry(tgt.coords, tgt.cells)
+    b = np.zeros(tgt.num_vertices)
+    contrib = (vol / (d + 1))[:, None] * (uq @ W)                # [C, j] = vol/(d+1) sum_q W[q,j] uq[q]
+    for loc in range(d + 1):
+        np.add.at(b, tgt.cells[:, loc], contrib[:, loc])
+    return spla.splu(assemble_mass(tgt.num_vertices, tgt.cells, vol).tocsc()).solve(b)
+
+
+def make_solution_monitor(src, u, gradient_scale_factor=None, hessian_scale_factor=None):
+    """The callable a mover evaluates every iteration (movement/monge_ampere.py:505-506 with a SolutionBasedMonitorBuilder):
+    x -> monitor on the mesh moved to x, the solution projected onto it first."""
+
+    def m(x):
+        tgt = OMesh(x, src.cells, src.bfacets, src.btags)
+        ut = u if np.array_equal(x, src.coords) else project_p1(src, u, tgt)
+        return solution_monitor(tgt, ut, gradient_scale_factor, hessian_scale_factor)
+
+    return m
+
+
 def solution_monitor(mesh, u, gradient_scale_factor=None, hessian_scale_factor=None):
     """movement/monitor.py:242-255 (gradient), :295-308 (Hessian), :346-365 (both): 1 + alpha gg / max|gg| + beta HH / max|HH|."""
     m = np.ones(mesh.num_vertices)
